@@ -1,0 +1,146 @@
+/*
+ * sqb200 — C ABI of the B200 (sm_100a) kernels behind sq-learn's quantum
+ * simulation path.
+ *
+ * The reference (federicomegler/sq-learn) has no FFI seam on this path: the
+ * estimators call sklearn/QuantumUtility/Utility.py by plain Python import
+ * (sklearn/cluster/_dmeans.py:40, sklearn/decomposition/_qPCA.py:27).  The
+ * boundary a maintainer binds is therefore this library, loaded with ctypes
+ * from the functions that keep the reference's Python names (INTEGRATION.md
+ * shows the stubs).  Each entry below cites the reference code it replaces.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - matrices are row-major (C order) fp64, labels int32, counts fp64
+ *     (exact integers < 2^53) so they share one all-reduce buffer;
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on
+ *     it and never synchronise;
+ *   - return value 0 = ok, otherwise see sq_status and sq_last_error();
+ *   - nothing is allocated behind the caller's back: scratch comes in through
+ *     (ws, ws_bytes), sized by the matching *_workspace_bytes();
+ *   - randomness is counter-based Philox4x32-10 keyed by (seed, offset +
+ *     element id, ...): results depend on (seed, offset) only, never on the
+ *     launch geometry or on how rows/vectors are sharded across GPUs.
+ */
+#ifndef SQB200_H
+#define SQB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum sq_status {
+    SQ_STATUS_OK = 0,
+    SQ_STATUS_INVALID = 1,     /* bad argument */
+    SQ_STATUS_CUDA = 2,        /* a CUDA runtime call failed */
+    SQ_STATUS_WORKSPACE = 3,   /* workspace missing or too small */
+    SQ_STATUS_UNSUPPORTED = 4  /* shape outside what this build supports */
+};
+
+/* Message of the last failing call on this host thread. */
+const char* sq_last_error(void);
+int sq_abi_version(void);
+
+/* ---- tomography --------------------------------------------------------- *
+ * real_tomography + QuantumState.measure + estimate_wald
+ * (sklearn/QuantumUtility/Utility.py:259-402, :51-55, :61-64), batched over B
+ * vectors of length d.  sched_host[0..sched_len) are the attempt sizes N
+ * (integers as doubles): one entry = single-shot mode (:365-398); the
+ * check_measure(np.geomspace(1,N,100)) schedule (:317-319, :414-422) =
+ * incremental mode, stopped at the first attempt with ||V-est|| <= delta when
+ * `stop` is set (:355-363).  norm_inf: 0 = L2, 1 = L-infinity (:356-359).
+ * Outputs: est[B,d], n_used[B] (N of the returned attempt), err[B]; optional
+ * (NULL to skip) trace[B,sched_len,d] = the estimate of every attempt made
+ * (the {N: estimate} dict real_tomography returns) and attempts[B].
+ * Vector b draws from the Philox stream (seed, vec_offset + b).           */
+int sq_tomography_max_fused_dim(void);
+int sq_tomography_batched(const double* V, long long B, int d, double delta, int norm_inf, int stop,
+                          const double* sched_host, int sched_len, unsigned long long seed,
+                          unsigned long long vec_offset, double* est, double* n_used, double* err, double* trace,
+                          int* attempts, void* stream);
+
+/* ---- q-means E-step ------------------------------------------------------ *
+ * labels_estimation (sklearn/cluster/_dmeans.py:732-777) with ipe /
+ * amplitude_estimation / median_evaluation (Utility.py:697-737, :442-531,
+ * :534-572) and select_labels (_dmeans.py:2252-2257) fused in.
+ * mode 0: exact argmin (delta == 0); 1: uniform pick in the delta window
+ * (true_distance_estimate=False); 2: IPE-estimated distances (True).
+ * xnorm[n] = ||x_i||^2 (sq_row_sqnorms).  Outputs: labels[n] int32,
+ * mindist[n] (may be NULL), inertia[1] = sum_i min_j D_ij, n_fixed[1] (may be
+ * NULL) = rows re-evaluated with the reference's exact arithmetic.          */
+size_t sq_qmeans_assign_workspace_bytes(long long n, int d, int k);
+int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, const double* C, int k, int mode,
+                     double delta, unsigned long long seed, unsigned long long offset, int* labels,
+                     double* mindist, double* inertia, int* n_fixed, void* ws, size_t ws_bytes, void* stream);
+
+/* row_norms(X, squared=True) (sklearn/utils/extmath.py:49-78) */
+int sq_row_sqnorms(const double* X, long long n, int d, double* out, void* stream);
+/* deterministic sum of n doubles; ws needs 8192 bytes */
+int sq_sum_f64(const double* v, long long n, double* out, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- q-means M-step ------------------------------------------------------ *
+ * _centers_update (sklearn/cluster/_dmeans.py:814-823): sums[k,d] and
+ * counts[k] of the rows carrying each label (this rank's rows only; the
+ * caller all-reduces sums and counts before sq_centroid_finalize).
+ * bad_label_flag[1] (may be NULL) is set to 1 if a label is outside [0,k).  */
+size_t sq_centroid_workspace_bytes(long long n, int d, int k);
+int sq_centroid_accumulate(const double* X, const int* labels, long long n, int d, int k, double* sums,
+                           double* counts, int* bad_label_flag, void* ws, size_t ws_bytes, void* stream);
+/* centres = sums / counts (np.true_divide, _dmeans.py:823); a cluster with
+ * no rows keeps c_old (the reference leaves that row uninitialised).        */
+int sq_centroid_finalize(const double* sums, const double* counts, const double* c_old, int k, int d,
+                         double* c_new, void* stream);
+/* squared_norm(a - b) (_dmeans.py:651), single deterministic reduction      */
+int sq_sqdiff_sum(const double* a, const double* b, long long n, double* out, void* stream);
+
+/* ---- scalar estimators --------------------------------------------------- *
+ * One outcome j in [0, M) per element of the law shared by
+ * amplitude_estimation (Utility.py:494-508) and phase_estimation
+ * (Utility.py:637-653): p(j) ~ 1/sin^2(pi (x - j)/M), x = M*omega, drawn in
+ * O(1) expected time.  The _bruteforce variant is the reference's O(M)
+ * inversion, kept as the device-side truth for tests.                       */
+int sq_fejer_sample(const double* M, const double* x, long long B, unsigned long long seed,
+                    unsigned long long offset, double* out_j, void* stream);
+int sq_fejer_sample_bruteforce(const double* M, const double* x, long long B, unsigned long long seed,
+                               unsigned long long offset, double* out_j, void* stream);
+/* out = x + TruncNormal(0,1;[-halfwidth, halfwidth]) per element:
+ * make_gaussian_est (Utility.py:88-104), introduce_error(_array) (:68-73).  */
+int sq_truncnorm_add(const double* x, long long L, double halfwidth, unsigned long long seed,
+                     unsigned long long offset, double* out, void* stream);
+/* Binomial(n_i, pl_i/(pl_i+pr_i)) per element: the sampler the tomography
+ * kernel splits its multinomial counts with (test hook; no reference
+ * counterpart beyond RandomState.choice, Utility.py:54).                    */
+int sq_binomial_sample(const double* n, const double* pl, const double* pr, long long B, unsigned long long seed,
+                       unsigned long long offset, double* out, void* stream);
+
+/* ---- mu-norm search -------------------------------------------------------- *
+ * best_mu / linear_search / __mu (Utility.py:196-231) for a whole p-grid in
+ * two streaming passes.  exp_row_host[g] = 2p_g, exp_col_host[g] = 2(1-p_g);
+ * exponent 0 means count_nonzero (:198-199).  Outputs (this rank's rows):
+ * rowmax[n_p], colsum[n_p, d], frob2[1].                                    */
+size_t sq_mu_norms_workspace_bytes(long long n, int d, int n_p);
+int sq_mu_norms(const double* X, long long n, int d, const double* exp_row_host, const double* exp_col_host, int n_p,
+                double* out_rowmax, double* out_colsum, double* out_frob2, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- Gram route for qPCA / condition number ------------------------------ *
+ * out_gram[d,d] = (X - mean)^T (X - mean) over this rank's rows on the fp64
+ * tensor cores (mean may be NULL: no centring).  New algorithm for the
+ * outputs of linalg.svd in qPCA._fit_full (sklearn/decomposition/_qPCA.py:
+ * 578-583) and np.linalg.svd in qMeans_.fit (sklearn/cluster/_dmeans.py:1244):
+ * sigma = sqrt(eig(G)), V = eigenvectors.                                   */
+size_t sq_gram_workspace_bytes(long long n, int d);
+int sq_gram_centered(const double* X, long long n, int d, const double* mean, double* out_gram, void* ws,
+                     size_t ws_bytes, void* stream);
+/* column sums of X (np.mean(X, axis=0) * n: _qPCA.py:578, _dmeans.py:1264) */
+size_t sq_col_sums_workspace_bytes(long long n, int d);
+int sq_col_sums(const double* X, long long n, int d, double* out, void* ws, size_t ws_bytes, void* stream);
+/* Y = X - mu row-wise (X -= X_mean, _dmeans.py:1266; _qPCA.py:579); Y may alias X */
+int sq_sub_rowvec(const double* X, const double* mu, long long n, int d, double* Y, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SQB200_H */

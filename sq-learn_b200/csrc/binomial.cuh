@@ -1,0 +1,94 @@
+// Exact binomial sampler for counts up to 2^52, used to draw the multinomial
+// measurement counts of the tomography kernel by conditional splitting.
+//
+// Reference behaviour being simulated: QuantumState.measure draws N outcomes
+// with RandomState.choice(p=probabilities) (Utility.py:51-55) and
+// estimate_wald counts them (Utility.py:61-64).  The vector of counts is
+// Multinomial(N, p); splitting N down a binary tree of bucket masses with one
+// Binomial(n_node, mass_left / mass_node) per node yields exactly that law at
+// O(#buckets) cost instead of O(N).
+//
+// Algorithms (published, restated here): sequential inversion (BINV,
+// Kachitvichyanukul & Schmeiser 1988) when n*min(p,q) < 10, otherwise
+// Hormann's transformed rejection with squeeze (BTRS, 1993) with Stirling
+// tail corrections.  Counts are carried as doubles (exact integers < 2^53).
+#pragma once
+#include "common.cuh"
+
+namespace sq {
+
+// Stirling series remainder: log(k!) - [ (k+1/2) log(k+1) - (k+1) + log(sqrt(2 pi)) ]
+__host__ __device__ inline double stirling_tail(double k) {
+    const double tab[10] = {0.08106146679532726, 0.04134069595540929, 0.02767792568499834,
+                            0.02079067210376509, 0.01664469118982119, 0.01387612882307075,
+                            0.01189670994589177, 0.01041126526197209, 0.009255462182712733,
+                            0.008330563433362871};
+    if (k <= 9.0) return tab[(int)k];
+    double kp1 = k + 1.0;
+    double kp1sq = kp1 * kp1;
+    return (1.0 / 12.0 - (1.0 / 360.0 - 1.0 / 1260.0 / kp1sq) / kp1sq) / kp1;
+}
+
+// Binomial(n, p) with p = pl / (pl + pr).  pl, pr >= 0 are the two bucket
+// masses, passed separately so that q = pr / (pl + pr) keeps full relative
+// accuracy when p is close to 1.
+__host__ __device__ inline double binomial_split(double n, double pl, double pr, Philox& rng) {
+    if (n <= 0.0 || pl <= 0.0) return 0.0;
+    if (pr <= 0.0) return n;
+    double tot = pl + pr;
+    bool flip = pl > pr;
+    double p = (flip ? pr : pl) / tot;  // p <= 1/2
+    double q = (flip ? pl : pr) / tot;
+    double k;
+    double np = n * p;
+    if (np < 10.0) {
+        // --- BINV: walk the pmf from 0 upwards ---
+        double s = p / q;
+        double a = (n + 1.0) * s;
+        double r0 = exp(n * log1p(-p));
+        double bound = fmin(n, np + 10.0 * sqrt(np * q + 1.0));
+        while (true) {
+            double u = rng.uniform();
+            double r = r0;
+            double x = 0.0;
+            bool ok = true;
+            while (u > r) {
+                u -= r;
+                x += 1.0;
+                if (x > bound) { ok = false; break; }
+                r *= (a / x - s);
+            }
+            if (ok) { k = x; break; }
+        }
+    } else {
+        // --- BTRS ---
+        double npq = np * q;
+        double spq = sqrt(npq);
+        double b = 1.15 + 2.53 * spq;
+        double a = -0.0873 + 0.0248 * b + 0.01 * p;
+        double c = np + 0.5;
+        double vr = 0.92 - 4.2 / b;
+        double alpha = (2.83 + 5.1 / b) * spq;
+        double r = p / q;
+        double m = floor((n + 1.0) * p);
+        while (true) {
+            double u, v;
+            rng.uniform2(u, v);
+            u -= 0.5;
+            double us = 0.5 - fabs(u);
+            k = floor((2.0 * a / us + b) * u + c);
+            if (us >= 0.07 && v <= vr) break;
+            if (k < 0.0 || k > n) continue;
+            v = log(v * alpha / (a / (us * us) + b));
+            double nm = n - m + 1.0;
+            double nk = n - k + 1.0;
+            double ub = (m + 0.5) * log((m + 1.0) / (r * nm)) + (n + 1.0) * log1p((k - m) / nk) +
+                        (k + 0.5) * log(r * nk / (k + 1.0)) + stirling_tail(m) + stirling_tail(n - m) -
+                        stirling_tail(k) - stirling_tail(n - k);
+            if (v <= ub) break;
+        }
+    }
+    return flip ? n - k : k;
+}
+
+}  // namespace sq

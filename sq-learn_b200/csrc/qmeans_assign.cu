@@ -1,0 +1,625 @@
+// K2 — q-means E-step: fp64 tensor-core distance GEMM fused with the noise
+// model and the arg-min, so the n x k distance matrix never reaches HBM.
+//
+// Replaces labels_estimation (sklearn/cluster/_dmeans.py:732-777), ipe
+// (sklearn/QuantumUtility/Utility.py:697-737), amplitude_estimation
+// (:442-531) + median_evaluation (:534-572) and select_labels
+// (_dmeans.py:2252-2257).  Three modes, as in the reference:
+//   EXACT  (delta == 0)               labels = argmin_j ||x_i - c_j||^2, exact
+//                                     ties broken uniformly at random (:771-772)
+//   WINDOW (delta > 0, !true_distance_estimate)   label drawn uniformly from
+//                                     {j : D_ij <= min_j D_ij + delta} (:740-751)
+//   IPE    (delta > 0, true_distance_estimate)    D_ij = |x|^2+|c|^2-2*ipe(x,c,delta/2),
+//                                     ipe = median of 13 amplitude-estimation
+//                                     draws (:753-769), then argmin
+// In every mode the reported inertia is sum_i min_j D_ij (:751, :773-775).
+//
+// Layout: X [n, d] and C [k, d] row-major fp64.  One CTA owns BM rows and
+// sweeps BN centroids at a time; X and C stream through a STAGES-deep
+// cp.async ring in k-chunks of 16, stored as [k/4][row][4] with the row
+// XOR-swizzled by (k/4) so both the async writes and the DMMA fragment reads
+// are bank-conflict free.  D = X C^T accumulates in registers with
+// mma.sync.m8n8k4.f64 (DMMA.8x8x4; tcgen05 has no fp64 kind).
+//
+// Bit-exact labels against cdist()**2: the GEMM form |c|^2 - 2 x.c rounds
+// differently from the reference's direct difference, so rows whose best and
+// second-best differ by less than a rounding bound are re-evaluated by
+// qmeans_fixup_kernel with the reference's own operation order (sequential
+// sum of squared differences, sqrt, square).
+#include "common.cuh"
+#include "sqb200.h"
+#include "fejer.cuh"
+
+namespace sq {
+
+enum AssignMode { MODE_EXACT = 0, MODE_WINDOW = 1, MODE_IPE = 2 };
+
+struct AssignArgs {
+    const double* X;       // [n, d]
+    const double* xnorm;   // [n]   ||x_i||^2
+    const double* C;       // [k, d]
+    const double* cnorm;   // [k]   ||c_j||^2
+    const double* rowmin_in;  // [n] optional precomputed min_j(|c_j|^2 - 2 x.c_j) (WINDOW, k > BN)
+    int* labels;           // [n]
+    double* mindist;       // [n]   min_j D_ij (clamped at 0)
+    double* rowmin_out;    // [n]   optional raw min (EXACT)
+    int* flag_count;       // [1]   number of near-tie rows
+    int* flag_rows;        // [n]   their indices
+    long long n;
+    int d, k;
+    int num_tiles;         // ceil(n / BM)
+    int NT, KC;            // centroid tiles, k-chunks
+    int mode;
+    double delta;
+    double tie_tol;        // relative rounding bound for the near-tie test
+    unsigned long long seed, offset;
+};
+
+template <int BM_, int BN_, int WARPS_M_, int WARPS_N_, int STAGES_>
+struct TileCfg {
+    static constexpr int BM = BM_, BN = BN_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, STAGES = STAGES_;
+    static constexpr int BK = 16, KB = BK / 4;
+    static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
+    static constexpr int MI = WM / 8, NI = WN / 8;
+    static constexpr int THREADS = 32 * WARPS_M * WARPS_N;
+    static constexpr int STAGE_DOUBLES = (BM + BN) * BK;
+    static_assert(WM % 8 == 0 && WN % 8 == 0, "warp tile must be a multiple of 8x8");
+};
+
+// ---- IPE noise model -------------------------------------------------------
+// One inner-product estimate turned into a squared distance (Utility.py:729-736
+// with _dmeans.py:765-769): returns 2*S*a_tilde, S = |x|^2+|c|^2.
+__device__ __noinline__ double ipe_distance(double dot, double xn, double cn, double eps, Philox rng) {
+    const double PI = 3.14159265358979323846;
+    double S = xn + cn;
+    if (!(S > 0.0)) return 0.0;
+    double a = (S - 2.0 * dot) / (2.0 * S);
+    if (a < 1e-15) a = 0.0;  // math.isclose(a, 0, abs_tol=1e-15); negatives are rounding noise
+    if (a > 1.0) a = 1.0;
+    double eps_a = eps * fmax(1.0, fabs(dot)) / S;
+    double M = ceil((PI / (2.0 * eps_a)) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
+    double x = M * (asin(sqrt(a)) / PI);
+    // median of Q = 13 draws (median_evaluation with gamma = 0.1)
+    double s[13];
+#pragma unroll 1
+    for (int q = 0; q < 13; ++q) {
+        double j = fejer_sample(M, x, rng);
+        double sn = sinpi(j / M);
+        double val = sn * sn;
+        int p = q;
+        while (p > 0 && s[p - 1] > val) { s[p] = s[p - 1]; --p; }
+        s[p] = val;
+    }
+    return 2.0 * S * s[6];
+}
+
+template <class Cfg, bool VEC16>
+__device__ __forceinline__ void load_chunk(double* stage, const AssignArgs& a, long long r0, int n0, int kc, int tid) {
+    constexpr int BM = Cfg::BM, BN = Cfg::BN;
+    constexpr int PPR = VEC16 ? 8 : 16;           // pieces per row per chunk
+    constexpr int PIECES = (BM + BN) * PPR;
+    double* As = stage;
+    double* Bs = stage + BM * Cfg::BK;
+    for (int p = tid; p < PIECES; p += Cfg::THREADS) {
+        int row = p / PPR, kp = p % PPR;
+        int kk = VEC16 ? kp * 2 : kp;             // k offset inside the chunk
+        int kglob = kc * Cfg::BK + kk;
+        int kb = kk >> 2;
+        bool isA = row < BM;
+        int lr = isA ? row : row - BM;
+        const double* src;
+        bool ok;
+        if (isA) {
+            long long gr = r0 + lr;
+            ok = (gr < a.n) && (kglob < a.d);
+            src = a.X + (ok ? gr * (long long)a.d + kglob : 0);
+        } else {
+            int gc = n0 + lr;
+            ok = (gc < a.k) && (kglob < a.d);
+            src = a.C + (ok ? (long long)gc * a.d + kglob : 0);
+        }
+        double* base = isA ? As : Bs;
+        int rows = isA ? BM : BN;
+        double* dst = base + ((kb * rows + (lr ^ kb)) << 2) + (kk & 3);
+        if (VEC16) cp_async16(dst, src, ok); else cp_async8(dst, src, ok);
+    }
+}
+
+template <class Cfg, bool VEC16, int MODE>
+__global__ void __launch_bounds__(Cfg::THREADS, 1) qmeans_assign_kernel(AssignArgs a) {
+    constexpr int BM = Cfg::BM, BN = Cfg::BN, MI = Cfg::MI, NI = Cfg::NI, WN_CNT = Cfg::WARPS_N;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ __align__(16) double smem[];
+    double* stages = smem;                                   // STAGES * STAGE_DOUBLES
+    double* red_m1 = stages + STAGES * Cfg::STAGE_DOUBLES;   // [BM][WN_CNT]
+    double* red_m2 = red_m1 + BM * WN_CNT;                   // [BM][WN_CNT]
+    double* run_m1 = red_m2 + BM * WN_CNT;                   // [BM]
+    double* run_m2 = run_m1 + BM;                            // [BM]
+    double* row_thr = run_m2 + BM;                           // [BM]
+    unsigned long long* cand = (unsigned long long*)(row_thr + BM);  // [BM]
+    int* red_a1 = (int*)(cand + BM);                         // [BM][WN_CNT]
+    int* run_a1 = red_a1 + BM * WN_CNT;                      // [BM]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp / WN_CNT, wn = warp % WN_CNT;
+    const int lq = lane >> 2, lr4 = lane & 3;
+
+    // tiles owned by this CTA: blockIdx.x, + gridDim.x, ...
+    const int my_tiles = (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int per_tile = a.NT * a.KC;
+    const long long total = (long long)my_tiles * per_tile;
+
+    auto issue = [&](long long q) {
+        if (q < total) {
+            int tl = (int)(q / per_tile);
+            int rem = (int)(q % per_tile);
+            int nt = rem / a.KC, kc = rem % a.KC;
+            long long tile = (long long)blockIdx.x + (long long)tl * gridDim.x;
+            load_chunk<Cfg, VEC16>(stages + (q % STAGES) * Cfg::STAGE_DOUBLES, a, tile * BM, nt * BN, kc, tid);
+        }
+        cp_async_commit();
+    };
+
+    for (int s = 0; s < STAGES - 1; ++s) issue(s);
+
+    double acc[MI][NI][2];
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    int kc = 0, nt = 0, tl = 0;
+    for (long long q = 0; q < total; ++q) {
+        cp_async_wait<STAGES - 2>();
+        __syncthreads();
+        issue(q + STAGES - 1);
+
+        const double* As = stages + (q % STAGES) * Cfg::STAGE_DOUBLES;
+        const double* Bs = As + BM * Cfg::BK;
+#pragma unroll
+        for (int kb = 0; kb < Cfg::KB; ++kb) {
+            double af[MI], bf[NI];
+#pragma unroll
+            for (int i = 0; i < MI; ++i) af[i] = As[((kb * BM + ((wm * Cfg::WM + i * 8 + lq) ^ kb)) << 2) + lr4];
+#pragma unroll
+            for (int j = 0; j < NI; ++j) bf[j] = Bs[((kb * BN + ((wn * Cfg::WN + j * 8 + lq) ^ kb)) << 2) + lr4];
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < NI; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+        }
+
+        if (kc == a.KC - 1) {
+            // ------------------------------ epilogue ------------------------------
+            const long long tile = (long long)blockIdx.x + (long long)tl * gridDim.x;
+            const long long r0 = tile * BM;
+            const int n0 = nt * BN;
+            const bool last_nt = (nt == a.NT - 1);
+
+            if (MODE == MODE_IPE) {
+                // replace every dot product by its noisy squared distance minus |x|^2
+#pragma unroll
+                for (int i = 0; i < MI; ++i) {
+                    long long gr = r0 + wm * Cfg::WM + i * 8 + lq;
+                    double xn = (gr < a.n) ? a.xnorm[gr] : 0.0;
+#pragma unroll
+                    for (int j = 0; j < NI; ++j)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            int col = n0 + wn * Cfg::WN + j * 8 + lr4 * 2 + e;
+                            if (gr < a.n && col < a.k) {
+                                Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x1bE0u, (unsigned)col);
+                                double cn = a.cnorm[col];
+                                double dt = ipe_distance(acc[i][j][e], xn, cn, 0.5 * a.delta, rng);
+                                // store in the same form the other modes use: v = D - |x|^2 = cn - 2*dot
+                                acc[i][j][e] = 0.5 * (cn - (dt - xn));
+                            }
+                        }
+                }
+            }
+
+            if (MODE == MODE_WINDOW && nt == 0 && tid < BM) cand[tid] = ~0ull;
+
+            // per-thread top-2 over its 2*NI columns, per row fragment
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                double m1 = INFINITY, m2 = INFINITY;
+                int a1 = 0x7fffffff;
+#pragma unroll
+                for (int j = 0; j < NI; ++j)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        int col = n0 + wn * Cfg::WN + j * 8 + lr4 * 2 + e;
+                        if (col < a.k) {
+                            double v = a.cnorm[col] - 2.0 * acc[i][j][e];
+                            if (v < m1) { m2 = m1; m1 = v; a1 = col; }
+                            else if (v < m2) m2 = v;
+                        }
+                    }
+                // merge across the 4 lanes that share this row
+#pragma unroll
+                for (int o = 1; o <= 2; o <<= 1) {
+                    double om1 = __shfl_xor_sync(0xffffffffu, m1, o);
+                    double om2 = __shfl_xor_sync(0xffffffffu, m2, o);
+                    int oa1 = __shfl_xor_sync(0xffffffffu, a1, o);
+                    if (om1 < m1 || (om1 == m1 && oa1 < a1)) { m2 = fmin(m1, om2); m1 = om1; a1 = oa1; }
+                    else m2 = fmin(m2, om1);
+                }
+                if (lr4 == 0) {
+                    int row = wm * Cfg::WM + i * 8 + lq;
+                    red_m1[row * WN_CNT + wn] = m1;
+                    red_m2[row * WN_CNT + wn] = m2;
+                    red_a1[row * WN_CNT + wn] = a1;
+                }
+            }
+            __syncthreads();
+            if (tid < BM) {
+                const int row = tid;
+                double m1 = red_m1[row * WN_CNT], m2 = red_m2[row * WN_CNT];
+                int a1 = red_a1[row * WN_CNT];
+                for (int w = 1; w < WN_CNT; ++w) {
+                    double om1 = red_m1[row * WN_CNT + w], om2 = red_m2[row * WN_CNT + w];
+                    int oa1 = red_a1[row * WN_CNT + w];
+                    if (om1 < m1 || (om1 == m1 && oa1 < a1)) { m2 = fmin(m1, om2); m1 = om1; a1 = oa1; }
+                    else m2 = fmin(m2, om1);
+                }
+                if (nt > 0) {
+                    double om1 = run_m1[row], om2 = run_m2[row];
+                    int oa1 = run_a1[row];
+                    if (om1 < m1 || (om1 == m1 && oa1 < a1)) { m2 = fmin(m1, om2); m1 = om1; a1 = oa1; }
+                    else m2 = fmin(m2, om1);
+                }
+                run_m1[row] = m1; run_m2[row] = m2; run_a1[row] = a1;
+                if (MODE == MODE_WINDOW) {
+                    long long gr = r0 + row;
+                    double base = (a.rowmin_in && gr < a.n) ? a.rowmin_in[gr] : m1;
+                    row_thr[row] = base + a.delta;
+                }
+                if (last_nt && MODE != MODE_WINDOW) {
+                    long long gr = r0 + row;
+                    if (gr < a.n) {
+                        double xn = a.xnorm[gr];
+                        a.labels[gr] = a1;
+                        a.mindist[gr] = fmax(xn + m1, 0.0);
+                        if (a.rowmin_out) a.rowmin_out[gr] = m1;
+                        if (MODE == MODE_EXACT && m2 < INFINITY && (m2 - m1) <= a.tie_tol * (xn + fabs(m1) + fabs(m2))) {
+                            int slot = atomicAdd(a.flag_count, 1);
+                            a.flag_rows[slot] = (int)gr;  // n < 2^31 per call (checked on the host)
+                        }
+                    }
+                }
+            }
+            if (MODE == MODE_WINDOW) {
+                __syncthreads();
+                // uniform pick inside the window: smallest random priority wins
+#pragma unroll
+                for (int i = 0; i < MI; ++i) {
+                    int row = wm * Cfg::WM + i * 8 + lq;
+                    long long gr = r0 + row;
+                    double thr = row_thr[row];
+                    unsigned long long best = ~0ull;
+#pragma unroll
+                    for (int j = 0; j < NI; ++j)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            int col = n0 + wn * Cfg::WN + j * 8 + lr4 * 2 + e;
+                            if (col < a.k) {
+                                double v = a.cnorm[col] - 2.0 * acc[i][j][e];
+                                if (v <= thr) {
+                                    Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, (unsigned)col);
+                                    unsigned r[4];
+                                    rng.block(r);
+                                    unsigned long long key = ((unsigned long long)r[0] << 32) | (unsigned)col;
+                                    best = key < best ? key : best;
+                                }
+                            }
+                        }
+#pragma unroll
+                    for (int o = 1; o <= 2; o <<= 1) {
+                        unsigned long long ob = __shfl_xor_sync(0xffffffffu, best, o);
+                        best = ob < best ? ob : best;
+                    }
+                    if (lr4 == 0 && best != ~0ull) atomicMin(&cand[row], best);
+                }
+                __syncthreads();
+                if (tid < BM && last_nt) {
+                    long long gr = r0 + tid;
+                    if (gr < a.n) {
+                        unsigned long long c = cand[tid];
+                        // with a precomputed row minimum the argmin itself is always a candidate
+                        a.labels[gr] = (c == ~0ull) ? run_a1[tid] : (int)(unsigned)(c & 0xffffffffu);
+                        double base = a.rowmin_in ? a.rowmin_in[gr] : run_m1[tid];
+                        a.mindist[gr] = fmax(a.xnorm[gr] + base, 0.0);
+                    }
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        }
+
+        if (++kc == a.KC) { kc = 0; if (++nt == a.NT) { nt = 0; ++tl; } }
+    }
+    cp_async_wait<0>();
+}
+
+// ---- near-tie rows: the reference's own arithmetic ---------------------------
+// cdist(X, C, "euclidean")**2 (_dmeans.py:736-737): s = sum_t (x_t - c_t)^2 in
+// index order without fused multiply-add, then sqrt, then square.  One warp
+// per flagged row, lanes over centroids; exact ties broken uniformly (:772).
+__global__ void qmeans_fixup_kernel(AssignArgs a) {
+    const int nflag = *a.flag_count;
+    const int lane = threadIdx.x & 31;
+    const int wglobal = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int f = wglobal; f < nflag; f += nwarps) {
+        const long long gr = a.flag_rows[f];
+        const double* x = a.X + gr * (long long)a.d;
+        double best = INFINITY;
+        for (int j = lane; j < a.k; j += 32) {
+            const double* c = a.C + (long long)j * a.d;
+            double s = 0.0;
+            for (int t = 0; t < a.d; ++t) {
+                double df = __dsub_rn(x[t], c[t]);
+                s = __dadd_rn(s, __dmul_rn(df, df));
+            }
+            double r = __dsqrt_rn(s);
+            double dd = __dmul_rn(r, r);
+            best = fmin(best, dd);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
+        // count exact ties and pick the r-th of them uniformly
+        int ties = 0;
+        for (int j0 = 0; j0 < a.k; j0 += 32) {
+            int j = j0 + lane;
+            bool hit = false;
+            if (j < a.k) {
+                const double* c = a.C + (long long)j * a.d;
+                double s = 0.0;
+                for (int t = 0; t < a.d; ++t) {
+                    double df = __dsub_rn(x[t], c[t]);
+                    s = __dadd_rn(s, __dmul_rn(df, df));
+                }
+                double r = __dsqrt_rn(s);
+                hit = (__dmul_rn(r, r) == best);
+            }
+            ties += __popc(__ballot_sync(0xffffffffu, hit));
+        }
+        Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x71E5u, 0u);
+        int pick = (int)(rng.uniform() * ties);
+        if (pick >= ties) pick = ties - 1;
+        int label = -1, seen = 0;
+        for (int j0 = 0; j0 < a.k && label < 0; j0 += 32) {
+            int j = j0 + lane;
+            bool hit = false;
+            if (j < a.k) {
+                const double* c = a.C + (long long)j * a.d;
+                double s = 0.0;
+                for (int t = 0; t < a.d; ++t) {
+                    double df = __dsub_rn(x[t], c[t]);
+                    s = __dadd_rn(s, __dmul_rn(df, df));
+                }
+                double r = __dsqrt_rn(s);
+                hit = (__dmul_rn(r, r) == best);
+            }
+            unsigned m = __ballot_sync(0xffffffffu, hit);
+            int cnt = __popc(m);
+            if (pick < seen + cnt) {
+                int want = pick - seen;
+                for (int b = 0; b < 32; ++b)
+                    if (m >> b & 1) { if (want == 0) { label = j0 + b; break; } --want; }
+            }
+            seen += cnt;
+        }
+        if (lane == 0) {
+            a.labels[gr] = label;
+            a.mindist[gr] = best;
+        }
+    }
+}
+
+// ---- ||row||^2 of a row-major matrix (row_norms(X, squared=True), extmath.py:49-78)
+__global__ void row_sqnorm_kernel(const double* __restrict__ X, long long n, int d, double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (; w < n; w += nw) {
+        const double* x = X + w * (long long)d;
+        double s = 0.0;
+        if ((d & 1) == 0) {
+            const double2* x2 = reinterpret_cast<const double2*>(x);
+            for (int t = lane; t < d / 2; t += 32) { double2 v = x2[t]; s = fma(v.x, v.x, s); s = fma(v.y, v.y, s); }
+        } else {
+            for (int t = lane; t < d; t += 32) { double v = x[t]; s = fma(v, v, s); }
+        }
+        s = warp_sum(s);
+        if (lane == 0) out[w] = s;
+    }
+}
+
+// deterministic sum of an array: fixed grid, fixed per-block order, second pass by one block
+__global__ void sum_partial_kernel(const double* __restrict__ v, long long n, double* __restrict__ part) {
+    __shared__ double red[32];
+    double s = 0.0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) s += v[i];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        part[blockIdx.x] = t;
+    }
+}
+__global__ void sum_final_kernel(const double* __restrict__ part, int np, double* __restrict__ out) {
+    __shared__ double red[32];
+    double s = 0.0;
+    for (int i = threadIdx.x; i < np; i += blockDim.x) s += part[i];
+    s = warp_sum(s);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        *out = t;
+    }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+struct AssignWs {
+    int* flag_count;
+    int* flag_rows;
+    double* cnorm;
+    double* rowmin;
+    double* partial;
+    double* mindist;
+};
+static const int SUM_BLOCKS = 1024;
+
+static size_t assign_ws_layout(long long n, int k, AssignWs* w, char* base) {
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return base ? base + o : nullptr; };
+    char* p;
+    p = take(256);                           if (w) w->flag_count = (int*)p;
+    p = take((size_t)n * sizeof(int));       if (w) w->flag_rows = (int*)p;
+    p = take((size_t)k * sizeof(double));    if (w) w->cnorm = (double*)p;
+    p = take((size_t)n * sizeof(double));    if (w) w->rowmin = (double*)p;
+    p = take((size_t)SUM_BLOCKS * sizeof(double)); if (w) w->partial = (double*)p;
+    p = take((size_t)n * sizeof(double));    if (w) w->mindist = (double*)p;
+    return off;
+}
+
+template <class Cfg>
+static size_t assign_smem_bytes() {
+    return (size_t)Cfg::STAGES * Cfg::STAGE_DOUBLES * 8 + (size_t)Cfg::BM * Cfg::WARPS_N * (8 + 8 + 4) +
+           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4) + 64;
+}
+
+template <class Cfg>
+static int launch_assign(AssignArgs a, cudaStream_t stream) {
+    a.num_tiles = (int)((a.n + Cfg::BM - 1) / Cfg::BM);
+    a.NT = (a.k + Cfg::BN - 1) / Cfg::BN;
+    a.KC = (a.d + Cfg::BK - 1) / Cfg::BK;
+    int grid = device_sm_count();
+    if (grid > a.num_tiles) grid = a.num_tiles;
+    size_t smem = assign_smem_bytes<Cfg>();
+    bool vec16 = (a.d & 1) == 0 && ((uintptr_t)a.X & 15) == 0 && ((uintptr_t)a.C & 15) == 0;
+#define SQ_LAUNCH_ASSIGN(V, M)                                                                                       \
+    do {                                                                                                            \
+        SQ_CUDA(cudaFuncSetAttribute(qmeans_assign_kernel<Cfg, V, M>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+                                     (int)smem));                                                                   \
+        qmeans_assign_kernel<Cfg, V, M><<<grid, Cfg::THREADS, smem, stream>>>(a);                                   \
+    } while (0)
+    if (vec16) {
+        if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT);
+        else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW);
+        else SQ_LAUNCH_ASSIGN(true, MODE_IPE);
+    } else {
+        if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(false, MODE_EXACT);
+        else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(false, MODE_WINDOW);
+        else SQ_LAUNCH_ASSIGN(false, MODE_IPE);
+    }
+#undef SQ_LAUNCH_ASSIGN
+    SQ_LAUNCH_CHECK("qmeans_assign_kernel");
+    return SQ_OK;
+}
+
+// tile shapes: wide (all of k <= 256 in one sweep) down to narrow for tiny k
+using CfgN256 = TileCfg<64, 256, 2, 8, 4>;   // 512 threads, 160 KB ring
+using CfgN128 = TileCfg<128, 128, 4, 4, 4>;  // 512 threads, 128 KB ring
+using CfgN64 = TileCfg<128, 64, 4, 2, 4>;    // 256 threads
+using CfgN32 = TileCfg<128, 32, 4, 1, 4>;    // 128 threads
+using CfgN16 = TileCfg<256, 16, 8, 1, 4>;    // 256 threads, k <= 16
+
+static int dispatch_assign(const AssignArgs& a, cudaStream_t stream, int* bn_used) {
+    int k = a.k;
+    if (k <= 16) { *bn_used = 16; return launch_assign<CfgN16>(a, stream); }
+    if (k <= 32) { *bn_used = 32; return launch_assign<CfgN32>(a, stream); }
+    if (k <= 64) { *bn_used = 64; return launch_assign<CfgN64>(a, stream); }
+    if (k <= 128) { *bn_used = 128; return launch_assign<CfgN128>(a, stream); }
+    *bn_used = 256;
+    return launch_assign<CfgN256>(a, stream);
+}
+
+}  // namespace sq
+
+using namespace sq;
+
+extern "C" int sq_row_sqnorms(const double* X, long long n, int d, double* out, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(X && out && n >= 0 && d >= 1, "sq_row_sqnorms: bad arguments");
+    if (n == 0) return SQ_OK;
+    long long blocks = (n + 7) / 8;
+    int cap = device_sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    row_sqnorm_kernel<<<(int)blocks, 256, 0, stream>>>(X, n, d, out);
+    SQ_LAUNCH_CHECK("row_sqnorm_kernel");
+    return SQ_OK;
+}
+
+extern "C" int sq_sum_f64(const double* v, long long n, double* out, void* ws, size_t ws_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(v && out && n >= 0, "sq_sum_f64: bad arguments");
+    if (ws_bytes < SUM_BLOCKS * sizeof(double) || !ws) { set_error("sq_sum_f64: workspace needs %d bytes", (int)(SUM_BLOCKS * sizeof(double))); return SQ_ERR_WORKSPACE; }
+    sum_partial_kernel<<<SUM_BLOCKS, 256, 0, stream>>>(v, n, (double*)ws);
+    SQ_LAUNCH_CHECK("sum_partial_kernel");
+    sum_final_kernel<<<1, 1024, 0, stream>>>((double*)ws, SUM_BLOCKS, out);
+    SQ_LAUNCH_CHECK("sum_final_kernel");
+    return SQ_OK;
+}
+
+extern "C" size_t sq_qmeans_assign_workspace_bytes(long long n, int d, int k) {
+    (void)d;
+    return assign_ws_layout(n, k, nullptr, nullptr);
+}
+
+extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, const double* C, int k,
+                                int mode, double delta, unsigned long long seed, unsigned long long offset,
+                                int* labels, double* mindist, double* inertia, int* n_fixed, void* ws,
+                                size_t ws_bytes, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(X && xnorm && C && labels && inertia, "sq_qmeans_assign: null pointer");
+    SQ_REQUIRE(n >= 1 && n < 2147483647LL && d >= 1 && k >= 1, "sq_qmeans_assign: bad shape n=%lld d=%d k=%d", n, d, k);
+    SQ_REQUIRE(mode >= 0 && mode <= 2, "sq_qmeans_assign: mode must be 0 (exact), 1 (delta window) or 2 (ipe)");
+    SQ_REQUIRE(mode == MODE_EXACT || delta > 0.0, "sq_qmeans_assign: noisy modes need delta > 0");
+    size_t need = assign_ws_layout(n, k, nullptr, nullptr);
+    if (!ws || ws_bytes < need) { set_error("sq_qmeans_assign: workspace needs %zu bytes, got %zu", need, ws_bytes); return SQ_ERR_WORKSPACE; }
+    AssignWs w;
+    assign_ws_layout(n, k, &w, (char*)ws);
+
+    SQ_CUDA(cudaMemsetAsync(w.flag_count, 0, sizeof(int), stream));
+    int rc = sq_row_sqnorms(C, k, d, w.cnorm, stream);
+    if (rc) return rc;
+
+    AssignArgs a;
+    a.X = X; a.xnorm = xnorm; a.C = C; a.cnorm = w.cnorm; a.rowmin_in = nullptr;
+    a.labels = labels; a.mindist = mindist ? mindist : w.mindist; a.rowmin_out = nullptr;
+    a.flag_count = w.flag_count; a.flag_rows = w.flag_rows;
+    a.n = n; a.d = d; a.k = k; a.mode = mode; a.delta = delta;
+    a.tie_tol = 16.0 * (d + 8) * 1.1102230246251565e-16;
+    a.seed = seed; a.offset = offset;
+    int bn = 0;
+    if (mode == MODE_WINDOW && k > 256) {
+        // the window needs the row minimum over all k before candidates can be drawn
+        AssignArgs pre = a;
+        pre.mode = MODE_EXACT; pre.rowmin_out = w.rowmin; pre.tie_tol = -1.0;
+        rc = dispatch_assign(pre, stream, &bn);
+        if (rc) return rc;
+        a.rowmin_in = w.rowmin;
+    }
+    rc = dispatch_assign(a, stream, &bn);
+    if (rc) return rc;
+    if (mode == MODE_EXACT) {
+        int fb = device_sm_count() * 4;
+        qmeans_fixup_kernel<<<fb, 256, 0, stream>>>(a);
+        SQ_LAUNCH_CHECK("qmeans_fixup_kernel");
+    }
+    rc = sq_sum_f64(a.mindist, n, inertia, w.partial, SUM_BLOCKS * sizeof(double), stream);
+    if (rc) return rc;
+    if (n_fixed) SQ_CUDA(cudaMemcpyAsync(n_fixed, w.flag_count, sizeof(int), cudaMemcpyDeviceToDevice, stream));
+    return SQ_OK;
+}
