@@ -550,3 +550,19 @@ def ipe(x, y, epsilon, Q=1, gamma=0.1):
         a = 0
     a_tilde = amplitude_estimation(a=a, gamma=gamma, epsilon=epsilon_a)
     return S * (1 - 2 * a_tilde) / 2
+
+
+def _sync_state():
+    """Give every rank of the process group rank 0's seed and stream offset, so
+    that replicated draws (centroid tomography, singular-value estimation) agree."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1):
+        return
+    dev = dv.require_cuda() if dist.get_backend() == "nccl" else torch.device("cpu")
+    s = _state["seed"]
+    t = torch.tensor([s & 0xFFFFFFFF, s >> 32, _state["offset"] & 0xFFFFFFFF, _state["offset"] >> 32],
+                     dtype=torch.int64, device=dev)
+    dist.broadcast(t, src=0)
+    v = [int(x) for x in t.cpu().tolist()]
+    _state["seed"] = v[0] | (v[1] << 32)
+    _state["offset"] = v[2] | (v[3] << 32)

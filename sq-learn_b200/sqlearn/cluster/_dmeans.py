@@ -1,0 +1,558 @@
+"""q-means (delta-means) clustering on a B200.
+
+Host-side mirror of the quantum part of the reference's
+``sklearn/cluster/_dmeans.py``: ``qMeans_`` with its constructor arguments,
+``fit / predict / transform / fit_predict / fit_transform / score`` and the
+helpers ``_kmeans_single_lloyd``, ``_labels_inertia``, ``labels_estimation``,
+``_centers_update``, ``select_labels``, ``_tolerance`` keep their names and
+meaning.  The arithmetic runs in CUDA kernels (see ``_engine.py`` and
+``include/sqb200.h``); arrays stay on the GPU between the E-step, the M-step
+and the centroid tomography.
+
+Deliberate differences from the reference, all listed in DESIGN.md:
+  * helpers take the device engine instead of host arrays, and return the
+    per-row minimum distance instead of the n x k distance matrix (which is
+    never materialised);
+  * the unconditional ``print(center_shift_total, tol)`` (_dmeans.py:652) is
+    dropped;
+  * an empty cluster keeps its previous centre and warns (the reference
+    indexes an uninitialised array, _dmeans.py:816-823);
+  * ``predict`` / ``score`` implement their evident intent (the reference
+    calls ``_labels_inertia`` with the wrong arity, _dmeans.py:1387, :1401);
+  * ``sample_weight`` is accepted and ignored, as in the reference (:812).
+"""
+import numbers
+import random
+import warnings
+
+import numpy as np
+import torch
+
+from .. import _device as dv
+from ..QuantumUtility import Utility as qu
+from ._engine import MODE_EXACT, MODE_IPE, MODE_WINDOW, QMeansEngine
+
+# the reference seeds Python's global generator when the module is imported (_dmeans.py:22)
+random.seed(a=1234)
+
+
+class ConvergenceWarning(UserWarning):
+    """Same role as sklearn.exceptions.ConvergenceWarning."""
+
+
+def check_random_state(seed):
+    """np.random.RandomState from None / int / instance (sklearn.utils.check_random_state)."""
+    if seed is None or seed is np.random:
+        return np.random.mtrand._rand
+    if isinstance(seed, numbers.Integral):
+        return np.random.RandomState(seed)
+    if isinstance(seed, np.random.RandomState):
+        return seed
+    raise ValueError('%r cannot be used to seed a numpy.random.RandomState instance' % seed)
+
+
+def select_labels(labels):
+    """Uniform choice among candidate centroid indices (reference: _dmeans.py:2252-2257).
+    On the device the same choice is made inside K2; this host version serves callers
+    that hold a candidate list."""
+    if len(labels) == 1:
+        return labels[0]
+    return random.choice(labels)
+
+
+def _tolerance(engine, tol):
+    """tol scaled by the mean per-feature variance (reference: _dmeans.py:253-261).
+    Uses the centred shard on the device: variance is shift invariant."""
+    if tol == 0:
+        return 0
+    # sum of squares per column through the mu-norm column pass (exponent 2)
+    X = engine.X
+    _, d = X.shape
+    from .. import _cabi
+    rowmax, colsum, fr = dv.empty((1,)), dv.empty((1, d)), dv.empty((1,))
+    nb = _cabi.lib.sq_mu_norms_workspace_bytes(engine.n, d, 1)
+    ws = dv.workspace(nb)
+    e2 = np.asarray([2.0])
+    _cabi.check(_cabi.lib.sq_mu_norms(dv.ptr(X), engine.n, d, e2.ctypes.data, e2.ctypes.data, 1, dv.ptr(rowmax),
+                                      dv.ptr(colsum), dv.ptr(fr), dv.ptr(ws), nb, dv.stream_ptr()), "sq_mu_norms")
+    csum = engine.col_sums()
+    cnt = torch.tensor([float(engine.n)], dtype=torch.float64, device=X.device)
+    dv.all_reduce_sum(colsum)
+    dv.all_reduce_sum(csum)
+    dv.all_reduce_sum(cnt)
+    n_glob = float(cnt.item())
+    var = colsum[0].cpu().numpy() / n_glob - (csum.cpu().numpy() / n_glob) ** 2
+    return float(np.mean(var) * tol)
+
+
+def _kmeans_plusplus(X, n_clusters, x_squared_norms, random_state, n_local_trials=None):
+    """k-means++ seeding on the host (reference: _dmeans.py:153-247, stock
+    scikit-learn): first centre uniform, then each next centre is the best of
+    2+log(k) candidates drawn with probability proportional to the squared
+    distance to the closest centre chosen so far.  Consumes ``random_state``
+    in the same order as the reference (randint, then random_sample per step)."""
+    n_samples, n_features = X.shape
+    centers = np.empty((n_clusters, n_features), dtype=X.dtype)
+    if n_local_trials is None:
+        n_local_trials = 2 + int(np.log(n_clusters))
+    center_id = random_state.randint(n_samples)
+    indices = np.full(n_clusters, -1, dtype=int)
+    centers[0] = X[center_id]
+    indices[0] = center_id
+
+    def sqdist(rows):
+        d2 = x_squared_norms[rows][:, None] - 2.0 * (X[rows] @ X.T) + x_squared_norms[None, :]
+        np.maximum(d2, 0, out=d2)
+        return d2
+
+    closest = sqdist(np.asarray([center_id]))[0]
+    current_pot = closest.sum()
+    for c in range(1, n_clusters):
+        rand_vals = random_state.random_sample(n_local_trials) * current_pot
+        cand = np.searchsorted(np.cumsum(closest, dtype=np.float64), rand_vals)
+        np.clip(cand, None, closest.size - 1, out=cand)
+        d2 = sqdist(cand)
+        np.minimum(closest, d2, out=d2)
+        pots = d2.sum(axis=1)
+        best = np.argmin(pots)
+        current_pot = pots[best]
+        closest = d2[best]
+        centers[c] = X[cand[best]]
+        indices[c] = cand[best]
+    return centers, indices
+
+
+def _mode_of(delta, true_distance_estimate):
+    if not delta or delta <= 0:
+        return MODE_EXACT
+    return MODE_IPE if true_distance_estimate else MODE_WINDOW
+
+
+def labels_estimation(engine, centers, delta, pool, true_distance_estimate):
+    """E-step on the device (reference: _dmeans.py:732-777).
+
+    Returns (labels int32 device tensor, per-row min distance device tensor,
+    inertia device scalar).  ``pool`` is accepted and unused: the IPE draws of
+    every (sample, centroid) pair run inside one kernel."""
+    mode = _mode_of(delta, true_distance_estimate)
+    row0, total = engine.row0, engine.n_total
+    seed, off = qu._take_streams(total)
+    engine.assign(centers, mode, delta if delta else 0.0, seed, off + row0)
+    return engine.labels, engine.mindist, engine.inertia
+
+
+def _labels_inertia(engine, centers, distances=None, delta=0, pool=None, true_distance_estimate=True,
+                    n_threads=None):
+    """E step of the q-means EM algorithm (reference: _dmeans.py:674-724)."""
+    return labels_estimation(engine, centers, delta, pool, true_distance_estimate)
+
+
+def _centers_update(engine, labels, error, intermediate_error, true_tomography, stop_when_reached_accuracy,
+                    centers_old=None, centers_out=None):
+    """M step (reference: _dmeans.py:780-830): per-cluster means, then optional
+    tomography of the centres with error ``error`` (= delta/2)."""
+    engine.accumulate()
+    engine.all_reduce()
+    if centers_out is None:
+        centers_out = dv.empty((engine.k, engine.d))
+    engine.finalize(centers_old, centers_out)
+    if intermediate_error:
+        centers_out = _centroid_tomography(engine, centers_out, error, true_tomography, stop_when_reached_accuracy)
+    return centers_out
+
+
+def _centroid_tomography(engine, centers, error, true_tomography, stop_when_reached_accuracy):
+    """tomography(centers, delta/2) (reference: _dmeans.py:825-828).  With several
+    ranks each one estimates a contiguous block of centroids and the blocks are
+    all-gathered; the Philox streams are keyed by centroid id, so the result
+    is the same as on one GPU."""
+    k, world, rank = engine.k, engine.world, engine.rank
+    if world == 1 or not true_tomography or k % world != 0:
+        # every rank draws from the same (synchronised) stream range, so all get the same centres
+        return qu.tomography(centers, error, true_tomography=true_tomography,
+                             stop_when_reached_accuracy=stop_when_reached_accuracy)
+    import torch.distributed as dist
+    per = k // world
+    seed, off = qu._take_streams(k)
+    mine = centers[rank * per:(rank + 1) * per].contiguous()
+    est = qu._tomography_device(mine, error, None, 'L2', stop_when_reached_accuracy, True, 0,
+                                vec_offset=off + rank * per, seed_=seed)[0]
+    out = torch.empty_like(centers)
+    dist.all_gather_into_tensor(out, est)
+    return out
+
+
+def _kmeans_single_lloyd(engine, sample_weight, centers_init, intermediate_err, true_tomography,
+                         stop_when_reached_accuracy, pool, true_distance_estimate, max_iter=300, verbose=False,
+                         tol=1e-4, delta=None):
+    """One run of q-means Lloyd iterations (reference: _dmeans.py:534-671).
+
+    ``centers_init`` is a device tensor [k, d].  Returns (labels, inertia,
+    centers, n_iter) with labels / centers still on the device.  Per iteration
+    the host reads back two doubles (inertia, centre shift) to take the same
+    decisions as the reference: best-by-inertia tracking (:646-649) and the
+    tolerance break (:651-658)."""
+    if delta == None:  # noqa: E711
+        delta = 0
+    k, d = engine.k, engine.d
+    centers = centers_init.clone()
+    centers_old = torch.empty_like(centers)
+    centers_new = torch.empty_like(centers)
+    best_labels = torch.empty_like(engine.labels)
+    best_centers = torch.empty_like(centers)
+    best_inertia = None
+    host = torch.empty((2,), dtype=torch.float64).pin_memory()
+    stats = {"fixed_rows": 0, "empty_clusters": 0}
+    center_shift_total = 0.0
+    i = 0
+    for i in range(max_iter):
+        centers_old.copy_(centers)
+        labels, _, inertia_dev = _labels_inertia(engine, centers, delta=delta, pool=pool,
+                                                 true_distance_estimate=true_distance_estimate)
+        error = delta / 2
+        out = _centers_update(engine, labels, error, intermediate_error=intermediate_err,
+                              true_tomography=true_tomography,
+                              stop_when_reached_accuracy=stop_when_reached_accuracy,
+                              centers_old=centers_old, centers_out=centers_new)
+        centers.copy_(out)
+        shift_dev = engine.shift(centers_old, centers)
+        host[0:1].copy_(engine.inertia, non_blocking=True)   # already summed over ranks by the M-step
+        host[1:2].copy_(shift_dev, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        inertia, center_shift_total = float(host[0]), float(host[1])
+        if verbose:
+            print("Iteration %2d, inertia %.3f" % (i, inertia))
+        if best_inertia is None or inertia < best_inertia:
+            best_labels.copy_(labels)
+            best_centers.copy_(centers)
+            best_inertia = inertia
+        if center_shift_total <= tol:
+            if verbose:
+                print("Converged at iteration %d: center shift %e within tolerance %e"
+                      % (i, center_shift_total, tol))
+            break
+    if center_shift_total > 0:
+        # rerun the E-step so that the labels match the returned centres (:660-666)
+        labels, _, inertia_dev = _labels_inertia(engine, best_centers, delta=delta, pool=pool,
+                                                 true_distance_estimate=true_distance_estimate)
+        red = inertia_dev.clone()
+        dv.all_reduce_sum(red)
+        best_inertia = float(red.item())
+        best_labels.copy_(labels)
+    if verbose and i + 1 == max_iter:
+        print("Reached {} iterations of q-means".format(i + 1))
+    empty = int((engine.counts == 0).sum().item())
+    if empty:
+        warnings.warn("%d cluster(s) received no sample; their previous centre was kept" % empty,
+                      ConvergenceWarning)
+    return best_labels, best_inertia, best_centers, i + 1
+
+
+from .._base import BaseEstimator, check_is_fitted  # noqa: E402
+
+
+def _validate_X(X, copy=True):
+    """C-ordered float64 2-D array (reference: _validate_data, _dmeans.py:1237-1240;
+    float32 input is accepted and promoted: all kernels compute in fp64)."""
+    if hasattr(X, "toarray") and not isinstance(X, np.ndarray):
+        raise TypeError("sparse input has no quantum path (the reference falls back to classical k-means, "
+                        "_dmeans.py:631-635); densify it first")
+    X = np.array(X, dtype=np.float64, order='C', copy=copy) if copy else np.ascontiguousarray(X, dtype=np.float64)
+    if X.ndim != 2:
+        raise ValueError("Expected 2D array, got array with shape %r" % (X.shape,))
+    if not np.isfinite(X).all():
+        raise ValueError("Input contains NaN, infinity or a value too large for dtype('float64').")
+    return X
+
+
+class qMeans_(BaseEstimator):
+    """q-means clustering (reference: sklearn/cluster/_dmeans.py:833-1469).
+
+    Same constructor as the reference (:1016-1021).  ``delta`` is the error of
+    the distance estimates and (halved) of the centroid tomography;
+    ``true_distance_estimate`` selects inner-product estimation (True) or the
+    delta-window rule (False); ``intermediate_error`` adds tomography noise to
+    the centres after every M-step.  Only ``algorithm='full'`` reaches the
+    quantum path, exactly as in the reference (:1274-1278).
+
+    Multi-GPU: under ``torch.distributed`` every rank passes its own rows;
+    centres, inertia and ``n_iter_`` are global, ``labels_`` are this rank's.
+    """
+
+    def __init__(self, n_clusters=8, *, init='k-means++', n_init=10, max_iter=300, tol=1e-4,
+                 precompute_distances='deprecated', verbose=0, random_state=None, copy_x=True,
+                 n_jobs='deprecated', algorithm='auto', delta=None, intermediate_error=False,
+                 true_tomography=True, stop_when_reached_accuracy=True, multiprocess=False,
+                 true_distance_estimate=True):
+        self.n_clusters = n_clusters
+        self.init = init
+        self.max_iter = max_iter
+        self.tol = tol
+        self.precompute_distances = precompute_distances
+        self.n_init = n_init
+        self.verbose = verbose
+        self.random_state = random_state
+        self.copy_x = copy_x
+        self.n_jobs = n_jobs
+        self.algorithm = algorithm
+        self.delta = delta
+        self.intermediate_error = intermediate_error
+        self.true_tomography = true_tomography
+        self.stop_when_reached_accuracy = stop_when_reached_accuracy
+        self.multiprocess = multiprocess
+        self.true_distance_estimate = true_distance_estimate
+
+    # ---- parameter checks (reference: _dmeans.py:1041-1102) -----------------
+    def _check_params(self, X):
+        if self.precompute_distances != 'deprecated':
+            warnings.warn("'precompute_distances' was deprecated in version 0.23 and will be removed in 1.0 "
+                          "(renaming of 0.25). It has no effect", FutureWarning)
+        if self.n_jobs != 'deprecated':
+            warnings.warn("'n_jobs' was deprecated in version 0.23 and will be removed in 1.0 "
+                          "(renaming of 0.25).", FutureWarning)
+        if self.n_init <= 0:
+            raise ValueError(f"n_init should be > 0, got {self.n_init} instead.")
+        self._n_init = self.n_init
+        if self.max_iter <= 0:
+            raise ValueError(f"max_iter should be > 0, got {self.max_iter} instead.")
+        if X.shape[0] < self.n_clusters:
+            raise ValueError(f"n_samples={X.shape[0]} should be >= n_clusters={self.n_clusters}.")
+        if self.algorithm not in ("auto", "full", "elkan"):
+            raise ValueError(f"Algorithm must be 'auto', 'full' or 'elkan', got {self.algorithm} instead.")
+        self._algorithm = self.algorithm
+        if self._algorithm == "auto":
+            self._algorithm = "full" if self.n_clusters == 1 else "elkan"
+        if self._algorithm == "elkan" and self.n_clusters == 1:
+            warnings.warn("algorithm='elkan' doesn't make sense for a single cluster. Using 'full' instead.",
+                          RuntimeWarning)
+            self._algorithm = "full"
+        if not (hasattr(self.init, '__array__') or callable(self.init)
+                or (isinstance(self.init, str) and self.init in ["k-means++", "random"])):
+            raise ValueError(f"init should be either 'k-means++', 'random', a ndarray or a callable, "
+                             f"got '{self.init}' instead.")
+        if hasattr(self.init, '__array__') and self._n_init != 1:
+            warnings.warn(f"Explicit initial center position passed: performing only one init in "
+                          f"{self.__class__.__name__} instead of n_init={self._n_init}.", RuntimeWarning,
+                          stacklevel=2)
+            self._n_init = 1
+
+    def _validate_center_shape(self, X, centers):
+        if centers.shape[0] != self.n_clusters:
+            raise ValueError(f"The shape of the initial centers {centers.shape} does not match the number of "
+                             f"clusters {self.n_clusters}.")
+        if centers.shape[1] != X.shape[1]:
+            raise ValueError(f"The shape of the initial centers {centers.shape} does not match the number of "
+                             f"features of the data {X.shape[1]}.")
+
+    def _init_centroids(self, X, x_squared_norms, init, random_state, init_size=None):
+        """Initial centres on the host (reference: _dmeans.py:1153-1209)."""
+        n_samples = X.shape[0]
+        n_clusters = self.n_clusters
+        if init_size is not None and init_size < n_samples:
+            idx = random_state.randint(0, n_samples, init_size)
+            X, x_squared_norms, n_samples = X[idx], x_squared_norms[idx], len(idx)
+        if isinstance(init, str) and init == 'k-means++':
+            centers, _ = _kmeans_plusplus(X, n_clusters, random_state=random_state,
+                                          x_squared_norms=x_squared_norms)
+        elif isinstance(init, str) and init == 'random':
+            seeds = random_state.permutation(n_samples)[:n_clusters]
+            centers = X[seeds]
+        elif hasattr(init, '__array__'):
+            centers = init
+        elif callable(init):
+            centers = np.ascontiguousarray(init(X, n_clusters, random_state=random_state), dtype=X.dtype)
+            self._validate_center_shape(X, centers)
+        return np.ascontiguousarray(centers, dtype=np.float64)
+
+    # ---- fit (reference: _dmeans.py:1211-1325) --------------------------------
+    def _preamble(self, engine):
+        """eta, muA and condition_number of the uncentred data (:1242-1245).  The
+        reference takes a full LAPACK SVD for min(S); here min(S) = sqrt(lambda_min(X^T X))
+        from the tensor-core Gram kernel and a d x d cuSOLVER eigensolve."""
+        from .. import _cabi
+        n, d = engine.n, engine.d
+        grid = [i for i in np.arange(0, 0.1, 0.05)] + [0.1]            # best_mu(X, 0, 0.1)
+        er = np.asarray([2 * p for p in grid] + [2.0])
+        ec = np.asarray([2 * (1 - p) for p in grid] + [2.0])
+        npk = len(er)
+        rowmax, colsum, fr = dv.empty((npk,)), dv.empty((npk, d)), dv.empty((1,))
+        nb = _cabi.lib.sq_mu_norms_workspace_bytes(n, d, npk)
+        ws = dv.workspace(nb)
+        _cabi.check(_cabi.lib.sq_mu_norms(dv.ptr(engine.X), n, d, er.ctypes.data, ec.ctypes.data, npk,
+                                          dv.ptr(rowmax), dv.ptr(colsum), dv.ptr(fr), dv.ptr(ws), nb,
+                                          dv.stream_ptr()), "sq_mu_norms")
+        G = dv.empty((d, d))
+        nb = _cabi.lib.sq_gram_workspace_bytes(n, d)
+        ws = dv.workspace(nb)
+        _cabi.check(_cabi.lib.sq_gram_centered(dv.ptr(engine.X), n, d, None, dv.ptr(G), dv.ptr(ws), nb,
+                                               dv.stream_ptr()), "sq_gram_centered")
+        if engine.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(rowmax, op=dist.ReduceOp.MAX)
+            dv.all_reduce_sum(colsum)
+            dv.all_reduce_sum(fr)
+            dv.all_reduce_sum(G)
+        s1 = rowmax.cpu().numpy()
+        s2 = colsum.max(dim=1).values.cpu().numpy()
+        self.eta = float(s1[-1])                                        # max_i ||x_i||^2
+        mu = list(np.sqrt(s1[:-1] * s2[:-1]))
+        self.muA = min(min(mu), float(np.sqrt(fr.item())))
+        lam = torch.linalg.eigvalsh(G)                                  # cuSOLVER, d x d
+        r = min(engine.n_total, d)
+        smin = float(torch.sqrt(torch.clamp(lam[d - r], min=0.0)).item())
+        self.condition_number = 1 / smin if smin > 0 else float('inf')
+
+    def fit(self, X, y=None, sample_weight=None):
+        """Compute q-means clustering (reference: _dmeans.py:1211-1325)."""
+        X = _validate_X(X, copy=self.copy_x)
+        dv.require_cuda()
+        rank, world = dv.dist_info()
+        if world > 1:
+            qu._sync_state()
+        Xd = dv.to_device(X, pin=True)
+        if Xd.data_ptr() == 0 or X.shape[0] == 0:
+            raise ValueError("Found array with 0 sample(s)")
+        engine = QMeansEngine(Xd, self.n_clusters)
+        self._engine_launches = 0
+        self._preamble(engine)
+
+        if self.delta == 0:
+            warnings.warn("Attention! You are running classic version of kmeans!")
+            if self.intermediate_error:
+                raise ValueError("intermediate_error value cannot be True if delta is zero.")
+        self._check_params(X)
+        random_state = check_random_state(self.random_state)
+
+        init = self.init
+        if hasattr(init, '__array__'):
+            init = np.array(init, dtype=np.float64, order='C', copy=True)
+            self._validate_center_shape(X, init)
+
+        # subtract the mean of X for more accurate distance computations (:1262-1269)
+        csum = engine.col_sums()
+        dv.all_reduce_sum(csum)
+        X_mean_dev = csum / float(engine.n_total)
+        engine.subtract_rowvec(X_mean_dev)
+        engine.refresh_norms()
+        X_mean = X_mean_dev.cpu().numpy()
+        if hasattr(init, '__array__'):
+            init -= X_mean
+        self._tol = _tolerance(engine, self.tol)
+
+        if self._algorithm != "full":
+            # the reference dispatches to _kmeans_single_elkan, which rejects the quantum keywords (:1294-1299)
+            raise TypeError("_kmeans_single_elkan() got an unexpected keyword argument 'delta' "
+                            "(use algorithm='full' for q-means, as in the reference)")
+
+        need_host = not hasattr(init, '__array__')
+        if need_host:
+            X -= X_mean                      # our private copy when copy_x=True, as in the reference
+            x_sq_host = np.einsum('ij,ij->i', X, X)
+        best_inertia = None
+        for _ in range(self._n_init):
+            centers_init = self._init_centroids(X, x_sq_host if need_host else None, init, random_state)
+            c_dev = dv.to_device(centers_init)
+            if world > 1:
+                import torch.distributed as dist
+                dist.broadcast(c_dev, src=0)
+            if self.verbose:
+                print("Initialization complete")
+            labels, inertia, centers, n_iter_ = _kmeans_single_lloyd(
+                engine, sample_weight, c_dev, max_iter=self.max_iter, verbose=self.verbose, tol=self._tol,
+                delta=self.delta, intermediate_err=self.intermediate_error, true_tomography=self.true_tomography,
+                stop_when_reached_accuracy=self.stop_when_reached_accuracy, pool=None,
+                true_distance_estimate=self.true_distance_estimate)
+            if best_inertia is None or inertia < best_inertia:
+                best_labels = labels.clone()
+                best_centers = centers.clone()
+                best_inertia = inertia
+                best_n_iter = n_iter_
+        if need_host and not self.copy_x:
+            X += X_mean
+        best_centers = best_centers + X_mean_dev
+        self._labels = best_labels.cpu().numpy()
+        distinct = len(np.unique(self._labels))
+        if world == 1 and distinct < self.n_clusters:
+            warnings.warn("Number of distinct clusters ({}) found smaller than n_clusters ({}). Possibly due to "
+                          "duplicate points in X.".format(distinct, self.n_clusters), ConvergenceWarning,
+                          stacklevel=2)
+        self.cluster_centers_ = best_centers.cpu().numpy()
+        self.inertia_ = best_inertia
+        self.n_iter_ = best_n_iter
+        self.n_features_in_ = X.shape[1]
+        self._engine_launches = engine.launches
+        return self
+
+    @property
+    def labels_(self):
+        """Labels of the training rows as a list of int, as in the reference (:628, :1322)."""
+        check_is_fitted(self, "_labels")
+        return self._labels.tolist()
+
+    def fit_predict(self, X, y=None, sample_weight=None):
+        warnings.warn('Attention! This computational path is purely classic.')
+        return self.fit(X, sample_weight=sample_weight).labels_
+
+    def fit_transform(self, X, y=None, sample_weight=None):
+        warnings.warn("Attention! This computational part is purely classical.")
+        return self.fit(X, sample_weight=sample_weight)._transform(_validate_X(X))
+
+    def transform(self, X):
+        warnings.warn("Attention! This computational part is purely classical.")
+        check_is_fitted(self, "cluster_centers_")
+        return self._transform(self._check_test_data(X))
+
+    def _check_test_data(self, X):
+        X = _validate_X(X, copy=False)
+        if X.shape[1] != self.n_features_in_:
+            raise ValueError("X has %d features, but %s is expecting %d features as input."
+                             % (X.shape[1], type(self).__name__, self.n_features_in_))
+        return X
+
+    def _transform(self, X):
+        """Distances to the centres, n x k (reference: euclidean_distances, :1349-1351).
+        Classical and off the hot path: a library call."""
+        Xd = dv.to_device(X)
+        C = dv.to_device(self.cluster_centers_)
+        return torch.cdist(Xd, C, compute_mode='donot_use_mm_for_euclid_dist').cpu().numpy()
+
+    def _predict_engine(self, X, delta):
+        Xd = dv.to_device(self._check_test_data(X), pin=True)
+        engine = QMeansEngine(Xd, self.n_clusters)
+        C = dv.to_device(self.cluster_centers_)
+        labels, mind, inertia = _labels_inertia(engine, C, delta=delta, pool=None,
+                                                true_distance_estimate=self.true_distance_estimate)
+        return labels, inertia
+
+    def predict(self, X, sample_weight=None, delta=None):
+        """Closest (or delta-noisy closest) centre of every row of X, list of int
+        (intent of the reference's predict, :1353-1391)."""
+        check_is_fitted(self, "cluster_centers_")
+        if delta == None:  # noqa: E711
+            delta = 0
+        labels, _ = self._predict_engine(X, delta)
+        return [int(lb) for lb in labels.cpu().numpy()]
+
+    def score(self, X, y=None, sample_weight=None):
+        """Opposite of the k-means objective on X (intent of :1393-1402)."""
+        check_is_fitted(self, "cluster_centers_")
+        _, inertia = self._predict_engine(X, 0)
+        red = inertia.clone()
+        dv.all_reduce_sum(red)
+        return -float(red.item())
+
+    def runtime_comparison(self, n_samples, n_features, saveas, well_clusterable=False, plot=False):
+        """Classical vs quantum cost model (reference: _dmeans.py:1412-1469).  The MATLAB
+        plot of the reference is left out (no MATLAB engine); the two cost grids are returned."""
+        if plot:
+            warnings.warn("plot=True needs the MATLAB engine the reference uses; ignored")
+        n, m = np.meshgrid(np.linspace(0, n_samples, dtype=np.int64, num=100),
+                           np.linspace(0, n_features, dtype=np.int64, num=100))
+        c_runtime = n * m * self.n_clusters * self.n_init
+        k, eta, kappa, mu, dl = self.n_clusters, self.eta, self.condition_number, self.muA, self.delta
+        if not well_clusterable:
+            q_runtime = (k * m * eta * kappa * (mu + k * eta / dl) / (dl ** 2)) + \
+                        ((k ** 2) * (eta ** 1.5) * kappa * mu) / (dl ** 2)
+        else:
+            q_runtime = ((k ** 2) * m * (eta ** 2.5) / (dl ** 3)) + (k ** 2.5) * (eta ** 2) / (dl ** 3)
+        return q_runtime, c_runtime

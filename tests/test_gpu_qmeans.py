@@ -1,0 +1,214 @@
+"""Parity of the q-means kernels (K2 E-step, K3 M-step, Lloyd loop) with the
+oracle and with fixtures produced by the reference's source.  Noiseless:
+labels bit-exact, distances / centres within 1e-10 relative (north_star).
+Noisy: same law (chi-square / KS at fixed seeds)."""
+import warnings
+
+import numpy as np
+import pytest
+from scipy import stats
+
+pytestmark = pytest.mark.gpu
+P_MIN = 1e-3
+
+
+@pytest.mark.parametrize("case", ["a", "b", "c"])
+def test_exact_assign_matches_reference_first_estep(cuda, golden_qmeans, case):
+    import gpu_util as G
+    from oracle import qmeans as oq
+    X, C0 = golden_qmeans[f"{case}_X"], golden_qmeans[f"{case}_C0"]
+    labels, mind, inertia, _ = G.assign(X, C0, mode=0)
+    assert np.array_equal(labels, golden_qmeans[f"{case}_labels_first"])
+    D = oq.cdist_sq(X, C0)
+    np.testing.assert_allclose(mind, D.min(axis=1), rtol=1e-10, atol=1e-12)
+    assert inertia == pytest.approx(float(golden_qmeans[f"{case}_inertia_first"]), rel=1e-10)
+
+
+@pytest.mark.parametrize("n,d,k", [(1, 1, 1), (5, 2, 1), (37, 3, 2), (1000, 7, 10), (777, 16, 16), (513, 33, 17),
+                                   (2049, 64, 33), (1500, 100, 64), (900, 130, 100), (1300, 128, 129),
+                                   (2000, 128, 256), (640, 61, 200), (1111, 48, 300), (700, 20, 600),
+                                   (70000, 32, 10)])
+def test_exact_assign_shapes_bit_exact_labels(cuda, n, d, k):
+    import gpu_util as G
+    from oracle import qmeans as oq
+    rs = np.random.RandomState(n + d + k)
+    C = rs.randn(k, d) * 2
+    X = C[rs.randint(0, k, n)] + rs.randn(n, d)
+    labels, mind, inertia, _ = G.assign(X, C, mode=0)
+    D = oq.cdist_sq(X, C)
+    assert np.array_equal(labels, D.argmin(axis=1))
+    np.testing.assert_allclose(mind, D.min(axis=1), rtol=1e-10, atol=1e-11)
+    assert inertia == pytest.approx(D.min(axis=1).sum(), rel=1e-10)
+
+
+def test_exact_assign_near_ties_use_reference_arithmetic(cuda):
+    """rows equidistant (up to an ulp) from two centres must follow cdist()**2's rounding"""
+    import gpu_util as G
+    from oracle import qmeans as oq
+    rs = np.random.RandomState(0)
+    d, k = 24, 9
+    C = rs.randn(k, d)
+    mids = []
+    for _ in range(400):
+        i, j = rs.choice(k, 2, replace=False)
+        m = 0.5 * (C[i] + C[j]) + rs.randn(d) * 1e-17
+        mids.append(m * (1 + rs.randint(-2, 3) * 2.0 ** -52))
+    X = np.vstack([np.asarray(mids), rs.randn(300, d)])
+    labels, mind, _, nfix = G.assign(X, C, mode=0)
+    D = oq.cdist_sq(X, C)
+    mins = D.min(axis=1)
+    ties = (D == mins[:, None]).sum(axis=1)
+    assert nfix >= 1
+    single = ties == 1
+    assert np.array_equal(labels[single], D.argmin(axis=1)[single])
+    # exact ties: any of the minimisers is legal (reference: random.choice, _dmeans.py:772)
+    assert all(D[r, labels[r]] == mins[r] for r in np.where(~single)[0])
+    flagged_exact = np.isclose(mind, mins, rtol=1e-10, atol=1e-13)
+    assert flagged_exact.all()
+
+
+def test_exact_ties_are_broken_uniformly(cuda):
+    import gpu_util as G
+    X = np.zeros((6000, 2))
+    C = np.array([[1.0, 0], [0, 1.0], [-1.0, 0], [2.0, 2.0]])
+    labels, _, _, nfix = G.assign(X, C, mode=0, seed=5)
+    assert nfix == 6000
+    cnt = np.bincount(labels, minlength=4)
+    assert cnt[3] == 0
+    assert stats.chisquare(cnt[:3]).pvalue > P_MIN
+
+
+def test_centroid_accumulate_matches_numpy_and_is_deterministic(cuda):
+    import gpu_util as G
+    rs = np.random.RandomState(1)
+    for n, d, k in [(1, 1, 1), (1000, 5, 3), (5000, 128, 256), (3000, 61, 7), (40000, 64, 10), (2500, 784, 10),
+                    (3000, 1100, 4)]:
+        X = rs.randn(n, d)
+        lab = rs.randint(0, k, n).astype(np.int32)
+        if k > 2:
+            lab[lab == 1] = 0  # an empty cluster
+        sums, counts, bad = G.accumulate(X, lab, k)
+        assert bad == 0
+        want = np.zeros((k, d))
+        np.add.at(want, lab, X)
+        np.testing.assert_allclose(sums, want, rtol=1e-12, atol=1e-11)
+        assert np.array_equal(counts, np.bincount(lab, minlength=k))
+        sums2, _, _ = G.accumulate(X, lab, k)
+        assert np.array_equal(sums, sums2)
+    _, _, bad = G.accumulate(rs.randn(10, 2), np.array([0, 1, 5, 0, 0, 0, 0, 0, 0, 0], dtype=np.int32), 3)
+    assert bad == 1
+
+
+@pytest.mark.parametrize("case", ["a", "b", "c", "toy"])
+def test_lloyd_noiseless_matches_reference(cuda, golden_qmeans, case):
+    import torch
+    from sqlearn.cluster._dmeans import _kmeans_single_lloyd
+    from sqlearn.cluster._engine import QMeansEngine
+    g = golden_qmeans
+    X = torch.as_tensor(g[f"{case}_X"]).cuda().contiguous()
+    C0 = torch.as_tensor(g[f"{case}_C0"]).cuda().contiguous()
+    eng = QMeansEngine(X, C0.shape[0])
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        labels, inertia, centers, n_iter = _kmeans_single_lloyd(
+            eng, None, C0, False, True, True, None, True, max_iter=10 if case == "toy" else 8, tol=0, delta=0)
+    assert n_iter == int(g[f"{case}_n_iter"])
+    assert np.array_equal(labels.cpu().numpy(), g[f"{case}_labels"])
+    np.testing.assert_allclose(centers.cpu().numpy(), g[f"{case}_centers"], rtol=1e-10, atol=1e-12)
+    assert inertia == pytest.approx(float(g[f"{case}_inertia"]), rel=1e-10)
+
+
+def test_window_mode_law_and_support(cuda, golden_stoch):
+    import gpu_util as G
+    from oracle import qmeans as oq
+    Xw, Cw, ref = golden_stoch["window_X"], golden_stoch["window_C"], golden_stoch["window_counts"]
+    labels, mind, inertia, _ = G.assign(np.repeat(Xw, 3000, axis=0), Cw, mode=1, delta=0.5, seed=9)
+    cnt = np.bincount(labels, minlength=4)
+    assert cnt[3] == 0
+    assert stats.chi2_contingency(np.stack([cnt[:3], ref[:3]]))[1] > P_MIN
+    np.testing.assert_allclose(mind, 1.0, rtol=1e-12)           # inertia uses the minimum, not the pick (:751)
+    # random data, several tile shapes: every pick lies inside the window, picks vary with the seed
+    rs = np.random.RandomState(2)
+    for n, d, k, delta in [(3000, 8, 12, 3.0), (2000, 128, 256, 30.0), (1500, 33, 300, 8.0), (800, 16, 100, 4.0)]:
+        X, C = rs.randn(n, d), rs.randn(k, d)
+        D = oq.cdist_sq(X, C)
+        mins = D.min(axis=1)
+        l1, m1, in1, _ = G.assign(X, C, mode=1, delta=delta, seed=1)
+        l2, _, _, _ = G.assign(X, C, mode=1, delta=delta, seed=2)
+        assert (D[np.arange(n), l1] <= mins + delta + 1e-9).all()
+        np.testing.assert_allclose(m1, mins, rtol=1e-10, atol=1e-11)
+        assert in1 == pytest.approx(mins.sum(), rel=1e-10)
+        ncand = (D <= (mins + delta)[:, None]).sum(axis=1)
+        assert (l1 != l2).mean() > 0.2 * (ncand > 1).mean()
+        assert np.array_equal(l1[ncand == 1], D.argmin(axis=1)[ncand == 1])
+        # uniformity over candidates: rank of the pick among the row's candidates
+        two = np.where(ncand == 2)[0]
+        if len(two) > 200:
+            first = np.array([np.where(D[r] <= mins[r] + delta)[0][0] for r in two])
+            hits = (l1[two] == first).sum()
+            assert stats.binomtest(int(hits), len(two), 0.5).pvalue > P_MIN
+
+
+def test_ipe_mode_distance_law(cuda, golden_stoch):
+    """k = 1: the reported min distance IS the IPE-estimated distance |x|^2+|c|^2-2*ipe(x,c)."""
+    import gpu_util as G
+    x, y, ref = golden_stoch["ipe_x"], golden_stoch["ipe_y"], golden_stoch["ipe_draws_e0.25"]
+    n = 4000
+    _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), y[None], mode=2, delta=0.5, seed=3)
+    ref_d = x @ x + y @ y - 2 * ref
+    assert len(np.unique(np.round(mind, 9))) > 3
+    assert stats.ks_2samp(mind, ref_d).pvalue > P_MIN
+
+
+def test_ipe_mode_label_law(cuda, golden_stoch):
+    import gpu_util as G
+    X, C, ref_lab = golden_stoch["ipe_X"], golden_stoch["ipe_C"], golden_stoch["ipe_labels"]
+    reps = 200
+    labels, _, _, _ = G.assign(np.tile(X, (reps, 1)), C, mode=2, delta=0.5, seed=4)
+    mine = labels.reshape(reps, len(X))
+    tab = np.stack([np.bincount(mine.ravel(), minlength=3) / reps * len(ref_lab),
+                    np.bincount(ref_lab.ravel(), minlength=3)])
+    assert stats.chi2_contingency(np.round(tab))[1] > P_MIN
+    # per-row agreement with the reference's empirical label frequencies
+    f_me = np.stack([(mine == j).mean(axis=0) for j in range(3)])
+    f_ref = np.stack([(ref_lab == j).mean(axis=0) for j in range(3)])
+    assert np.abs(f_me - f_ref).max() < 0.35  # 40 reference repetitions only
+
+
+def test_qmeans_fit_end_to_end(cuda, golden_qmeans):
+    from oracle import qmeans as oq
+    from sqlearn import QuantumUtility as Q
+    from sqlearn.cluster import qMeans_
+    g = golden_qmeans
+    X = g["a_X"] + 3.0        # fit centres internally; reference centres are for the centred data
+    C0 = g["a_C0"] + 3.0
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        Q.seed(1)
+        est = qMeans_(n_clusters=5, init=C0, n_init=1, max_iter=8, tol=0, delta=0, algorithm='full').fit(X)
+    assert est.labels_ == [int(v) for v in g["a_labels"]]
+    np.testing.assert_allclose(est.cluster_centers_, g["a_centers"] + 3.0, rtol=1e-9, atol=1e-9)
+    assert est.n_iter_ == int(g["a_n_iter"])
+    assert est.inertia_ == pytest.approx(float(g["a_inertia"]), rel=1e-9)
+    Xc = g["a_X"]
+    assert est.eta == pytest.approx(np.max(np.einsum("ij,ij->i", X, X)), rel=1e-12)
+    assert est.condition_number == pytest.approx(1 / np.linalg.svd(X, compute_uv=False).min(), rel=1e-8)
+    from oracle import quantum_utility as oqu
+    assert est.muA == pytest.approx(oqu.best_mu(X, 0, 0.1)[1], rel=1e-10)
+    assert est.predict(X[:50]) == est.labels_[:50]
+    assert est.score(X) == pytest.approx(-oq.cdist_sq(X, est.cluster_centers_).min(axis=1).sum(), rel=1e-9)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        with pytest.raises(TypeError, match="elkan"):
+            qMeans_(n_clusters=5, delta=0.5).fit(X)
+        with pytest.raises(ValueError, match="intermediate_error"):
+            qMeans_(n_clusters=5, delta=0, intermediate_error=True, algorithm='full').fit(X)
+        # noisy run: every mode runs, centroid tomography returns unit-norm centres (D5)
+        Q.seed(2)
+        e2 = qMeans_(n_clusters=5, init=C0, n_init=1, max_iter=3, tol=0, delta=0.5, algorithm='full',
+                     intermediate_error=True, true_distance_estimate=False).fit(X)
+        norms = np.linalg.norm(e2.cluster_centers_ - X.mean(axis=0), axis=1)
+        np.testing.assert_allclose(norms, 1.0, atol=1e-9)
+        e3 = qMeans_(n_clusters=5, init='k-means++', n_init=2, max_iter=3, delta=0.5, algorithm='full',
+                     random_state=0).fit(X)
+        assert len(e3.labels_) == len(X) and np.isfinite(e3.inertia_)

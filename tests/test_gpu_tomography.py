@@ -1,0 +1,180 @@
+"""K1 (batched tomography) and its binomial sampler against the reference's
+law: fixtures hold samples drawn by the reference's own code; chi-square / KS
+at fixed seeds, plus the properties the algorithm guarantees."""
+import numpy as np
+import pytest
+from scipy import stats
+
+pytestmark = pytest.mark.gpu
+P_MIN = 1e-3
+
+
+@pytest.mark.parametrize("n,p", [(1, 0.3), (7, 0.5), (40, 0.01), (40, 0.2), (200, 0.03), (30, 0.9), (1000, 0.5),
+                                 (1000, 0.999), (12345, 0.0008), (100000, 0.3), (10 ** 7, 1e-6)])
+def test_binomial_sampler_chisquare(cuda, n, p):
+    import gpu_util as G
+    B = 200000
+    out = G.binomial(np.full(B, float(n)), np.full(B, p), np.full(B, 1 - p), seed=n)
+    assert out.min() >= 0 and out.max() <= n and np.all(out == np.floor(out))
+    lo, hi = int(stats.binom.ppf(1e-7, n, p)), int(stats.binom.ppf(1 - 1e-7, n, p))
+    ks = np.arange(lo, hi + 1)
+    pmf = stats.binom.pmf(ks, n, p)
+    obs = np.array([(out == k).sum() for k in ks], dtype=float) if hi - lo < 400 else \
+        np.histogram(out, bins=np.arange(lo - 0.5, hi + 1.5))[0].astype(float)
+    # merge sparse cells
+    order = np.argsort(pmf)
+    exp = pmf * B
+    small = exp < 8
+    o = np.append(obs[~small], obs[small].sum() + (B - obs.sum()))
+    e = np.append(exp[~small], exp[small].sum() + (B - exp.sum()))
+    keep = e > 0
+    assert stats.chisquare(o[keep], e[keep] * o[keep].sum() / e[keep].sum()).pvalue > P_MIN
+
+
+def test_binomial_huge_counts_moments(cuda):
+    import gpu_util as G
+    B = 100000
+    for n, p in [(5e12, 0.37), (3e9, 1e-4), (8e14, 0.5)]:
+        out = G.binomial(np.full(B, n), np.full(B, p), np.full(B, 1 - p), seed=7)
+        z = (out - n * p) / np.sqrt(n * p * (1 - p))
+        assert abs(z.mean()) < 5 / np.sqrt(B)
+        assert abs(z.std() - 1) < 0.02
+        assert stats.kstest(z, "norm").pvalue > P_MIN
+    # degenerate inputs
+    out = G.binomial(np.array([0.0, 5.0, 5.0]), np.array([0.5, 0.0, 1.0]), np.array([0.5, 1.0, 0.0]))
+    assert list(out) == [0.0, 0.0, 5.0]
+
+
+def _default_runs(G, v, delta, B, seed, norm_inf=0):
+    from oracle import quantum_utility as qu
+    N = qu.tomography_N(len(v), delta, "inf" if norm_inf else "L2")
+    sched = qu.schedule(N).astype(float)
+    return G.tomography(np.repeat(v[None], B, axis=0), delta, sched, norm_inf=norm_inf, stop=1, seed=seed)
+
+
+def test_default_mode_matches_reference_law(cuda, golden_stoch):
+    import gpu_util as G
+    v = golden_stoch["tomo_v"]
+    est, n_used, err = _default_runs(G, v, 0.3, 4000, seed=11)
+    assert err.max() <= 0.3
+    np.testing.assert_allclose(err, np.linalg.norm(v[None] - est, axis=1), rtol=1e-12)
+    assert stats.ks_2samp(err, golden_stoch["tomo_default_err"]).pvalue > P_MIN
+    assert stats.ks_2samp(n_used, golden_stoch["tomo_default_N"]).pvalue > P_MIN
+
+
+@pytest.mark.parametrize("norm", ["L2", "inf"])
+def test_single_shot_matches_reference_law(cuda, golden_stoch, norm):
+    import gpu_util as G
+    from oracle import quantum_utility as qu
+    v = golden_stoch["tomo_v"]
+    N = qu.tomography_N(16, 0.3, norm)
+    est, n_used, err = G.tomography(np.repeat(v[None], 4000, axis=0), 0.3, [N], norm_inf=int(norm == "inf"), seed=12)
+    assert (n_used == N).all()
+    want = np.linalg.norm(v[None] - est, ord=2 if norm == "L2" else np.inf, axis=1)
+    np.testing.assert_allclose(err, want, rtol=1e-12)
+    assert stats.ks_2samp(err, golden_stoch[f"tomo_single_{norm}_err"]).pvalue > P_MIN
+    assert stats.ks_2samp(est[:, 0], golden_stoch[f"tomo_single_{norm}_c0"]).pvalue > P_MIN
+    # theorem: ||est - v|| <= delta except with small probability
+    assert (err > 0.3).mean() < 0.01
+
+
+def test_small_N_sign_errors_and_components(cuda, golden_stoch):
+    import gpu_util as G
+    v = golden_stoch["tomo_v"]
+    B = 6000
+    est, _, _ = G.tomography(np.repeat(v[None], B, axis=0), 0.3, [40.0], seed=13)
+    wrong = int(np.sum(np.sign(est) != np.sign(v)[None]))
+    ref_wrong, ref_total = golden_stoch["tomo_N40_signerr"]
+    p = (wrong + ref_wrong) / (B * 16 + ref_total)
+    z = (wrong / (B * 16) - ref_wrong / ref_total) / np.sqrt(p * (1 - p) * (1 / (B * 16) + 1 / ref_total))
+    assert abs(z) < 4
+    assert stats.ks_2samp(est[:, 3], golden_stoch["tomo_N40_c3"]).pvalue > P_MIN
+    # squared estimates are multinomial frequencies: they sum to one, multiples of 1/N
+    np.testing.assert_allclose((est ** 2).sum(axis=1), 1.0, atol=1e-12)
+    np.testing.assert_allclose(est ** 2 * 40, np.round(est ** 2 * 40), atol=1e-9)
+
+
+def test_stage_one_counts_are_multinomial(cuda):
+    """est_i^2 * N ~ Binomial(N, v_i^2) marginally (chi-square on one component)"""
+    import gpu_util as G
+    rs = np.random.RandomState(5)
+    v = rs.uniform(-1, 1, 37)
+    v /= np.linalg.norm(v)
+    N, B = 60, 20000
+    est, _, _ = G.tomography(np.repeat(v[None], B, axis=0), 0.5, [float(N)], seed=14)
+    for comp in (0, 17, 36):
+        c = np.round(est[:, comp] ** 2 * N).astype(int)
+        pmf = stats.binom.pmf(np.arange(N + 1), N, v[comp] ** 2)
+        obs = np.bincount(c, minlength=N + 1).astype(float)
+        small = pmf * B < 8
+        o = np.append(obs[~small], obs[small].sum())
+        e = np.append(pmf[~small], pmf[small].sum()) * B
+        assert stats.chisquare(o, e * o.sum() / e.sum()).pvalue > P_MIN
+
+
+def test_normalisation_rule_and_zero_vector(cuda):
+    import gpu_util as G
+    from oracle import quantum_utility as qu
+    rs = np.random.RandomState(6)
+    v = rs.uniform(-1, 1, 20)
+    v /= np.linalg.norm(v)
+    N = qu.tomography_N(20, 0.1)
+    V = np.stack([5 * v, 1.005 * v, 0.5 * v, np.zeros(20)])
+    est, n_used, err = G.tomography(V, 0.1, [N], seed=15)
+    # rows 0 and 2 were renormalised, row 1 (within rtol 1e-2 of unit norm) kept as is (Utility.py:301-304)
+    np.testing.assert_allclose(np.linalg.norm(est[:3], axis=1), 1.0, atol=1e-12)
+    assert err[0] == pytest.approx(np.linalg.norm(v - est[0]), rel=1e-12)
+    assert err[1] == pytest.approx(np.linalg.norm(1.005 * v - est[1]), rel=1e-12)
+    assert (est[3] == 0).all() and n_used[3] == 0
+    assert (err[:3] < 0.1).all()
+
+
+@pytest.mark.parametrize("d", [1, 2, 3, 61, 128, 784, 1000, 4096])
+def test_dims_and_sharding_invariance(cuda, d):
+    """any d up to the fused limit; a vector's result depends on (seed, global id) only"""
+    import gpu_util as G
+    from oracle import quantum_utility as qu
+    rs = np.random.RandomState(d)
+    B = 6
+    V = rs.uniform(-1, 1, (B, d))
+    V /= np.linalg.norm(V, axis=1, keepdims=True)
+    delta = 0.25
+    N = max(qu.tomography_N(d, delta), 50)
+    sched = qu.schedule(N).astype(float)
+    est, n_used, err = G.tomography(V, delta, sched, stop=1, seed=21, vec_offset=100)
+    assert (err <= delta).all()
+    np.testing.assert_allclose(np.linalg.norm(est, axis=1), 1.0, atol=1e-10)
+    lo = G.tomography(V[:2], delta, sched, stop=1, seed=21, vec_offset=100)
+    hi = G.tomography(V[2:], delta, sched, stop=1, seed=21, vec_offset=102)
+    assert np.array_equal(np.vstack([lo[0], hi[0]]), est)
+    assert np.array_equal(np.concatenate([lo[1], hi[1]]), n_used)
+    other = G.tomography(V, delta, sched, stop=1, seed=22, vec_offset=100)
+    if d > 2:
+        assert not np.array_equal(other[0], est)
+
+
+def test_trace_and_public_api(cuda, golden_stoch):
+    import gpu_util as G
+    from oracle import quantum_utility as qu
+    from sqlearn import QuantumUtility as Q
+    v = golden_stoch["tomo_v"]
+    sched = qu.schedule(qu.tomography_N(16, 0.3)).astype(float)
+    est, n_used, err, tr, att = G.tomography(v, 0.3, sched, stop=1, seed=31, trace=True)
+    a = int(att[0])
+    assert n_used[0] == sched[a - 1]
+    assert np.array_equal(tr[0, a - 1], est[0])
+    errs = np.linalg.norm(v[None] - tr[0, :a], axis=1)
+    assert (errs[:-1] > 0.3).all() and errs[-1] <= 0.3
+    Q.seed(3)
+    res = Q.real_tomography(v, delta=0.3)
+    assert list(res.keys()) == [int(s) for s in sched[:len(res)]]
+    assert np.linalg.norm(v - np.asarray(list(res.values())[-1])) <= 0.3
+    out = Q.tomography(np.stack([v, -v]), 0.3)
+    assert out.shape == (2, 16) and (np.linalg.norm(out - np.stack([v, -v]), axis=1) <= 0.3).all()
+    assert Q.tomography(v, 0) is v
+    with pytest.raises(AssertionError):
+        Q.tomography(v, -1)
+    g = Q.tomography(v, 0.3, true_tomography=False)
+    assert np.abs(g - v).max() <= 0.3 / 4
+    single = Q.real_tomography(v, delta=0.3, incremental_measure=False)
+    assert list(single.keys()) == [qu.tomography_N(16, 0.3)]
