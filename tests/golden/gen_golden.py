@@ -170,5 +170,9 @@ for _ in range(40):
     lab, _, _ = quiet(dm.labels_estimation, Xi, Ci, 0.5, None, True)
     ipe_labels.append(np.asarray(lab))
 st["ipe_X"], st["ipe_C"], st["ipe_labels"] = Xi, Ci, np.asarray(ipe_labels, dtype=np.int32)
+# a pair whose amplitude-estimation phase falls between two grid points: the median of 13 varies
+y2 = y * 0.816
+st["ipe_y2"] = y2
+st["ipe2_draws_e0.25"] = np.sort([quiet(u.ipe, x, y2, 0.25) for _ in range(1500)])
 np.savez_compressed(os.path.join(HERE, "stochastic_reference.npz"), **st)
 print("golden fixtures written to", HERE)

@@ -152,12 +152,21 @@ def test_window_mode_law_and_support(cuda, golden_stoch):
 def test_ipe_mode_distance_law(cuda, golden_stoch):
     """k = 1: the reported min distance IS the IPE-estimated distance |x|^2+|c|^2-2*ipe(x,c)."""
     import gpu_util as G
-    x, y, ref = golden_stoch["ipe_x"], golden_stoch["ipe_y"], golden_stoch["ipe_draws_e0.25"]
     n = 4000
-    _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), y[None], mode=2, delta=0.5, seed=3)
-    ref_d = x @ x + y @ y - 2 * ref
-    assert len(np.unique(np.round(mind, 9))) > 3
-    assert stats.ks_2samp(mind, ref_d).pvalue > P_MIN
+    x = golden_stoch["ipe_x"]
+    for ykey, rkey, spread in (("ipe_y", "ipe_draws_e0.25", False), ("ipe_y2", "ipe2_draws_e0.25", True)):
+        y, ref = golden_stoch[ykey], golden_stoch[rkey]
+        _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), y[None], mode=2, delta=0.5, seed=3)
+        ref_d = x @ x + y @ y - 2 * ref
+        vals = np.unique(np.round(ref_d, 9))
+        if spread:
+            assert len(vals) >= 2 and len(np.unique(np.round(mind, 9))) >= 2
+        # same support, same frequencies
+        tab = np.stack([[np.isclose(mind, v, rtol=1e-9).sum() for v in vals],
+                        [np.isclose(ref_d, v, rtol=1e-9).sum() for v in vals]])
+        assert tab[0].sum() == n
+        if len(vals) > 1:
+            assert stats.chi2_contingency(tab[:, tab.sum(axis=0) > 0])[1] > P_MIN
 
 
 def test_ipe_mode_label_law(cuda, golden_stoch):

@@ -130,6 +130,9 @@ def test_ae_median_and_ipe_law(golden_stoch):
     x, y = golden_stoch["ipe_x"], golden_stoch["ipe_y"]
     dr = [qu.ipe(x, y, 0.25, rng=rng) for _ in range(1500)]
     assert stats.ks_2samp(dr, golden_stoch["ipe_draws_e0.25"]).pvalue > P_MIN
+    dr2 = [qu.ipe(x, golden_stoch["ipe_y2"], 0.25, rng=rng) for _ in range(1500)]
+    assert len(np.unique(np.round(dr2, 9))) >= 2
+    assert stats.ks_2samp(dr2, golden_stoch["ipe2_draws_e0.25"]).pvalue > P_MIN
 
 
 def test_window_and_ipe_labels(golden_stoch):
