@@ -76,6 +76,12 @@ int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, c
                      double delta, unsigned long long seed, unsigned long long offset, int* labels,
                      double* mindist, double* inertia, int* n_fixed, void* ws, size_t ws_bytes, void* stream);
 
+/* Timing hook for the roofline measurement (no reference counterpart): enable = 2 resets
+ * the counters and turns per-launch CUDA-event timing of the main E-step kernel on (each
+ * sq_qmeans_assign then blocks until its kernel ends); 1 = on, 0 = off.  The totals seen
+ * before the call are returned through total_ms / launches (either may be NULL).        */
+int sq_profile_assign(int enable, double* total_ms, long long* launches);
+
 /* row_norms(X, squared=True) (sklearn/utils/extmath.py:49-78) */
 int sq_row_sqnorms(const double* X, long long n, int d, double* out, void* stream);
 /* deterministic sum of n doubles; ws needs 8192 bytes */

@@ -499,6 +499,13 @@ static size_t assign_smem_bytes() {
            (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4) + 64;
 }
 
+// optional timing of the main kernel alone (bench.py's roofline leg): events are
+// recorded on the launching stream around the kernel when profiling is on
+static bool g_prof_on = false;
+static cudaEvent_t g_prof_ev[2] = {nullptr, nullptr};
+static double g_prof_ms = 0.0;
+static long long g_prof_launches = 0;
+
 template <class Cfg>
 static int launch_assign(AssignArgs a, cudaStream_t stream) {
     a.num_tiles = (int)((a.n + Cfg::BM - 1) / Cfg::BM);
@@ -508,6 +515,10 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
     if (grid > a.num_tiles) grid = a.num_tiles;
     size_t smem = assign_smem_bytes<Cfg>();
     bool vec16 = (a.d & 1) == 0 && ((uintptr_t)a.X & 15) == 0 && ((uintptr_t)a.C & 15) == 0;
+    if (g_prof_on) {
+        if (!g_prof_ev[0]) { SQ_CUDA(cudaEventCreate(&g_prof_ev[0])); SQ_CUDA(cudaEventCreate(&g_prof_ev[1])); }
+        SQ_CUDA(cudaEventRecord(g_prof_ev[0], stream));
+    }
 #define SQ_LAUNCH_ASSIGN(V, M)                                                                                       \
     do {                                                                                                            \
         SQ_CUDA(cudaFuncSetAttribute(qmeans_assign_kernel<Cfg, V, M>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
@@ -524,6 +535,15 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
         else SQ_LAUNCH_ASSIGN(false, MODE_IPE);
     }
 #undef SQ_LAUNCH_ASSIGN
+    if (g_prof_on) {
+        // blocking on purpose: profiling mode trades overlap for a per-launch duration
+        SQ_CUDA(cudaEventRecord(g_prof_ev[1], stream));
+        SQ_CUDA(cudaEventSynchronize(g_prof_ev[1]));
+        float ms = 0.f;
+        SQ_CUDA(cudaEventElapsedTime(&ms, g_prof_ev[0], g_prof_ev[1]));
+        g_prof_ms += ms;
+        ++g_prof_launches;
+    }
     SQ_LAUNCH_CHECK("qmeans_assign_kernel");
     return SQ_OK;
 }
@@ -621,5 +641,13 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     rc = sq_sum_f64(a.mindist, n, inertia, w.partial, SUM_BLOCKS * sizeof(double), stream);
     if (rc) return rc;
     if (n_fixed) SQ_CUDA(cudaMemcpyAsync(n_fixed, w.flag_count, sizeof(int), cudaMemcpyDeviceToDevice, stream));
+    return SQ_OK;
+}
+
+extern "C" int sq_profile_assign(int enable, double* total_ms, long long* launches) {
+    if (total_ms) *total_ms = g_prof_ms;
+    if (launches) *launches = g_prof_launches;
+    g_prof_on = enable != 0;
+    if (enable == 2) { g_prof_ms = 0.0; g_prof_launches = 0; g_prof_on = true; }
     return SQ_OK;
 }
