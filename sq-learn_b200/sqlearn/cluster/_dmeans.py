@@ -182,6 +182,26 @@ def _centroid_tomography(engine, centers, error, true_tomography, stop_when_reac
     return out
 
 
+def _lloyd_iteration(engine, centers, centers_old, centers_new, host, delta, intermediate_err, true_tomography,
+                     stop_when_reached_accuracy, pool, true_distance_estimate):
+    """One pass of the loop body of _kmeans_single_lloyd (reference: _dmeans.py:619-651):
+    E-step, M-step (+ centroid tomography), centre shift; updates ``centers`` in place and
+    returns (inertia, shift) read back through the pinned 2-double buffer ``host``."""
+    centers_old.copy_(centers)
+    labels, _, _ = _labels_inertia(engine, centers, delta=delta, pool=pool,
+                                   true_distance_estimate=true_distance_estimate)
+    out = _centers_update(engine, labels, delta / 2, intermediate_error=intermediate_err,
+                          true_tomography=true_tomography,
+                          stop_when_reached_accuracy=stop_when_reached_accuracy,
+                          centers_old=centers_old, centers_out=centers_new)
+    centers.copy_(out)
+    shift_dev = engine.shift(centers_old, centers)
+    host[0:1].copy_(engine.inertia, non_blocking=True)   # already summed over ranks by the M-step
+    host[1:2].copy_(shift_dev, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return float(host[0]), float(host[1])
+
+
 def _kmeans_single_lloyd(engine, sample_weight, centers_init, intermediate_err, true_tomography,
                          stop_when_reached_accuracy, pool, true_distance_estimate, max_iter=300, verbose=False,
                          tol=1e-4, delta=None):
@@ -206,20 +226,10 @@ def _kmeans_single_lloyd(engine, sample_weight, centers_init, intermediate_err, 
     center_shift_total = 0.0
     i = 0
     for i in range(max_iter):
-        centers_old.copy_(centers)
-        labels, _, inertia_dev = _labels_inertia(engine, centers, delta=delta, pool=pool,
-                                                 true_distance_estimate=true_distance_estimate)
-        error = delta / 2
-        out = _centers_update(engine, labels, error, intermediate_error=intermediate_err,
-                              true_tomography=true_tomography,
-                              stop_when_reached_accuracy=stop_when_reached_accuracy,
-                              centers_old=centers_old, centers_out=centers_new)
-        centers.copy_(out)
-        shift_dev = engine.shift(centers_old, centers)
-        host[0:1].copy_(engine.inertia, non_blocking=True)   # already summed over ranks by the M-step
-        host[1:2].copy_(shift_dev, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-        inertia, center_shift_total = float(host[0]), float(host[1])
+        labels = engine.labels
+        inertia, center_shift_total = _lloyd_iteration(
+            engine, centers, centers_old, centers_new, host, delta, intermediate_err, true_tomography,
+            stop_when_reached_accuracy, pool, true_distance_estimate)
         if verbose:
             print("Iteration %2d, inertia %.3f" % (i, inertia))
         if best_inertia is None or inertia < best_inertia:
@@ -260,8 +270,6 @@ def _validate_X(X, copy=True):
     X = np.array(X, dtype=np.float64, order='C', copy=copy) if copy else np.ascontiguousarray(X, dtype=np.float64)
     if X.ndim != 2:
         raise ValueError("Expected 2D array, got array with shape %r" % (X.shape,))
-    if not np.isfinite(X).all():
-        raise ValueError("Input contains NaN, infinity or a value too large for dtype('float64').")
     return X
 
 
@@ -414,6 +422,9 @@ class qMeans_(BaseEstimator):
             raise ValueError("Found array with 0 sample(s)")
         engine = QMeansEngine(Xd, self.n_clusters)
         self._engine_launches = 0
+        # _assert_all_finite of the reference's check_array, evaluated on the device: ||X||_F^2 is finite
+        if not bool(torch.isfinite(engine.xnorm.sum()).item()):
+            raise ValueError("Input contains NaN, infinity or a value too large for dtype('float64').")
         self._preamble(engine)
 
         if self.delta == 0:
