@@ -76,6 +76,23 @@ int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, c
                      double delta, unsigned long long seed, unsigned long long offset, int* labels,
                      double* mindist, double* inertia, int* n_fixed, void* ws, size_t ws_bytes, void* stream);
 
+/* Same E-step as sq_qmeans_assign for callers that cannot give the library a workspace
+ * (no counterpart in the reference).  Meant for hosts that are not allowed to allocate on
+ * the device: a plugin inside a process whose GPU memory belongs to another framework's
+ * pool, or a serving loop that cannot afford the device-wide synchronisation cudaMalloc
+ * implies.  The scratch is a 2 MiB array built into the library (resident on every GPU
+ * that loads it, until exit), so a call is limited to n <= 65536 rows and k <= 1024
+ * centroids; larger sizes return SQ_STATUS_UNSUPPORTED with a message.  Nothing is
+ * allocated or freed by this call.  The first call on each device looks up the array's
+ * device address (that device must be current) - make that first call before starting any
+ * stream capture.  All calls share the one array and it keeps the previous call's contents:
+ * two calls whose kernels can run at the same time on one GPU (different streams, no
+ * dependency) race on it; serialise them.  Inputs, outputs and results are those of
+ * sq_qmeans_assign.                                                                      */
+int sq_qmeans_assign_noalloc(const double* X, const double* xnorm, long long n, int d, const double* C, int k,
+                             int mode, double delta, unsigned long long seed, unsigned long long offset, int* labels,
+                             double* mindist, double* inertia, int* n_fixed, void* stream);
+
 /* Timing hook for the roofline measurement (no reference counterpart): enable = 2 resets
  * the counters and turns per-launch CUDA-event timing of the main E-step kernel on (each
  * sq_qmeans_assign then blocks until its kernel ends); 1 = on, 0 = off.  The totals seen

@@ -651,3 +651,61 @@ extern "C" int sq_profile_assign(int enable, double* total_ms, long long* launch
     if (enable == 2) { g_prof_ms = 0.0; g_prof_launches = 0; g_prof_on = true; }
     return SQ_OK;
 }
+
+// ---------------------------------------------------------------------------
+// E-step for callers that must not allocate device memory
+// ---------------------------------------------------------------------------
+// Some hosts of this library cannot hand it a workspace: a plugin running
+// inside a process whose device memory is entirely owned by another
+// framework's pool, a latency-critical serving loop where cudaMalloc's
+// implicit device-wide synchronisation is not acceptable, or glue code that
+// only ever sees the caller's input and output buffers.  For them the scratch
+// of sq_qmeans_assign lives in the fixed array below.  The array is part of
+// the library image: every GPU that loads libsqb200.so carries these 2 MiB
+// until the process exits, whether or not this entry point is ever called.
+#define SQ_NOALLOC_MAX_ROWS 65536
+#define SQ_NOALLOC_MAX_CLUSTERS 1024
+#define SQ_NOALLOC_SCRATCH_BYTES (2u << 20)
+static __device__ __align__(256) unsigned char g_noalloc_scratch[SQ_NOALLOC_SCRATCH_BYTES];
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not an
+// address a kernel can use; the per-device address comes from the runtime.
+static void* g_noalloc_ptr[64] = {nullptr};
+
+static int noalloc_scratch_for_current_device(void** out) {
+    int dev = -1;
+    SQ_CUDA(cudaGetDevice(&dev));
+    SQ_REQUIRE(dev >= 0 && dev < 64, "sq_qmeans_assign_noalloc: device ordinal %d not supported", dev);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        SQ_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return SQ_OK;
+}
+
+extern "C" int sq_qmeans_assign_noalloc(const double* X, const double* xnorm, long long n, int d, const double* C,
+                                        int k, int mode, double delta, unsigned long long seed,
+                                        unsigned long long offset, int* labels, double* mindist, double* inertia,
+                                        int* n_fixed, void* stream_) {
+    if (n > SQ_NOALLOC_MAX_ROWS || k > SQ_NOALLOC_MAX_CLUSTERS) {
+        set_error("sq_qmeans_assign_noalloc: n=%lld rows / k=%d centroids exceed the built-in scratch "
+                  "(at most %d rows and %d centroids per call); split the batch or use sq_qmeans_assign "
+                  "with a workspace", n, k, SQ_NOALLOC_MAX_ROWS, SQ_NOALLOC_MAX_CLUSTERS);
+        return SQ_ERR_UNSUPPORTED;
+    }
+    SQ_REQUIRE(n >= 1 && k >= 1, "sq_qmeans_assign_noalloc: bad shape n=%lld k=%d", n, k);
+    size_t need = assign_ws_layout(n, k, nullptr, nullptr);
+    if (need > SQ_NOALLOC_SCRATCH_BYTES) {  // cannot happen within the limits above; kept as a guard
+        set_error("sq_qmeans_assign_noalloc: scratch of %zu bytes exceeds the built-in %u", need, SQ_NOALLOC_SCRATCH_BYTES);
+        return SQ_ERR_UNSUPPORTED;
+    }
+    void* scratch = nullptr;
+    int rc = noalloc_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    // sq_qmeans_assign zeroes the one word that has to start at zero (the near-tie counter) itself;
+    // everything else in the scratch is written before it is read.
+    return sq_qmeans_assign(X, xnorm, n, d, C, k, mode, delta, seed, offset, labels, mindist, inertia, n_fixed,
+                            scratch, SQ_NOALLOC_SCRATCH_BYTES, stream_);
+}

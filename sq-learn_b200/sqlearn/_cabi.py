@@ -27,6 +27,8 @@ SIGNATURES = {
     "sq_qmeans_assign_workspace_bytes": (c_size_t, [c_ll, c_int, c_int]),
     "sq_qmeans_assign": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p, c_int, c_int, c_double, c_ull, c_ull,
                                  c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "sq_qmeans_assign_noalloc": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p, c_int, c_int, c_double, c_ull, c_ull,
+                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "sq_profile_assign": (c_int, [c_int, c_void_p, c_void_p]),
     "sq_row_sqnorms": (c_int, [c_void_p, c_ll, c_int, c_void_p, c_void_p]),
     "sq_sum_f64": (c_int, [c_void_p, c_ll, c_void_p, c_void_p, c_size_t, c_void_p]),
