@@ -29,6 +29,7 @@
 #include "common.cuh"
 #include "sqb200.h"
 #include "fejer.cuh"
+#include <cstdlib>
 
 namespace sq {
 
@@ -53,12 +54,13 @@ struct AssignArgs {
     double delta;
     double tie_tol;        // relative rounding bound for the near-tie test
     unsigned long long seed, offset;
+    int dbg;               // SQ_ASSIGN_DBG experiments: 1 = no loads, 2 = no epilogue (timing only, wrong results)
 };
 
-template <int BM_, int BN_, int WARPS_M_, int WARPS_N_, int STAGES_>
+template <int BM_, int BN_, int WARPS_M_, int WARPS_N_, int STAGES_, int BK_ = 16, int MIN_CTAS_ = 1>
 struct TileCfg {
     static constexpr int BM = BM_, BN = BN_, WARPS_M = WARPS_M_, WARPS_N = WARPS_N_, STAGES = STAGES_;
-    static constexpr int BK = 16, KB = BK / 4;
+    static constexpr int BK = BK_, KB = BK / 4, MIN_CTAS = MIN_CTAS_;
     static constexpr int WM = BM / WARPS_M, WN = BN / WARPS_N;
     static constexpr int MI = WM / 8, NI = WN / 8;
     static constexpr int THREADS = 32 * WARPS_M * WARPS_N;
@@ -93,74 +95,93 @@ __device__ __noinline__ double ipe_distance(double dot, double xn, double cn, do
     return 2.0 * S * s[6];
 }
 
-template <class Cfg, bool VEC16>
-__device__ __forceinline__ void load_chunk(double* stage, const AssignArgs& a, long long r0, int n0, int kc, int tid) {
-    constexpr int BM = Cfg::BM, BN = Cfg::BN;
-    constexpr int PPR = VEC16 ? 8 : 16;           // pieces per row per chunk
-    constexpr int PIECES = (BM + BN) * PPR;
-    double* As = stage;
-    double* Bs = stage + BM * Cfg::BK;
-    for (int p = tid; p < PIECES; p += Cfg::THREADS) {
-        int row = p / PPR, kp = p % PPR;
-        int kk = VEC16 ? kp * 2 : kp;             // k offset inside the chunk
-        int kglob = kc * Cfg::BK + kk;
-        int kb = kk >> 2;
-        bool isA = row < BM;
-        int lr = isA ? row : row - BM;
-        const double* src;
-        bool ok;
-        if (isA) {
-            long long gr = r0 + lr;
-            ok = (gr < a.n) && (kglob < a.d);
-            src = a.X + (ok ? gr * (long long)a.d + kglob : 0);
-        } else {
-            int gc = n0 + lr;
-            ok = (gc < a.k) && (kglob < a.d);
-            src = a.C + (ok ? (long long)gc * a.d + kglob : 0);
-        }
-        double* base = isA ? As : Bs;
-        int rows = isA ? BM : BN;
-        double* dst = base + ((kb * rows + (lr ^ kb)) << 2) + (kk & 3);
-        if (VEC16) cp_async16(dst, src, ok); else cp_async8(dst, src, ok);
-    }
-}
-
 template <class Cfg, bool VEC16, int MODE>
-__global__ void __launch_bounds__(Cfg::THREADS, 1) qmeans_assign_kernel(AssignArgs a) {
+__global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_kernel(AssignArgs a) {
     constexpr int BM = Cfg::BM, BN = Cfg::BN, MI = Cfg::MI, NI = Cfg::NI, WN_CNT = Cfg::WARPS_N;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ __align__(16) double smem[];
     double* stages = smem;                                   // STAGES * STAGE_DOUBLES
-    double* red_m1 = stages + STAGES * Cfg::STAGE_DOUBLES;   // [BM][WN_CNT]
-    double* red_m2 = red_m1 + BM * WN_CNT;                   // [BM][WN_CNT]
-    double* run_m1 = red_m2 + BM * WN_CNT;                   // [BM]
-    double* run_m2 = run_m1 + BM;                            // [BM]
-    double* row_thr = run_m2 + BM;                           // [BM]
-    unsigned long long* cand = (unsigned long long*)(row_thr + BM);  // [BM]
-    int* red_a1 = (int*)(cand + BM);                         // [BM][WN_CNT]
-    int* run_a1 = red_a1 + BM * WN_CNT;                      // [BM]
+    double* wmin = stages + STAGES * Cfg::STAGE_DOUBLES;     // [BM][WN_CNT] per-warp row minima
+    double* xn_s = wmin + BM * WN_CNT;                       // [BM] ||x||^2 of the tile's rows
+    double* thr_s = xn_s + BM;                               // [BM] precomputed row minimum (WINDOW, k > BN)
+    double* run_m1 = thr_s + BM;                             // [BM] running minimum over centroid tiles
+    unsigned long long* cand = (unsigned long long*)(run_m1 + BM);  // [BM] (priority << 32 | col), WINDOW
+    int* cnt = (int*)(cand + BM);                            // [BM] candidates found in the row
+    int* first = cnt + BM;                                   // [BM] lowest candidate column
+    int* run_a1 = first + BM;                                // [BM]
+    int* run_cnt = run_a1 + BM;                              // [BM]
+    double* cn_s = (double*)(run_cnt + BM);                  // [NT*BN] centroid norms (+inf past k)
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp / WN_CNT, wn = warp % WN_CNT;
     const int lq = lane >> 2, lr4 = lane & 3;
+
+    for (int j = tid; j < a.NT * BN; j += Cfg::THREADS) cn_s[j] = (j < a.k) ? a.cnorm[j] : INFINITY;
 
     // tiles owned by this CTA: blockIdx.x, + gridDim.x, ...
     const int my_tiles = (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const int per_tile = a.NT * a.KC;
     const long long total = (long long)my_tiles * per_tile;
 
-    auto issue = [&](long long q) {
-        if (q < total) {
-            int tl = (int)(q / per_tile);
-            int rem = (int)(q % per_tile);
-            int nt = rem / a.KC, kc = rem % a.KC;
-            long long tile = (long long)blockIdx.x + (long long)tl * gridDim.x;
-            load_chunk<Cfg, VEC16>(stages + (q % STAGES) * Cfg::STAGE_DOUBLES, a, tile * BM, nt * BN, kc, tid);
+    // ---- loader state: every thread copies the same (row offset, k offset) piece of each pass ----
+    constexpr int PPR = VEC16 ? Cfg::BK / 2 : Cfg::BK;  // pieces per row per chunk
+    constexpr int RPI = Cfg::THREADS / PPR;        // rows covered by one pass of the CTA
+    constexpr int NA = (BM + RPI - 1) / RPI, NB = (BN + RPI - 1) / RPI;
+    static_assert(RPI % 4 == 0, "row swizzle needs passes aligned to 4 rows");
+    static_assert(MI <= 4, "the multi-candidate path selects accumulator rows by hand for MI <= 4");
+    const int r_t = tid / PPR;
+    const int kk = VEC16 ? (tid % PPR) * 2 : (tid % PPR);
+    const int kb_t = kk >> 2;
+    const int dstA0 = ((kb_t * BM + (r_t ^ kb_t)) << 2) + (kk & 3);
+    const int dstB0 = BM * Cfg::BK + ((kb_t * BN + (r_t ^ kb_t)) << 2) + (kk & 3);
+    const long long rpi_d = (long long)RPI * a.d;
+    long long p_left = total;
+    long long p_tile = blockIdx.x;
+    int p_nt = 0, p_kc = 0, p_stage = 0;
+    const double* a_ptr = a.X + (p_tile * BM + r_t) * (long long)a.d + kk;
+    long long a_rem = a.n - (p_tile * BM + r_t);   // rows left from this thread's first row
+    const double* b_ptr = a.C + (long long)r_t * a.d + kk;
+    int b_rem = a.k - r_t;
+
+    auto issue = [&]() {
+        if (p_left > 0 && !(a.dbg & 1)) {
+            double* st = stages + p_stage * Cfg::STAGE_DOUBLES;
+            const int koff = p_kc * Cfg::BK;
+            const bool kok = koff + kk < a.d;
+#pragma unroll
+            for (int i = 0; i < NA; ++i) {
+                if (BM % RPI == 0 || r_t + i * RPI < BM) {
+                    bool ok = kok && (long long)(i * RPI) < a_rem;
+                    const double* src = ok ? a_ptr + i * rpi_d + koff : a.X;
+                    if (VEC16) cp_async16(st + dstA0 + i * RPI * 4, src, ok); else cp_async8(st + dstA0 + i * RPI * 4, src, ok);
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < NB; ++i) {
+                if (BN % RPI == 0 || r_t + i * RPI < BN) {
+                    bool ok = kok && i * RPI < b_rem;
+                    const double* src = ok ? b_ptr + i * rpi_d + koff : a.C;
+                    if (VEC16) cp_async16(st + dstB0 + i * RPI * 4, src, ok); else cp_async8(st + dstB0 + i * RPI * 4, src, ok);
+                }
+            }
+            --p_left;
+            p_stage = (p_stage + 1 == STAGES) ? 0 : p_stage + 1;
+            if (++p_kc == a.KC) {
+                p_kc = 0;
+                if (++p_nt == a.NT) {
+                    p_nt = 0;
+                    p_tile += gridDim.x;
+                    a_ptr = a.X + (p_tile * BM + r_t) * (long long)a.d + kk;
+                    a_rem = a.n - (p_tile * BM + r_t);
+                }
+                b_ptr = a.C + ((long long)p_nt * BN + r_t) * a.d + kk;
+                b_rem = a.k - (p_nt * BN + r_t);
+            }
         }
         cp_async_commit();
     };
 
-    for (int s = 0; s < STAGES - 1; ++s) issue(s);
+    for (int s = 0; s < STAGES - 1; ++s) issue();
 
     double acc[MI][NI][2];
 #pragma unroll
@@ -168,168 +189,200 @@ __global__ void __launch_bounds__(Cfg::THREADS, 1) qmeans_assign_kernel(AssignAr
 #pragma unroll
         for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    int kc = 0, nt = 0, tl = 0;
+    // fragment offsets inside a stage (doubles); kb only permutes rows inside aligned groups of 4
+    const int fragA = ((wm * Cfg::WM + lq) << 2) + lr4;
+    const int fragB = BM * Cfg::BK + ((wn * Cfg::WN + lq) << 2) + lr4;
+
+    int kc = 0, nt = 0, tl = 0, c_stage = 0;
     for (long long q = 0; q < total; ++q) {
         cp_async_wait<STAGES - 2>();
         __syncthreads();
-        issue(q + STAGES - 1);
+        issue();
 
-        const double* As = stages + (q % STAGES) * Cfg::STAGE_DOUBLES;
-        const double* Bs = As + BM * Cfg::BK;
+        const double* St = stages + c_stage * Cfg::STAGE_DOUBLES;
+        c_stage = (c_stage + 1 == STAGES) ? 0 : c_stage + 1;
 #pragma unroll
         for (int kb = 0; kb < Cfg::KB; ++kb) {
             double af[MI], bf[NI];
+            // (row ^ kb) with row = base + 8*i + lq: only lq's low two bits change
+            const int swz = ((lq ^ kb) - lq) << 2;
 #pragma unroll
-            for (int i = 0; i < MI; ++i) af[i] = As[((kb * BM + ((wm * Cfg::WM + i * 8 + lq) ^ kb)) << 2) + lr4];
+            for (int i = 0; i < MI; ++i) af[i] = St[fragA + swz + ((kb * BM + i * 8) << 2)];
 #pragma unroll
-            for (int j = 0; j < NI; ++j) bf[j] = Bs[((kb * BN + ((wn * Cfg::WN + j * 8 + lq) ^ kb)) << 2) + lr4];
+            for (int j = 0; j < NI; ++j) bf[j] = St[fragB + swz + ((kb * BN + j * 8) << 2)];
 #pragma unroll
             for (int i = 0; i < MI; ++i)
 #pragma unroll
                 for (int j = 0; j < NI; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
         }
 
-        if (kc == a.KC - 1) {
+        if (kc == a.KC - 1 && (a.dbg & 2)) {
+            if (acc[0][0][0] == 12345.678) a.mindist[0] = acc[MI - 1][NI - 1][1];
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+#pragma unroll
+                for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        } else if (kc == a.KC - 1) {
             // ------------------------------ epilogue ------------------------------
+            // v = |c|^2 - 2 x.c per element; the row minimum is found first, then the set of
+            // "candidates" v <= min + thr: thr = delta (WINDOW), a rounding bound (EXACT: more than
+            // one candidate sends the row to the exact fix-up) or 0 (IPE).  Rows with a single
+            // candidate - the common case - need no random number at all.
             const long long tile = (long long)blockIdx.x + (long long)tl * gridDim.x;
             const long long r0 = tile * BM;
             const int n0 = nt * BN;
             const bool last_nt = (nt == a.NT - 1);
+            const int colbase = n0 + wn * Cfg::WN + lr4 * 2;
 
+            if (tid < BM) {
+                long long gr = r0 + tid;
+                xn_s[tid] = (gr < a.n) ? a.xnorm[gr] : 0.0;
+                if (MODE == MODE_WINDOW && a.rowmin_in) thr_s[tid] = (gr < a.n) ? a.rowmin_in[gr] : 0.0;
+                if (MODE != MODE_WINDOW || nt == 0) { cnt[tid] = 0; first[tid] = 0x7fffffff; cand[tid] = ~0ull; }
+            }
             if (MODE == MODE_IPE) {
-                // replace every dot product by its noisy squared distance minus |x|^2
+                __syncthreads();  // xn_s
+                // replace every dot product by (noisy squared distance - |x|^2), stored as the dot
+                // product that would give it, so the code below is shared with the other modes
 #pragma unroll
                 for (int i = 0; i < MI; ++i) {
-                    long long gr = r0 + wm * Cfg::WM + i * 8 + lq;
-                    double xn = (gr < a.n) ? a.xnorm[gr] : 0.0;
+                    const int row = wm * Cfg::WM + i * 8 + lq;
+                    const long long gr = r0 + row;
+                    const double xn = xn_s[row];
 #pragma unroll
                     for (int j = 0; j < NI; ++j)
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
-                            int col = n0 + wn * Cfg::WN + j * 8 + lr4 * 2 + e;
+                            int col = colbase + j * 8 + e;
                             if (gr < a.n && col < a.k) {
                                 Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x1bE0u, (unsigned)col);
-                                double cn = a.cnorm[col];
+                                double cn = cn_s[col];
                                 double dt = ipe_distance(acc[i][j][e], xn, cn, 0.5 * a.delta, rng);
-                                // store in the same form the other modes use: v = D - |x|^2 = cn - 2*dot
                                 acc[i][j][e] = 0.5 * (cn - (dt - xn));
                             }
                         }
                 }
             }
-
-            if (MODE == MODE_WINDOW && nt == 0 && tid < BM) cand[tid] = ~0ull;
-
-            // per-thread top-2 over its 2*NI columns, per row fragment
+            // ---- phase A: v in place, per-warp row minima ----
+#pragma unroll
+            for (int j = 0; j < NI; ++j) {
+                const double2 cn2 = *reinterpret_cast<const double2*>(cn_s + colbase + j * 8);
+#pragma unroll
+                for (int i = 0; i < MI; ++i) {
+                    acc[i][j][0] = fma(-2.0, acc[i][j][0], cn2.x);
+                    acc[i][j][1] = fma(-2.0, acc[i][j][1], cn2.y);
+                }
+            }
 #pragma unroll
             for (int i = 0; i < MI; ++i) {
-                double m1 = INFINITY, m2 = INFINITY;
-                int a1 = 0x7fffffff;
+                double m = fmin(acc[i][0][0], acc[i][0][1]);
+#pragma unroll
+                for (int j = 1; j < NI; ++j) m = fmin(m, fmin(acc[i][j][0], acc[i][j][1]));
+                m = fmin(m, __shfl_xor_sync(0xffffffffu, m, 1));
+                m = fmin(m, __shfl_xor_sync(0xffffffffu, m, 2));
+                if (lr4 == 0) wmin[(wm * Cfg::WM + i * 8 + lq) * WN_CNT + wn] = m;
+            }
+            __syncthreads();
+            // ---- phase B: row minimum over the warps, candidates ----
+            bool have_multi = false;
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                const int row = wm * Cfg::WM + i * 8 + lq;
+                double tmin = wmin[row * WN_CNT];
+#pragma unroll
+                for (int w = 1; w < WN_CNT; ++w) tmin = fmin(tmin, wmin[row * WN_CNT + w]);
+                double thr;
+                if (MODE == MODE_WINDOW) thr = (a.rowmin_in ? thr_s[row] : tmin) + a.delta;
+                else if (MODE == MODE_EXACT) thr = tmin + fmax(a.tie_tol, 0.0) * (xn_s[row] + 2.0 * fabs(tmin));
+                else thr = tmin;
+                unsigned mask = 0;
 #pragma unroll
                 for (int j = 0; j < NI; ++j)
 #pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        int col = n0 + wn * Cfg::WN + j * 8 + lr4 * 2 + e;
-                        if (col < a.k) {
-                            double v = a.cnorm[col] - 2.0 * acc[i][j][e];
-                            if (v < m1) { m2 = m1; m1 = v; a1 = col; }
-                            else if (v < m2) m2 = v;
-                        }
-                    }
-                // merge across the 4 lanes that share this row
-#pragma unroll
-                for (int o = 1; o <= 2; o <<= 1) {
-                    double om1 = __shfl_xor_sync(0xffffffffu, m1, o);
-                    double om2 = __shfl_xor_sync(0xffffffffu, m2, o);
-                    int oa1 = __shfl_xor_sync(0xffffffffu, a1, o);
-                    if (om1 < m1 || (om1 == m1 && oa1 < a1)) { m2 = fmin(m1, om2); m1 = om1; a1 = oa1; }
-                    else m2 = fmin(m2, om1);
+                    for (int e = 0; e < 2; ++e) mask |= (acc[i][j][e] <= thr ? 1u : 0u) << (j * 2 + e);
+                if (mask) {
+                    int b0 = __ffs(mask) - 1;
+                    atomicAdd(&cnt[row], __popc(mask));
+                    atomicMin(&first[row], colbase + (b0 >> 1) * 8 + (b0 & 1));
                 }
-                if (lr4 == 0) {
-                    int row = wm * Cfg::WM + i * 8 + lq;
-                    red_m1[row * WN_CNT + wn] = m1;
-                    red_m2[row * WN_CNT + wn] = m2;
-                    red_a1[row * WN_CNT + wn] = a1;
+                if (MODE == MODE_WINDOW) {
+                    // keep the mask for the rare multi-candidate path (bits 8*i .. 8*i + 2*NI - 1 of a 64-bit word
+                    // would not fit for NI = 4 and MI = 4: recomputed there instead)
                 }
             }
             __syncthreads();
+            if (MODE == MODE_WINDOW) {
+                // rows with several candidates: uniform pick = smallest random priority
+#pragma unroll
+                for (int i = 0; i < MI; ++i) have_multi |= (cnt[wm * Cfg::WM + i * 8 + lq] > 1) || (a.NT > 1);
+                if (__syncthreads_or(have_multi)) {
+                    if (have_multi) {
+#pragma unroll 1
+                        for (int i = 0; i < MI; ++i) {
+                            const int row = wm * Cfg::WM + i * 8 + lq;
+                            if (cnt[row] <= 1 && a.NT == 1) continue;
+                            const long long gr = r0 + row;
+                            double tmin = wmin[row * WN_CNT];
+                            for (int w = 1; w < WN_CNT; ++w) tmin = fmin(tmin, wmin[row * WN_CNT + w]);
+                            const double thr = (a.rowmin_in ? thr_s[row] : tmin) + a.delta;
+                            unsigned long long best = ~0ull;
+#pragma unroll
+                            for (int j = 0; j < NI; ++j)
+#pragma unroll
+                                for (int e = 0; e < 2; ++e) {
+                                    double v = (i == 0) ? acc[0][j][e] : (i == 1 && MI > 1) ? acc[MI > 1 ? 1 : 0][j][e]
+                                             : (i == 2 && MI > 2) ? acc[MI > 2 ? 2 : 0][j][e] : acc[MI - 1][j][e];
+                                    int col = colbase + j * 8 + e;
+                                    if (v <= thr && col < a.k) {
+                                        Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, (unsigned)col);
+                                        unsigned r[4];
+                                        rng.block(r);
+                                        unsigned long long key = ((unsigned long long)r[0] << 32) | (unsigned)col;
+                                        best = key < best ? key : best;
+                                    }
+                                }
+                            if (best != ~0ull) atomicMin(&cand[row], best);
+                        }
+                    }
+                    __syncthreads();
+                }
+            }
+            // ---- phase C: one thread per row folds the tile into the running state and writes out ----
             if (tid < BM) {
                 const int row = tid;
-                double m1 = red_m1[row * WN_CNT], m2 = red_m2[row * WN_CNT];
-                int a1 = red_a1[row * WN_CNT];
-                for (int w = 1; w < WN_CNT; ++w) {
-                    double om1 = red_m1[row * WN_CNT + w], om2 = red_m2[row * WN_CNT + w];
-                    int oa1 = red_a1[row * WN_CNT + w];
-                    if (om1 < m1 || (om1 == m1 && oa1 < a1)) { m2 = fmin(m1, om2); m1 = om1; a1 = oa1; }
-                    else m2 = fmin(m2, om1);
-                }
-                if (nt > 0) {
-                    double om1 = run_m1[row], om2 = run_m2[row];
-                    int oa1 = run_a1[row];
-                    if (om1 < m1 || (om1 == m1 && oa1 < a1)) { m2 = fmin(m1, om2); m1 = om1; a1 = oa1; }
-                    else m2 = fmin(m2, om1);
-                }
-                run_m1[row] = m1; run_m2[row] = m2; run_a1[row] = a1;
+                const long long gr = r0 + row;
+                double tmin = wmin[row * WN_CNT];
+                for (int w = 1; w < WN_CNT; ++w) tmin = fmin(tmin, wmin[row * WN_CNT + w]);
+                const double xn = xn_s[row];
                 if (MODE == MODE_WINDOW) {
-                    long long gr = r0 + row;
-                    double base = (a.rowmin_in && gr < a.n) ? a.rowmin_in[gr] : m1;
-                    row_thr[row] = base + a.delta;
-                }
-                if (last_nt && MODE != MODE_WINDOW) {
-                    long long gr = r0 + row;
-                    if (gr < a.n) {
-                        double xn = a.xnorm[gr];
+                    if (last_nt && gr < a.n) {
+                        const unsigned long long c = cand[row];
+                        a.labels[gr] = (c != ~0ull) ? (int)(unsigned)(c & 0xffffffffu) : first[row];
+                        const double base = a.rowmin_in ? thr_s[row] : tmin;
+                        a.mindist[gr] = fmax(xn + base, 0.0);
+                    }
+                } else {
+                    const int c = cnt[row], f = first[row];
+                    double m1 = tmin;
+                    int a1 = f, rc = c;
+                    if (nt > 0) {
+                        const double pm = run_m1[row];
+                        const double tol = (MODE == MODE_EXACT) ? fmax(a.tie_tol, 0.0) * (xn + 2.0 * fabs(fmin(pm, tmin))) : 0.0;
+                        if (tmin < pm - tol) { /* new tile wins outright */ }
+                        else if (tmin <= pm + tol) {        // indistinguishable: count both (over-counting only flags more rows)
+                            rc = c + run_cnt[row];
+                            if (!(tmin < pm || (tmin == pm && f < run_a1[row]))) { m1 = pm; a1 = run_a1[row]; }
+                        } else { m1 = pm; a1 = run_a1[row]; rc = run_cnt[row]; }
+                    }
+                    run_m1[row] = m1; run_a1[row] = a1; run_cnt[row] = rc;
+                    if (last_nt && gr < a.n) {
                         a.labels[gr] = a1;
                         a.mindist[gr] = fmax(xn + m1, 0.0);
                         if (a.rowmin_out) a.rowmin_out[gr] = m1;
-                        if (MODE == MODE_EXACT && m2 < INFINITY && (m2 - m1) <= a.tie_tol * (xn + fabs(m1) + fabs(m2))) {
+                        if (MODE == MODE_EXACT && rc > 1 && a.tie_tol >= 0.0) {
                             int slot = atomicAdd(a.flag_count, 1);
                             a.flag_rows[slot] = (int)gr;  // n < 2^31 per call (checked on the host)
                         }
-                    }
-                }
-            }
-            if (MODE == MODE_WINDOW) {
-                __syncthreads();
-                // uniform pick inside the window: smallest random priority wins
-#pragma unroll
-                for (int i = 0; i < MI; ++i) {
-                    int row = wm * Cfg::WM + i * 8 + lq;
-                    long long gr = r0 + row;
-                    double thr = row_thr[row];
-                    unsigned long long best = ~0ull;
-#pragma unroll
-                    for (int j = 0; j < NI; ++j)
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            int col = n0 + wn * Cfg::WN + j * 8 + lr4 * 2 + e;
-                            if (col < a.k) {
-                                double v = a.cnorm[col] - 2.0 * acc[i][j][e];
-                                if (v <= thr) {
-                                    Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, (unsigned)col);
-                                    unsigned r[4];
-                                    rng.block(r);
-                                    unsigned long long key = ((unsigned long long)r[0] << 32) | (unsigned)col;
-                                    best = key < best ? key : best;
-                                }
-                            }
-                        }
-#pragma unroll
-                    for (int o = 1; o <= 2; o <<= 1) {
-                        unsigned long long ob = __shfl_xor_sync(0xffffffffu, best, o);
-                        best = ob < best ? ob : best;
-                    }
-                    if (lr4 == 0 && best != ~0ull) atomicMin(&cand[row], best);
-                }
-                __syncthreads();
-                if (tid < BM && last_nt) {
-                    long long gr = r0 + tid;
-                    if (gr < a.n) {
-                        unsigned long long c = cand[tid];
-                        // with a precomputed row minimum the argmin itself is always a candidate
-                        a.labels[gr] = (c == ~0ull) ? run_a1[tid] : (int)(unsigned)(c & 0xffffffffu);
-                        double base = a.rowmin_in ? a.rowmin_in[gr] : run_m1[tid];
-                        a.mindist[gr] = fmax(a.xnorm[gr] + base, 0.0);
                     }
                 }
             }
@@ -495,8 +548,8 @@ static size_t assign_ws_layout(long long n, int k, AssignWs* w, char* base) {
 
 template <class Cfg>
 static size_t assign_smem_bytes() {
-    return (size_t)Cfg::STAGES * Cfg::STAGE_DOUBLES * 8 + (size_t)Cfg::BM * Cfg::WARPS_N * (8 + 8 + 4) +
-           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4) + 64;
+    return (size_t)Cfg::STAGES * Cfg::STAGE_DOUBLES * 8 + (size_t)Cfg::BM * Cfg::WARPS_N * 8 +
+           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4 * 4) + 64;  // + NT*BN centroid norms, added at launch
 }
 
 // optional timing of the main kernel alone (bench.py's roofline leg): events are
@@ -511,18 +564,24 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
     a.num_tiles = (int)((a.n + Cfg::BM - 1) / Cfg::BM);
     a.NT = (a.k + Cfg::BN - 1) / Cfg::BN;
     a.KC = (a.d + Cfg::BK - 1) / Cfg::BK;
-    int grid = device_sm_count();
-    if (grid > a.num_tiles) grid = a.num_tiles;
-    size_t smem = assign_smem_bytes<Cfg>();
+    size_t smem = assign_smem_bytes<Cfg>() + (size_t)a.NT * Cfg::BN * sizeof(double);
+    if (smem > 227 * 1024) { set_error("sq_qmeans_assign: k=%d needs %zu bytes of shared memory", a.k, smem); return SQ_ERR_UNSUPPORTED; }
     bool vec16 = (a.d & 1) == 0 && ((uintptr_t)a.X & 15) == 0 && ((uintptr_t)a.C & 15) == 0;
     if (g_prof_on) {
         if (!g_prof_ev[0]) { SQ_CUDA(cudaEventCreate(&g_prof_ev[0])); SQ_CUDA(cudaEventCreate(&g_prof_ev[1])); }
         SQ_CUDA(cudaEventRecord(g_prof_ev[0], stream));
     }
+    // persistent grid: one CTA per resident slot, tiles handed out by static striding
 #define SQ_LAUNCH_ASSIGN(V, M)                                                                                       \
     do {                                                                                                            \
         SQ_CUDA(cudaFuncSetAttribute(qmeans_assign_kernel<Cfg, V, M>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
                                      (int)smem));                                                                   \
+        int per_sm = 1;                                                                                             \
+        SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, qmeans_assign_kernel<Cfg, V, M>,             \
+                                                              Cfg::THREADS, smem));                                 \
+        if (per_sm < 1) per_sm = 1;                                                                                 \
+        int grid = device_sm_count() * per_sm;                                                                      \
+        if (grid > a.num_tiles) grid = a.num_tiles;                                                                 \
         qmeans_assign_kernel<Cfg, V, M><<<grid, Cfg::THREADS, smem, stream>>>(a);                                   \
     } while (0)
     if (vec16) {
@@ -549,11 +608,12 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
 }
 
 // tile shapes: wide (all of k <= 256 in one sweep) down to narrow for tiny k
-using CfgN256 = TileCfg<64, 256, 2, 8, 4>;   // 512 threads, 160 KB ring
-using CfgN128 = TileCfg<128, 128, 4, 4, 4>;  // 512 threads, 128 KB ring
-using CfgN64 = TileCfg<128, 64, 4, 2, 4>;    // 256 threads
-using CfgN32 = TileCfg<128, 32, 4, 1, 4>;    // 128 threads
-using CfgN16 = TileCfg<256, 16, 8, 1, 4>;    // 256 threads, k <= 16
+// Two CTAs share an SM so that one CTA's epilogue (tensor pipe idle) overlaps the other's main loop.
+using CfgN256 = TileCfg<32, 256, 1, 8, 5, 8, 2>;   // 256 threads, 5 x 18 KB ring, 2 CTAs/SM
+using CfgN128 = TileCfg<64, 128, 2, 4, 5, 8, 2>;   // 256 threads, 5 x 12 KB ring
+using CfgN64 = TileCfg<128, 64, 4, 2, 4, 16, 2>;   // 256 threads, 4 x 24 KB ring
+using CfgN32 = TileCfg<128, 32, 4, 1, 4, 16, 2>;   // 128 threads
+using CfgN16 = TileCfg<256, 16, 8, 1, 3, 16, 2>;   // 256 threads, k <= 16
 
 static int dispatch_assign(const AssignArgs& a, cudaStream_t stream, int* bn_used) {
     int k = a.k;
@@ -622,6 +682,7 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     a.n = n; a.d = d; a.k = k; a.mode = mode; a.delta = delta;
     a.tie_tol = 16.0 * (d + 8) * 1.1102230246251565e-16;
     a.seed = seed; a.offset = offset;
+    { const char* e = getenv("SQ_ASSIGN_DBG"); a.dbg = e ? atoi(e) : 0; }
     int bn = 0;
     if (mode == MODE_WINDOW && k > 256) {
         // the window needs the row minimum over all k before candidates can be drawn
