@@ -30,6 +30,8 @@
 #include "sqb200.h"
 #include "fejer.cuh"
 #include <cstdlib>
+#include <cstring>
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched at run time, no libcuda link)
 
 namespace sq {
 
@@ -95,11 +97,41 @@ __device__ __noinline__ double ipe_distance(double dot, double xn, double cn, do
     return 2.0 * S * s[6];
 }
 
-template <class Cfg, bool VEC16, int MODE>
-__global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_kernel(AssignArgs a) {
+// ---- TMA / mbarrier helpers (sm_90+ PTX; SASS: UTMALDG, SYNCS) -----------------
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t}"
+        ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity)
+        : "memory");
+}
+// one 2-D box: coordinates (c0 = element along the row, c1 = row)
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, unsigned long long* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(map), "r"(c0), "r"(c1),
+          "r"((unsigned)__cvta_generic_to_shared(bar))
+        : "memory");
+}
+
+template <class Cfg, bool VEC16, int MODE, bool TMA>
+__global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_kernel(AssignArgs a, const __grid_constant__ CUtensorMap tmA,
+                                                                          const __grid_constant__ CUtensorMap tmB) {
     constexpr int BM = Cfg::BM, BN = Cfg::BN, MI = Cfg::MI, NI = Cfg::NI, WN_CNT = Cfg::WARPS_N;
     constexpr int STAGES = Cfg::STAGES;
-    extern __shared__ __align__(16) double smem[];
+    extern __shared__ __align__(1024) double smem[];           // fragment blocks are 256 B: keep them line-aligned
     double* stages = smem;                                   // STAGES * STAGE_DOUBLES
     double* wmin = stages + STAGES * Cfg::STAGE_DOUBLES;     // [BM][WN_CNT] per-warp row minima
     double* xn_s = wmin + BM * WN_CNT;                       // [BM] ||x||^2 of the tile's rows
@@ -111,12 +143,21 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     int* run_a1 = first + BM;                                // [BM]
     int* run_cnt = run_a1 + BM;                              // [BM]
     double* cn_s = (double*)(run_cnt + BM);                  // [NT*BN] centroid norms (+inf past k)
+    unsigned long long* full_bar = (unsigned long long*)(cn_s + a.NT * BN);  // [STAGES] TMA completion barriers
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp / WN_CNT, wn = warp % WN_CNT;
     const int lq = lane >> 2, lr4 = lane & 3;
 
     for (int j = tid; j < a.NT * BN; j += Cfg::THREADS) cn_s[j] = (j < a.k) ? a.cnorm[j] : INFINITY;
+    if (TMA) {
+        if (tid == 0) {
+            for (int s = 0; s < STAGES; ++s) mbar_init(&full_bar[s], 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        }
+        __syncthreads();
+    }
 
     // tiles owned by this CTA: blockIdx.x, + gridDim.x, ...
     const int my_tiles = (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
@@ -144,6 +185,27 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     int b_rem = a.k - r_t;
 
     auto issue = [&]() {
+        if (TMA) {
+            // one thread hands the whole chunk to the TMA unit: per k-block of 4 one box {4, rows} for X and
+            // one for C, landing as dense [k/4][row][4] slabs; rows / columns past the end arrive as zeros
+            if (tid == 0 && p_left > 0) {
+                double* st = stages + p_stage * Cfg::STAGE_DOUBLES;
+                mbar_expect_tx(&full_bar[p_stage], Cfg::STAGE_DOUBLES * 8);
+                const int k0 = p_kc * Cfg::BK;
+#pragma unroll
+                for (int kb = 0; kb < Cfg::KB; ++kb) {
+                    tma_load_2d(st + kb * BM * 4, &tmA, k0 + kb * 4, (int)(p_tile * BM), &full_bar[p_stage]);
+                    tma_load_2d(st + BM * Cfg::BK + kb * BN * 4, &tmB, k0 + kb * 4, p_nt * BN, &full_bar[p_stage]);
+                }
+                --p_left;
+                p_stage = (p_stage + 1 == STAGES) ? 0 : p_stage + 1;
+                if (++p_kc == a.KC) {
+                    p_kc = 0;
+                    if (++p_nt == a.NT) { p_nt = 0; p_tile += gridDim.x; }
+                }
+            }
+            return;
+        }
         if (p_left > 0 && !(a.dbg & 1)) {
             double* st = stages + p_stage * Cfg::STAGE_DOUBLES;
             const int koff = p_kc * Cfg::BK;
@@ -194,18 +256,20 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     const int fragB = BM * Cfg::BK + ((wn * Cfg::WN + lq) << 2) + lr4;
 
     int kc = 0, nt = 0, tl = 0, c_stage = 0;
+    unsigned c_phase = 0;
     for (long long q = 0; q < total; ++q) {
-        cp_async_wait<STAGES - 2>();
+        if (TMA) mbar_wait(&full_bar[c_stage], c_phase);
+        else cp_async_wait<STAGES - 2>();
         __syncthreads();
         issue();
 
         const double* St = stages + c_stage * Cfg::STAGE_DOUBLES;
-        c_stage = (c_stage + 1 == STAGES) ? 0 : c_stage + 1;
+        if (++c_stage == STAGES) { c_stage = 0; c_phase ^= 1; }
 #pragma unroll
         for (int kb = 0; kb < Cfg::KB; ++kb) {
             double af[MI], bf[NI];
             // (row ^ kb) with row = base + 8*i + lq: only lq's low two bits change
-            const int swz = ((lq ^ kb) - lq) << 2;
+            const int swz = TMA ? 0 : ((lq ^ kb) - lq) << 2;   // TMA slabs are dense, cp.async slabs are XOR-swizzled
 #pragma unroll
             for (int i = 0; i < MI; ++i) af[i] = St[fragA + swz + ((kb * BM + i * 8) << 2)];
 #pragma unroll
@@ -559,6 +623,30 @@ static cudaEvent_t g_prof_ev[2] = {nullptr, nullptr};
 static double g_prof_ms = 0.0;
 static long long g_prof_launches = 0;
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency,
+// so the library still loads on a machine without a driver).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static int make_tensor_map_2d(CUtensorMap* map, const double* base, unsigned long long cols, unsigned long long rows,
+                              unsigned box_cols, unsigned box_rows) {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) return 1;
+        fn = (EncodeTiledFn)p;
+    }
+    cuuint64_t gdim[2] = {cols, rows};
+    cuuint64_t gstride[1] = {cols * sizeof(double)};
+    cuuint32_t box[2] = {box_cols, box_rows > 256 ? 256u : box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)base, gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? 0 : 1;
+}
+
 template <class Cfg>
 static int launch_assign(AssignArgs a, cudaStream_t stream) {
     a.num_tiles = (int)((a.n + Cfg::BM - 1) / Cfg::BM);
@@ -571,27 +659,42 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
         if (!g_prof_ev[0]) { SQ_CUDA(cudaEventCreate(&g_prof_ev[0])); SQ_CUDA(cudaEventCreate(&g_prof_ev[1])); }
         SQ_CUDA(cudaEventRecord(g_prof_ev[0], stream));
     }
+    // TMA path: tensor maps over X [n, d] and C [k, d] with a box of {4 doubles, rows}
+    CUtensorMap tmA, tmB;
+    memset(&tmA, 0, sizeof(tmA));
+    memset(&tmB, 0, sizeof(tmB));
+    bool use_tma = vec16 && !getenv("SQ_ASSIGN_NO_TMA") && !(a.dbg & 1);
+    if (use_tma) {
+        int r1 = make_tensor_map_2d(&tmA, a.X, (unsigned long long)a.d, (unsigned long long)a.n, 4, Cfg::BM);
+        int r2 = make_tensor_map_2d(&tmB, a.C, (unsigned long long)a.d, (unsigned long long)a.k, 4, Cfg::BN);
+        if (r1 || r2) use_tma = false;  // driver without the encoder: cp.async path
+    }
+    smem += Cfg::STAGES * sizeof(unsigned long long);
     // persistent grid: one CTA per resident slot, tiles handed out by static striding
-#define SQ_LAUNCH_ASSIGN(V, M)                                                                                       \
+#define SQ_LAUNCH_ASSIGN(V, M, T)                                                                                     \
     do {                                                                                                            \
-        SQ_CUDA(cudaFuncSetAttribute(qmeans_assign_kernel<Cfg, V, M>, cudaFuncAttributeMaxDynamicSharedMemorySize,  \
+        SQ_CUDA(cudaFuncSetAttribute(qmeans_assign_kernel<Cfg, V, M, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                      (int)smem));                                                                   \
         int per_sm = 1;                                                                                             \
-        SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, qmeans_assign_kernel<Cfg, V, M>,             \
+        SQ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, qmeans_assign_kernel<Cfg, V, M, T>,          \
                                                               Cfg::THREADS, smem));                                 \
         if (per_sm < 1) per_sm = 1;                                                                                 \
         int grid = device_sm_count() * per_sm;                                                                      \
         if (grid > a.num_tiles) grid = a.num_tiles;                                                                 \
-        qmeans_assign_kernel<Cfg, V, M><<<grid, Cfg::THREADS, smem, stream>>>(a);                                   \
+        qmeans_assign_kernel<Cfg, V, M, T><<<grid, Cfg::THREADS, smem, stream>>>(a, tmA, tmB);                      \
     } while (0)
-    if (vec16) {
-        if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT);
-        else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW);
-        else SQ_LAUNCH_ASSIGN(true, MODE_IPE);
+    if (use_tma) {
+        if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT, true);
+        else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW, true);
+        else SQ_LAUNCH_ASSIGN(true, MODE_IPE, true);
+    } else if (vec16) {
+        if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT, false);
+        else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW, false);
+        else SQ_LAUNCH_ASSIGN(true, MODE_IPE, false);
     } else {
-        if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(false, MODE_EXACT);
-        else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(false, MODE_WINDOW);
-        else SQ_LAUNCH_ASSIGN(false, MODE_IPE);
+        if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(false, MODE_EXACT, false);
+        else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(false, MODE_WINDOW, false);
+        else SQ_LAUNCH_ASSIGN(false, MODE_IPE, false);
     }
 #undef SQ_LAUNCH_ASSIGN
     if (g_prof_on) {
