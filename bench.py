@@ -187,7 +187,7 @@ def run_reference_arm(args):
 def run_b200(args):
     import torch
     import torch.distributed as dist
-    from sqlearn import QuantumUtility as Q
+    from sqlearn.QuantumUtility import Utility as Q
     from sqlearn import _cabi
     from sqlearn.cluster import qMeans_
     from sqlearn.cluster import _dmeans as D
@@ -201,6 +201,8 @@ def run_b200(args):
     device = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=device)
     assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
 
