@@ -157,6 +157,13 @@ int sq_mu_norms(const double* X, long long n, int d, const double* exp_row_host,
 size_t sq_gram_workspace_bytes(long long n, int d);
 int sq_gram_centered(const double* X, long long n, int d, const double* mean, double* out_gram, void* ws,
                      size_t ws_bytes, void* stream);
+/* svd_flip's decision data (sklearn/utils/extmath.py:552-557, called at _qPCA.py:583) without
+ * materialising U: for every right singular vector v_j (rows of Vt [r,d]) the row i that
+ * maximises |x_i.v_j - mu_v[j]| over this rank's rows.  out_key[j] = bits(|y|) with bit 0
+ * replaced by the sign of y (1 = negative); combine ranks with max.  mu_v[j] = mean.v_j
+ * (pass zeros for centred X).                                                            */
+int sq_project_absmax(const double* X, long long n, int d, const double* Vt, int r, const double* mu_v,
+                      unsigned long long* out_key, void* stream);
 /* column sums of X (np.mean(X, axis=0) * n: _qPCA.py:578, _dmeans.py:1264) */
 size_t sq_col_sums_workspace_bytes(long long n, int d);
 int sq_col_sums(const double* X, long long n, int d, double* out, void* ws, size_t ws_bytes, void* stream);

@@ -85,3 +85,48 @@ def seed_everything(util, s):
                                               if not k.startswith("__")})
     util.np.random.RandomState = lambda *a, **k: rs
     return rs
+
+
+def load_qpca(util=None):
+    """Class ``qPCA`` of the reference (decomposition/_qPCA.py), AST-extracted and exec'd over a
+    minimal stand-in for ``_BasePCA`` (only _validate_data and the transform pair, restated
+    from decomposition/_base.py:97-164) and the installed scikit-learn's svd_flip/stable_cumsum."""
+    import numbers
+    from math import log, sqrt
+    from scipy import linalg
+    from scipy.sparse import issparse
+    from sklearn.utils.extmath import stable_cumsum, svd_flip
+    util = util or load_utility()
+    path = os.path.join(REF, "sklearn", "decomposition", "_qPCA.py")
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        tree = ast.parse(open(path).read())
+    keep = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "qPCA"]
+    for node in ast.walk(keep[0]):      # the class decorates __init__ with a sklearn-internal helper
+        if isinstance(node, ast.FunctionDef):
+            node.decorator_list = []
+
+    class _BasePCA:
+        def _validate_data(self, X, dtype=None, ensure_2d=True, copy=False, reset=True):
+            return np.array(X, dtype=np.float64, copy=True) if copy else np.asarray(X, dtype=np.float64)
+
+        def transform(self, X, use_classical_components=True):
+            X = np.asarray(X, dtype=np.float64)
+            if self.mean_ is not None:
+                X = X - self.mean_
+            comp = self.components_ if use_classical_components else self.estimate_right_sv
+            Xt = np.dot(X, comp.T)
+            if self.whiten:
+                Xt /= np.sqrt(self.explained_variance_ if use_classical_components else self.factor_score_estimation)
+            return Xt
+
+        def inverse_transform(self, X, use_classical_components=True):
+            comp = self.components_ if use_classical_components else self.estimate_right_sv
+            return np.dot(X, comp) + self.mean_
+
+    ns = {k: getattr(util, k) for k in dir(util) if not k.startswith("__")}
+    ns.update(np=np, linalg=linalg, issparse=issparse, svd_flip=svd_flip, stable_cumsum=stable_cumsum, log=log,
+              sqrt=sqrt, numbers=numbers, warnings=warnings, random=random, _BasePCA=_BasePCA,
+              check_is_fitted=lambda *a, **k: None, _infer_dimension=None)
+    exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
+    return ns["qPCA"]

@@ -35,7 +35,7 @@
 
 namespace sq {
 
-enum AssignMode { MODE_EXACT = 0, MODE_WINDOW = 1, MODE_IPE = 2 };
+enum AssignMode { MODE_EXACT = 0, MODE_WINDOW = 1, MODE_IPE = 2, MODE_COLABS = 3 };
 
 struct AssignArgs {
     const double* X;       // [n, d]
@@ -48,6 +48,7 @@ struct AssignArgs {
     double* rowmin_out;    // [n]   optional raw min (EXACT)
     int* flag_count;       // [1]   number of near-tie rows
     int* flag_rows;        // [n]   their indices
+    unsigned long long* colkey;  // [k] MODE_COLABS: max over rows of (bits(|y|) with the sign of y in bit 0)
     long long n;
     int d, k;
     int num_tiles;         // ceil(n / BM)
@@ -251,6 +252,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
 #pragma unroll
         for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
+    // MODE_COLABS keeps, per owned column, the largest |x.v - mu.v| seen over all of this CTA's tiles
+    unsigned long long colbest[NI][2];
+#pragma unroll
+    for (int j = 0; j < NI; ++j) colbest[j][0] = colbest[j][1] = 0ull;
+
     // fragment offsets inside a stage (doubles); kb only permutes rows inside aligned groups of 4
     const int fragA = ((wm * Cfg::WM + lq) << 2) + lr4;
     const int fragB = BM * Cfg::BK + ((wn * Cfg::WN + lq) << 2) + lr4;
@@ -286,6 +292,26 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
             for (int i = 0; i < MI; ++i)
 #pragma unroll
                 for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+        } else if (kc == a.KC - 1 && MODE == MODE_COLABS) {
+            // column-wise |max| of Y = X V^T - mu V^T (svd_flip's arg-max over all rows); NT must be 1
+            const long long tile = (long long)blockIdx.x + (long long)tl * gridDim.x;
+            const long long r0 = tile * BM;
+            const int colbase = wn * Cfg::WN + lr4 * 2;
+#pragma unroll
+            for (int j = 0; j < NI; ++j) {
+                const double2 mv = *reinterpret_cast<const double2*>(cn_s + colbase + j * 8);
+#pragma unroll
+                for (int i = 0; i < MI; ++i) {
+                    if (r0 + wm * Cfg::WM + i * 8 + lq < a.n) {
+                        double y0 = acc[i][j][0] - mv.x, y1 = acc[i][j][1] - mv.y;
+                        unsigned long long k0 = ((unsigned long long)__double_as_longlong(fabs(y0)) & ~1ull) | (y0 < 0.0 ? 1ull : 0ull);
+                        unsigned long long k1 = ((unsigned long long)__double_as_longlong(fabs(y1)) & ~1ull) | (y1 < 0.0 ? 1ull : 0ull);
+                        colbest[j][0] = k0 > colbest[j][0] ? k0 : colbest[j][0];
+                        colbest[j][1] = k1 > colbest[j][1] ? k1 : colbest[j][1];
+                    }
+                    acc[i][j][0] = acc[i][j][1] = 0.0;
+                }
+            }
         } else if (kc == a.KC - 1) {
             // ------------------------------ epilogue ------------------------------
             // v = |c|^2 - 2 x.c per element; the row minimum is found first, then the set of
@@ -459,6 +485,21 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
         if (++kc == a.KC) { kc = 0; if (++nt == a.NT) { nt = 0; ++tl; } }
     }
     cp_async_wait<0>();
+    if (MODE == MODE_COLABS) {
+#pragma unroll
+        for (int j = 0; j < NI; ++j)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                unsigned long long v = colbest[j][e];
+#pragma unroll
+                for (int o = 4; o < 32; o <<= 1) {
+                    unsigned long long w = __shfl_xor_sync(0xffffffffu, v, o);
+                    v = w > v ? w : v;
+                }
+                int col = wn * Cfg::WN + lr4 * 2 + j * 8 + e;
+                if (lq == 0 && col < a.k) atomicMax(&a.colkey[col], v);
+            }
+    }
 }
 
 // ---- near-tie rows: the reference's own arithmetic ---------------------------
@@ -686,15 +727,18 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
     if (use_tma) {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT, true);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW, true);
-        else SQ_LAUNCH_ASSIGN(true, MODE_IPE, true);
+        else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(true, MODE_IPE, true);
+        else SQ_LAUNCH_ASSIGN(true, MODE_COLABS, true);
     } else if (vec16) {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT, false);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW, false);
-        else SQ_LAUNCH_ASSIGN(true, MODE_IPE, false);
+        else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(true, MODE_IPE, false);
+        else SQ_LAUNCH_ASSIGN(true, MODE_COLABS, false);
     } else {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(false, MODE_EXACT, false);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(false, MODE_WINDOW, false);
-        else SQ_LAUNCH_ASSIGN(false, MODE_IPE, false);
+        else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(false, MODE_IPE, false);
+        else SQ_LAUNCH_ASSIGN(false, MODE_COLABS, false);
     }
 #undef SQ_LAUNCH_ASSIGN
     if (g_prof_on) {
@@ -872,4 +916,27 @@ extern "C" int sq_qmeans_assign_noalloc(const double* X, const double* xnorm, lo
     // everything else in the scratch is written before it is read.
     return sq_qmeans_assign(X, xnorm, n, d, C, k, mode, delta, seed, offset, labels, mindist, inertia, n_fixed,
                             scratch, SQ_NOALLOC_SCRATCH_BYTES, stream_);
+}
+
+// ---------------------------------------------------------------------------
+// K5: which row carries the largest |u_ij| of every left singular vector, and its sign
+// ---------------------------------------------------------------------------
+extern "C" int sq_project_absmax(const double* X, long long n, int d, const double* Vt, int r, const double* mu_v,
+                                 unsigned long long* out_key, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(X && Vt && mu_v && out_key, "sq_project_absmax: null pointer");
+    SQ_REQUIRE(n >= 1 && n < 2147483647LL && d >= 1 && r >= 1, "sq_project_absmax: bad shape n=%lld d=%d r=%d", n, d, r);
+    SQ_CUDA(cudaMemsetAsync(out_key, 0, (size_t)r * sizeof(unsigned long long), stream));
+    // the columns are swept in blocks of at most 256 (one centroid tile per launch)
+    for (int c0 = 0; c0 < r; c0 += 256) {
+        int rc = r - c0 < 256 ? r - c0 : 256;
+        AssignArgs a;
+        memset(&a, 0, sizeof(a));
+        a.X = X; a.C = Vt + (long long)c0 * d; a.cnorm = mu_v + c0; a.colkey = out_key + c0;
+        a.n = n; a.d = d; a.k = rc; a.mode = MODE_COLABS;
+        int bn = 0;
+        int rcode = dispatch_assign(a, stream, &bn);
+        if (rcode) return rcode;
+    }
+    return SQ_OK;
 }

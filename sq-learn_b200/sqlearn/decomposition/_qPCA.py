@@ -1,0 +1,513 @@
+"""Quantum PCA on a B200 (mirror of the reference's sklearn/decomposition/_qPCA.py).
+
+Same constructor, ``fit`` / ``transform`` keyword arguments and fitted attributes as the
+reference class ``qPCA``.  What runs where:
+  * singular values / right singular vectors: the reference takes a LAPACK SVD of the
+    centred data (_qPCA.py:578-583); here the centred Gram matrix is formed on the fp64
+    tensor cores (K4) and only the d x d symmetric eigenproblem goes to cuSOLVER.  sigma =
+    sqrt(lambda); relative error of sigma_i ~ eps_mach * (sigma_1/sigma_i)^2.
+  * svd_flip's signs need arg-max |U[:, j]| over all rows: K5 streams X once more through
+    the tensor cores without materialising U.
+  * best_mu over the 11-point grid: K6; singular-value estimation (consistent phase
+    estimation): K7; tomography of the singular vectors and of the projected rows: K1.
+Quirks kept on purpose: ``left_sv`` is the first n_components ROWS of U (_qPCA.py:631);
+tomography returns estimates of the normalised vectors.  Differences: the matplotlib /
+MATLAB plots are left out; 'arpack' / 'randomized' solvers (purely classical in the
+reference) are served by the full solver; ``condition_number_estimation`` and
+``fit_transform`` implement their evident intent (the reference passes keyword names
+that do not exist, _qPCA.py:937-945, :472-475).
+"""
+import numbers
+import random
+import warnings
+from math import log, sqrt
+
+import numpy as np
+import torch
+
+from .. import _cabi
+from .. import _device as dv
+from ..QuantumUtility import Utility as qu
+from ..QuantumUtility.Utility import (QuantumState, amplitude_estimation, estimate_wald, tomography,
+                                      unwrap_phase_est_arguments, wrapper_phase_est_arguments)
+from ._base import _BasePCA
+
+
+def _cpe(thetas, epsilon, gamma):
+    """consistent_phase_estimation for an array of phases (one kernel launch)."""
+    return qu._consistent_phase_estimation_batch(np.asarray(thetas, dtype=np.float64), epsilon, gamma)
+
+
+class qPCA(_BasePCA):
+    """Quantum principal component analysis (reference: _qPCA.py:113-1315)."""
+
+    def __init__(self, n_components=None, *, copy=True, whiten=False, svd_solver='auto', tol=0.0,
+                 iterated_power='auto', random_state=None, name=None):
+        self.n_components = n_components
+        self.copy = copy
+        self.whiten = whiten
+        self.svd_solver = svd_solver
+        self.tol = tol
+        self.iterated_power = iterated_power
+        self.random_state = random_state
+        self.name = name
+        if random_state:
+            random.seed(random_state)
+            qu.seed(random_state)          # the reference's draws come from `random` (_qPCA.py:353-354)
+        self.quantum_runtime_container = []
+
+    # ------------------------------------------------------------------ fit
+    def fit(self, X, y=None, quantum_retained_variance=False, eps=0, theta_major=0, theta_minor=0, eta=0,
+            theta_estimate=False, use_computed_qcomponents=False, eps_theta=0, p=0, estimate_all=False, delta=0,
+            true_tomography=True, fs_ratio_estimation=False, norm='L2', stop_when_reached_accuracy=False,
+            incremental_measure=False, faster_measure_increment=0, check_sv_uniform_distribution=False,
+            spectral_norm_est=False, condition_number_est=False, estimate_least_k=False):
+        """Fit the model with X (reference: _qPCA.py:357-465; same keyword arguments)."""
+        if quantum_retained_variance:
+            if eps <= 0:
+                raise ValueError("eps must be > 0")
+            if theta_major <= 0 and theta_estimate == False:  # noqa: E712
+                raise ValueError("theta must be > 0")
+        if theta_estimate:
+            if p <= 0 and not isinstance(self.n_components, int):
+                raise ValueError("p must be > 0")
+        self._fit(X, quantum_retained_variance=quantum_retained_variance, eps=eps, theta_major=theta_major,
+                  theta_minor=theta_minor, eta=eta, theta_estimate=theta_estimate,
+                  use_computed_qcomponents=use_computed_qcomponents, eps_theta=eps_theta, ret_var=p,
+                  estimate_all=estimate_all, delta=delta, true_tomography=true_tomography,
+                  fs_ratio_estimation=fs_ratio_estimation, norm=norm,
+                  stop_when_reached_accuracy=stop_when_reached_accuracy, incremental_measure=incremental_measure,
+                  faster_measure_increment=faster_measure_increment,
+                  check_sv_uniform_distribution=check_sv_uniform_distribution, spectral_norm_est=spectral_norm_est,
+                  condition_number_est=condition_number_est, estimate_least_k=estimate_least_k)
+        return self
+
+    def fit_transform(self, X, y=None, quantum_retained_variance=False, eps=0, theta=0, eta=0, theta_estimate=False,
+                      use_computed_qcomponents=False, eps_theta=0, ret_var=0, estimate_all=False, delta=0,
+                      error=False):
+        """U * S (or U * sqrt(n-1) when whitening) divided by the spectral norm (intent of _qPCA.py:467-483)."""
+        self.fit(X, quantum_retained_variance=quantum_retained_variance, eps=eps, theta_major=theta, eta=eta,
+                 theta_estimate=theta_estimate, use_computed_qcomponents=use_computed_qcomponents,
+                 eps_theta=eps_theta, p=ret_var, estimate_all=estimate_all, delta=delta)
+        Y = self._project(np.asarray(X, dtype=np.float64), self.components_).cpu().numpy()   # = U * S
+        if self.whiten:
+            Y = Y / self.singular_values_ * sqrt(np.asarray(X).shape[0] - 1)
+        return Y / self.spectral_norm
+
+    def _fit(self, X, quantum_retained_variance, eps, theta_major, theta_minor, eta, theta_estimate,
+             use_computed_qcomponents, eps_theta, ret_var, estimate_all, delta, true_tomography,
+             fs_ratio_estimation, norm, stop_when_reached_accuracy, incremental_measure, faster_measure_increment,
+             check_sv_uniform_distribution, spectral_norm_est, condition_number_est, estimate_least_k):
+        """Store the quantum parameters and dispatch on the solver (reference: _qPCA.py:485-555)."""
+        self.delta = delta
+        self.eps_theta = eps_theta
+        self.eps = eps
+        self.theta_estimate = theta_estimate
+        self.estimate_all = estimate_all
+        self.estimate_least_k = estimate_least_k
+        self.fs_ratio_estimation = fs_ratio_estimation
+        self.quantum_retained_variance = quantum_retained_variance
+        self.eta = eta
+        self.theta_major = theta_major
+        self.theta_minor = theta_minor
+        self.ret_var = ret_var
+        self.tomography_norm = norm
+        self.true_tomography = true_tomography
+        self.stop_when_reached_accuracy = stop_when_reached_accuracy
+        self.incremental_measure = incremental_measure
+        self.faster_measure_increment = faster_measure_increment
+        self.check_sv_uniform_distribution = check_sv_uniform_distribution
+        self.spectral_norm_est = spectral_norm_est
+        self.condition_number_est = condition_number_est
+        if hasattr(X, "toarray") and not isinstance(X, np.ndarray):
+            raise TypeError('PCA does not support sparse input. See TruncatedSVD for a possible alternative.')
+        X = np.array(X, dtype=np.float64, order='C', copy=True) if self.copy else \
+            np.ascontiguousarray(X, dtype=np.float64)
+        if X.ndim != 2:
+            raise ValueError("Expected 2D array, got array with shape %r" % (X.shape,))
+        if self.n_components is None:
+            self.n_components_flag = False
+            n_components = min(X.shape) if self.svd_solver != 'arpack' else min(X.shape) - 1
+        else:
+            self.n_components_flag = True
+            n_components = self.n_components
+        self._fit_svd_solver = self.svd_solver
+        if self._fit_svd_solver == 'auto':
+            if max(X.shape) <= 500 or n_components == 'mle':
+                self._fit_svd_solver = 'full'
+            elif n_components >= 1 and n_components < .8 * min(X.shape):
+                self._fit_svd_solver = 'randomized'
+            else:
+                self._fit_svd_solver = 'full'
+        if self._fit_svd_solver == 'full':
+            return self._fit_full(X, n_components=n_components)
+        elif self._fit_svd_solver in ['arpack', 'randomized']:
+            warnings.warn('Attention! This computational path is purely classic!')
+            return self._fit_full(X, n_components=n_components, classic_only=True)
+        raise ValueError("Unrecognized svd_solver='{0}'".format(self._fit_svd_solver))
+
+    # ------------------------------------------------------------------ spectral decomposition on the device
+    def _device_svd(self, X):
+        """mean, singular values, right singular vectors (svd_flip'ed), and the first rows of U.
+
+        Returns (mean [d], S [r], Vt [r, d], U_rows(k) callable, frob_norm, Xd centred on the device)."""
+        dev = dv.require_cuda()
+        n, d = X.shape
+        Xd = dv.to_device(X, pin=False)
+        nb = _cabi.lib.sq_col_sums_workspace_bytes(n, d)
+        ws = dv.workspace(nb)
+        csum = dv.empty((d,))
+        _cabi.check(_cabi.lib.sq_col_sums(dv.ptr(Xd), n, d, dv.ptr(csum), dv.ptr(ws), nb, dv.stream_ptr()), "sq_col_sums")
+        cnt = torch.tensor([float(n)], dtype=torch.float64, device=dev)
+        dv.all_reduce_sum(csum)
+        dv.all_reduce_sum(cnt)
+        n_glob = int(cnt.item())
+        mean = csum / float(n_glob)
+        _cabi.check(_cabi.lib.sq_sub_rowvec(dv.ptr(Xd), dv.ptr(mean), n, d, dv.ptr(Xd), dv.stream_ptr()), "sq_sub_rowvec")
+        G = dv.empty((d, d))
+        nb = _cabi.lib.sq_gram_workspace_bytes(n, d)
+        ws = dv.workspace(nb)
+        _cabi.check(_cabi.lib.sq_gram_centered(dv.ptr(Xd), n, d, None, dv.ptr(G), dv.ptr(ws), nb, dv.stream_ptr()),
+                    "sq_gram_centered")
+        dv.all_reduce_sum(G)
+        lam, V = torch.linalg.eigh(G)                      # ascending; cuSOLVER, d x d (off the hot path)
+        r = min(n_glob, d)
+        lam = torch.flip(lam, dims=[0])[:r]
+        Vt = torch.flip(V, dims=[1]).T[:r].contiguous()    # rows = right singular vectors, descending sigma
+        S = torch.sqrt(torch.clamp(lam, min=0.0))
+        # svd_flip (u-based): sign of the entry of largest |.| in every column of U = X V / S
+        keys = torch.zeros((r,), dtype=torch.int64, device=dev)
+        zeros = torch.zeros((r,), dtype=torch.float64, device=dev)
+        _cabi.check(_cabi.lib.sq_project_absmax(dv.ptr(Xd), n, d, dv.ptr(Vt), r, dv.ptr(zeros), dv.ptr(keys),
+                                                dv.stream_ptr()), "sq_project_absmax")
+        rank, world = dv.dist_info()
+        if world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(keys, op=dist.ReduceOp.MAX)
+        signs = 1.0 - 2.0 * (keys & 1).to(torch.float64)
+        signs = torch.where(keys == 0, torch.ones_like(signs), signs)      # all-zero column: np.sign(0) would zero it
+        Vt = Vt * signs[:, None]
+        frob = float(torch.sqrt(torch.clamp(torch.trace(G), min=0.0)).item())
+        return mean, S, Vt, frob, Xd, n_glob
+
+    def _fit_full(self, X, n_components, classic_only=False):
+        """Fit by full decomposition of the centred data (reference: _qPCA.py:557-676)."""
+        n_samples, n_features = X.shape
+        if n_components == 'mle':
+            if n_samples < n_features:
+                raise ValueError("n_components='mle' is only supported if n_samples >= n_features")
+            raise NotImplementedError("n_components='mle' (Minka's dimension inference) is outside the quantum path")
+        elif not 0 <= n_components <= min(n_samples, n_features):
+            raise ValueError("n_components=%r must be between 0 and min(n_samples, n_features)=%r with "
+                             "svd_solver='full'" % (n_components, min(n_samples, n_features)))
+        elif n_components >= 1:
+            if not isinstance(n_components, numbers.Integral):
+                raise ValueError("n_components=%r must be of type int when greater than or equal to 1, "
+                                 "was of type=%r" % (n_components, type(n_components)))
+        mean, S_d, Vt_d, frob, Xd, n_glob = self._device_svd(X)
+        self.mean_ = mean.cpu().numpy()
+        S = S_d.cpu().numpy()
+        Vt = Vt_d.cpu().numpy()
+        components_ = Vt
+        explained_variance_ = (S ** 2) / (n_glob - 1)
+        total_var = explained_variance_.sum()
+        explained_variance_ratio_ = explained_variance_ / total_var
+        singular_values_ = S.copy()
+        if 0 < n_components < 1.0:
+            ratio_cumsum = np.cumsum(explained_variance_ratio_, dtype=np.float64)
+            n_components = np.searchsorted(ratio_cumsum, n_components, side='right') + 1
+        if n_components < min(n_features, n_samples):
+            self.noise_variance_ = explained_variance_[n_components:].mean()
+        else:
+            self.noise_variance_ = 0.
+        self.n_samples_, self.n_features_ = n_glob, n_features
+        if isinstance(self.ret_var, int):
+            self.ret_var = np.sum(explained_variance_ratio_[:self.ret_var])
+        if self.n_components_flag == False:  # noqa: E712
+            n_components = self.ret_variance(explained_variance_ratio_, self.ret_var)
+            self.components_retained_ = n_components
+        self.components_ = components_[:n_components]
+        self.n_components_ = n_components
+        self.all_components = components_
+        self.explained_variance_all = explained_variance_
+        self.explained_variance_ratio_all = explained_variance_ratio_
+        self.explained_variance_ = explained_variance_[:n_components]
+        self.explained_variance_ratio_ = explained_variance_ratio_[:n_components]
+        self.singular_values_ = singular_values_[:n_components]
+        # first n_components ROWS of U (reference :631), from this rank's first rows
+        k_rows = min(int(n_components), Xd.shape[0])
+        U_rows = torch.matmul(Xd[:k_rows], Vt_d.T) / torch.clamp(S_d, min=1e-300)[None, :]
+        self.left_sv = U_rows.cpu().numpy()
+        self.spectral_norm = self.singular_values_[0]
+        self.frob_norm = frob
+        self._frob_sq = frob ** 2
+        self.norm_muA, self.muA = qu.best_mu(Xd, start=0, step=0.1)
+        if classic_only:
+            return None, S, Vt
+        if self.condition_number_est:
+            self.est_cond_number = self.condition_number_estimation(epsilon=self.eps, delta=self.delta)
+        if self.spectral_norm_est:
+            self.est_spectral_norm = self.spectral_norm_estimation(epsilon=self.eps, delta=self.delta)
+        if self.theta_estimate:
+            self.est_theta = self.estimate_theta(epsilon=self.eps_theta, eta=self.eta, p=self.ret_var)
+        if self.quantum_retained_variance:
+            self.p = self.quantum_factor_score_ratio_sum(eps=self.eps, theta=self.theta_major, eta=self.eta)
+        kw = dict(true_tomography=self.true_tomography, norm=self.tomography_norm,
+                  stop_when_reached_accuracy=self.stop_when_reached_accuracy,
+                  incremental_measure=self.incremental_measure,
+                  faster_measure_increment=self.faster_measure_increment,
+                  check_sv_uniform_distribution=self.check_sv_uniform_distribution)
+        if self.estimate_least_k:
+            (self.estimate_least_right_sv, self.estimate_least_left_sv, self.estimate_least_s_values,
+             self.estimate_least_fs, self.estimate_least_fs_ratio) = \
+                self.least_k_sv_extractors(X=None, delta=self.delta, eps=self.eps, theta=self.theta_minor, **kw)
+        if self.estimate_all:
+            (self.estimate_right_sv, self.estimate_left_sv, self.estimate_s_values, self.estimate_fs,
+             self.estimate_fs_ratio) = \
+                self.topk_sv_extractors(X=None, delta=self.delta, eps=self.eps, theta=self.theta_major, **kw)
+        return None, S, Vt
+
+    # ------------------------------------------------------------------ singular value estimation
+    def _estimate_singular_values(self, sv, scale, eps_scaled):
+        """sigma -> theta -> consistent PE -> sigma~ for an array of singular values (the pattern of
+        _qPCA.py:1031-1037): theta = 2 acos(sigma/scale) / (eps_scaled + pi)."""
+        theta = np.array([wrapper_phase_est_arguments(s) / (eps_scaled + np.pi) for s in np.clip(sv / scale, -1, 1)])
+        est = _cpe(theta, eps_scaled, 1 - 1 / self.n_features_)
+        return np.array([unwrap_phase_est_arguments(th, eps=eps_scaled) for th in est])
+
+    def topk_sv_extractors(self, X, delta, eps, theta, true_tomography, norm, stop_when_reached_accuracy,
+                           incremental_measure, faster_measure_increment, check_sv_uniform_distribution):
+        """Theorem 11: estimates of the top singular values, vectors and factor scores
+        (reference: _qPCA.py:1025-1068)."""
+        if theta == 0:
+            theta = self.est_theta
+        est = self._estimate_singular_values(self.singular_values_, self.muA, eps / self.muA) * self.muA
+        sel = est >= theta
+        self.top_k_true_singular_value = self.singular_values_[sel]
+        singular_value_estimation = est[sel]
+        if check_sv_uniform_distribution:
+            warnings.warn("check_sv_uniform_distribution plots with matplotlib in the reference; ignored")
+        self.topk = len(singular_value_estimation)
+        self.topk_p = sum(self.top_k_true_singular_value ** 2) / sum(self.singular_values_ ** 2)
+        self.topk_right_singular_vectors = self.components_[sel]
+        self.topk_left_singular_vectors = self.left_sv[sel]
+        kw = dict(true_tomography=true_tomography, norm=norm, stop_when_reached_accuracy=stop_when_reached_accuracy,
+                  incremental_measure=incremental_measure, faster_measure_increment=faster_measure_increment)
+        right = tomography(self.topk_right_singular_vectors, delta, **kw)
+        left = tomography(self.topk_left_singular_vectors, delta, **kw)
+        fs = singular_value_estimation ** 2
+        fs_ratio = np.array([f / self._frob_sq for f in fs])
+        return right, left, singular_value_estimation, fs / (self.n_samples_ - 1), fs_ratio
+
+    def least_k_sv_extractors(self, X, delta, eps, theta, true_tomography, norm, stop_when_reached_accuracy,
+                              incremental_measure, faster_measure_increment, check_sv_uniform_distribution):
+        """Estimates of the smallest non-zero singular values and vectors (reference: _qPCA.py:1070-1121)."""
+        if theta == 0:
+            theta = self.least_theta
+        cut = np.where(np.isclose(self.singular_values_, 0))[0][0]     # IndexError without a zero value, as the reference
+        sv = self.singular_values_[:cut]
+        est = self._estimate_singular_values(sv, self.muA, eps / self.muA) * self.muA
+        sel = est < theta
+        self.least_k_true_singular_value = sv[sel]
+        singular_value_estimation = est[sel]
+        if check_sv_uniform_distribution:
+            warnings.warn("check_sv_uniform_distribution plots with matplotlib in the reference; ignored")
+        self.least_k = len(singular_value_estimation)
+        self.least_k_p = sum(self.least_k_true_singular_value ** 2) / sum(self.singular_values_ ** 2)
+        self.leastk_right_singular_vectors = self.components_[:cut][sel]
+        self.leastk_left_singular_vectors = self.left_sv[:cut][sel]
+        kw = dict(true_tomography=true_tomography, norm=norm, stop_when_reached_accuracy=stop_when_reached_accuracy,
+                  incremental_measure=incremental_measure, faster_measure_increment=faster_measure_increment)
+        right = tomography(self.leastk_right_singular_vectors, delta, **kw)
+        left = tomography(self.leastk_left_singular_vectors, delta, **kw)
+        fs = singular_value_estimation ** 2
+        fs_ratio = np.array([f / self._frob_sq for f in fs])
+        return right, left, singular_value_estimation, fs / (self.n_samples_ - 1), fs_ratio
+
+    def quantum_factor_score_ratio_sum(self, eps, theta, eta):
+        """Theorem 9: amplitude estimate of the variance retained above theta (reference: _qPCA.py:982-999)."""
+        if not theta:
+            theta = self.est_theta
+        est = self._estimate_singular_values(self.singular_values_, self.muA, eps)
+        selected = self.singular_values_[est >= theta]
+        p = sum(selected ** 2) / sum(self.singular_values_ ** 2)
+        return amplitude_estimation(a=p, epsilon=eta)
+
+    def estimate_theta(self, epsilon, eta, p):
+        """Theorem 10: binary search for the threshold retaining variance p (reference: _qPCA.py:1002-1022;
+        the reference's progress prints are dropped)."""
+        lo, hi = 0, 1
+        if np.abs(lo - p) <= eta:
+            return self.muA
+        if np.abs(hi - p) <= eta:
+            return 0
+        n_iterations = int(np.ceil((np.log(self.muA / epsilon))))
+        tau = (lo + hi) / 2
+        for _ in range(n_iterations):
+            p_est = self.quantum_factor_score_ratio_sum(eps=epsilon / self.muA, theta=tau, eta=eta / 2)
+            if np.abs(p_est - p) <= eta / 2:
+                return tau * self.muA
+            if p_est < p:
+                hi = tau
+            else:
+                lo = tau
+            tau = (hi + lo) / 2
+        raise ValueError("The binary search doesn't found any values")
+
+    def _binary_search_norm(self, epsilon, delta, smaller):
+        lo, hi = 0, 1
+        n_iterations = int(np.ceil((np.log(self.frob_norm / epsilon))))
+        tau = (lo + hi) / 2
+        for _ in range(n_iterations):
+            # the reference passes epsilon/frob_norm as the CPE accuracy and 1/epsilon as the wrap constant
+            theta = np.array([wrapper_phase_est_arguments(s) / ((1 / epsilon) + np.pi)
+                              for s in np.clip(self.singular_values_ / self.frob_norm, -1, 1)])
+            cp = _cpe(theta, epsilon / self.frob_norm, 1 - 1 / self.n_features_)
+            est = np.array([unwrap_phase_est_arguments(th, eps=1 / epsilon) for th in cp])
+            selected = self.singular_values_[est <= tau] if smaller else self.singular_values_[est >= tau]
+            eta = min(np.sum(np.square(selected)) / (self.frob_norm ** 2), 1)
+            eta_est = amplitude_estimation(a=eta, epsilon=delta)
+            if (eta_est == 1) if smaller else (eta_est == 0):
+                hi = tau
+            else:
+                lo = tau
+            tau = (hi + lo) / 2
+        return tau * self.frob_norm
+
+    def spectral_norm_estimation(self, epsilon, delta):
+        """Binary search for the spectral norm (reference: _qPCA.py:882-907)."""
+        return self._binary_search_norm(epsilon, delta, smaller=False)
+
+    def condition_number_estimation(self, epsilon, delta):
+        """Binary search from below (intent of _qPCA.py:909-961, whose calls use keyword names that do not
+        exist and raise TypeError in the reference)."""
+        return self._binary_search_norm(epsilon, delta, smaller=True)
+
+    # ------------------------------------------------------------------ transform
+    def transform(self, X, classic_transform=True, epsilon_delta=0, quantum_representation=False, norm='None', psi=0,
+                  true_tomography=True, use_classical_components=True):
+        """Classical projection, or a quantum representation of it (reference: _qPCA.py:773-843)."""
+        if classic_transform:
+            if epsilon_delta != 0 or quantum_representation or norm or psi != 0:
+                warnings.warn("Warning! You are using the classical transform, so the quantum parameter are useless.")
+            return super().transform(X)
+        X_final = super().transform(X, use_classical_components)
+        if use_classical_components == False:  # noqa: E712
+            return X_final
+        if quantum_representation:
+            assert (psi > 0 if norm != 'est_representation' else psi >= 0)
+            assert (epsilon_delta > 0)
+            result = self.compute_quantum_representation(X_final, psi=psi, epsilon_delta=epsilon_delta, type=norm,
+                                                         true_tomography=true_tomography)
+            return {'quantum_representation_results': result}
+
+    def inverse_transform(self, X, use_classical_components=True):
+        return super().inverse_transform(X, use_classical_components)
+
+    def compute_error(self, U, epsilon_delta, true_tomography):
+        """Row-wise tomography of the projected data and its Frobenius error (reference: _qPCA.py:848-857)."""
+        if true_tomography == False:  # noqa: E712
+            epsilon_delta = np.sqrt(self.n_components_) * (epsilon_delta)
+        A_sign = tomography(U, epsilon_delta, true_tomography=true_tomography)
+        f_norm = np.linalg.norm(U - A_sign)
+        return A_sign, epsilon_delta, f_norm
+
+    def compute_quantum_representation(self, X, psi, epsilon_delta, true_tomography, type='None'):
+        """The four representations of _qPCA.py:859-880."""
+        if type == 'est_representation':
+            return self.compute_error(X, epsilon_delta, true_tomography)
+        elif type == 'q_state':
+            Y_sign = tomography(X, psi, true_tomography=true_tomography)
+            f_norm = np.linalg.norm(Y_sign)
+            norm_Y = [np.linalg.norm(Y_sign[i, :], ord=2) / f_norm for i in range(len(Y_sign))]
+            Yi_ = [Y_sign[i, :] / f_norm for i in range(len(Y_sign))]
+            return QuantumState(registers=Yi_, amplitudes=norm_Y)
+        elif type == 'None':
+            return tomography(X, psi, true_tomography=true_tomography)
+        elif type == 'f_norm':
+            Y_sign = tomography(X, psi, true_tomography=true_tomography)
+            return Y_sign / np.linalg.norm(Y_sign)
+
+    # ------------------------------------------------------------------ classical leftovers of the class
+    def score_samples(self, X):
+        """Log-likelihood of each sample under the probabilistic PCA model (reference: _qPCA.py:753-764)."""
+        X = np.asarray(X, dtype=np.float64)
+        Xr = X - self.mean_
+        n_features = X.shape[1]
+        precision = self.get_precision()
+        log_like = -.5 * (Xr * (np.dot(Xr, precision))).sum(axis=1)
+        log_like -= .5 * (n_features * log(2. * np.pi) - np.linalg.slogdet(precision)[1])
+        return log_like
+
+    def score(self, X, y=None):
+        return np.mean(self.score_samples(X))
+
+    def ret_variance(self, explained_variance_ratio_, variance):
+        """Components needed to retain `variance` (reference: _qPCA.py:1228-1233)."""
+        ratio_cumsum = np.cumsum(explained_variance_ratio_, dtype=np.float64)
+        return np.searchsorted(ratio_cumsum, variance, side='right') + 1
+
+    def q_ret_variance(self, measurements, variance):
+        """Components needed, from sampled singular values (reference: _qPCA.py:1210-1226)."""
+        if isinstance(self.n_components, int):
+            return self.n_components
+        q_state = QuantumState(registers=self.scaled_singular_values, amplitudes=self.scaled_singular_values)
+        estimations = estimate_wald(q_state.measure(measurements))
+        sv = sorted(estimations.keys(), reverse=True)
+        dict_elem = np.array(list(map(estimations.get, sv)))
+        exp_var, i = 0, 0
+        while exp_var <= variance:
+            exp_var += dict_elem[i]
+            i += 1
+        return i
+
+    def accumulate_q_runtime(self, n_samples, n_features, estimate_components='all'):
+        """Quantum cost model of the steps that were run (reference: _qPCA.py:1123-1208)."""
+        self.theta = self.est_theta if self.theta_major == 0 else self.theta_major
+        out = self.quantum_runtime_container
+        if self.theta_estimate:
+            out.append((self.muA * np.log(self.muA / self.eps_theta) * np.log(n_samples * n_features)) /
+                       (self.eps_theta * self.eta))
+        if self.quantum_retained_variance:
+            out.append(self.muA / (self.eps * self.eta))
+        if self.estimate_all:
+            common = (self.spectral_norm * self.muA * self.topk * np.log(self.topk)) / \
+                     (self.theta * np.sqrt(self.topk_p) * self.eps)
+            if self.tomography_norm == 'L2':
+                left = (self.spectral_norm * self.muA * self.topk * np.log(self.topk) * n_samples *
+                        np.log(n_samples)) / (self.theta * np.sqrt(self.topk_p) * self.eps * self.delta ** 2)
+                right = ((self.spectral_norm / self.theta) * (1 / np.sqrt(self.topk_p)) * (self.muA / self.eps) *
+                         ((self.topk * np.log(self.topk) * n_features * np.log(n_features)) / (self.delta ** 2)))
+            else:
+                c = (self.spectral_norm * self.muA * self.topk) / (self.theta * self.eps * self.delta ** 2)
+                left = np.full(shape=np.shape(n_samples), fill_value=c)
+                right = np.full(shape=np.shape(n_features), fill_value=c)
+            out.append({'all': left + right, 'left_sv': left, 'right_sv': right}[estimate_components] + common)
+        if self.estimate_least_k:
+            nz = self.singular_values_[:(np.where(np.isclose(self.singular_values_, 0)))[0][0]]
+            if self.tomography_norm == 'L2':
+                left = ((self.theta_minor / nz[-1]) * (1 / np.sqrt(self.least_k_p)) * (self.muA / self.eps) *
+                        ((self.least_k * np.log(self.least_k) * n_samples * np.log(n_samples)) / (self.delta ** 2)))
+                right = ((self.theta_minor / nz[-2]) * (1 / np.sqrt(self.least_k_p)) * (self.muA / self.eps) *
+                         ((self.least_k * np.log(self.least_k) * n_features * np.log(n_features)) / (self.delta ** 2)))
+            else:
+                c = (self.spectral_norm * self.muA * self.least_k) / (self.theta_minor * self.eps * self.delta ** 2)
+                left = np.full(shape=np.shape(n_samples), fill_value=c)
+                right = np.full(shape=np.shape(n_features), fill_value=c)
+            tail = {'all': nz[-2], 'left_sv': nz[-1], 'right_sv': nz[-2]}[estimate_components]
+            out.append({'all': right + left, 'left_sv': left, 'right_sv': right}[estimate_components] +
+                       (self.theta_minor * self.muA * self.least_k) / (tail * np.sqrt(self.least_k_p) * self.eps))
+        return out
+
+    def runtime_comparison(self, n_samples, n_features, saveas, estimate_components='all', classic_runtime='classic'):
+        """Classical vs quantum cost grids (reference: _qPCA.py:1235-1315); the MATLAB plot is left out and
+        the two grids are returned instead."""
+        n, m = np.meshgrid(np.linspace(1, n_samples, dtype=np.int64, num=100),
+                           np.linspace(1, n_features, dtype=np.int64, num=100))
+        if classic_runtime == 'rand':
+            c_runtime = (n * m * np.log(self.components_retained_))
+        elif classic_runtime == 'classic':
+            c_runtime = n * m ** 2
+        q_runtime = self.accumulate_q_runtime(n_samples=n, n_features=m, estimate_components=estimate_components)
+        q_runtime = np.sum(q_runtime, axis=0) if len(q_runtime) > 1 else q_runtime[0]
+        return q_runtime, c_runtime

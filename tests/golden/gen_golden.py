@@ -176,3 +176,48 @@ st["ipe_y2"] = y2
 st["ipe2_draws_e0.25"] = np.sort([quiet(u.ipe, x, y2, 0.25) for _ in range(1500)])
 np.savez_compressed(os.path.join(HERE, "stochastic_reference.npz"), **st)
 print("golden fixtures written to", HERE)
+
+# ---------------------------------------------------------------- qPCA (reference class, AST-loaded)
+QP = refload.load_qpca(u)
+warnings.filterwarnings("ignore")
+qp = {}
+rs = np.random.RandomState(21)
+Xp = rs.randn(300, 12) @ np.diag(np.linspace(6, 0.5, 12)) @ rs.randn(12, 12) + rs.randn(12) * 3
+qp["X"] = Xp
+ref = quiet(lambda: QP(n_components=5, svd_solver='full').fit(Xp.copy()))
+for name in ("mean_", "components_", "singular_values_", "explained_variance_", "explained_variance_ratio_",
+             "left_sv", "noise_variance_", "spectral_norm", "frob_norm", "muA"):
+    qp[name] = np.asarray(getattr(ref, name))
+qp["norm_muA"] = np.asarray([ref.norm_muA])
+qp["transform"] = quiet(ref.transform, Xp[:40])
+# the stock-test anchor: a matrix with prescribed singular values (sklearn/decomposition/tests/test_pca.py:159-189)
+rs2 = np.random.RandomState(0)
+Xs = rs2.randn(100, 110)
+Us, _, Vs = np.linalg.svd(Xs - Xs.mean(axis=0), full_matrices=False)
+Xs_hat = (Us[:, :3] * np.array([3.142, 2.718, 1.0])) @ Vs[:3]
+qp["Xs_hat"] = Xs_hat
+qp["Xs_sv"] = quiet(lambda: QP(n_components=3, svd_solver='full').fit(Xs_hat.copy())).singular_values_
+# stochastic: estimated singular values, error of the estimated vectors, representation error
+theta = float(ref.singular_values_[3]) * 0.98
+est_sv, right_err, left_err, topk, frep = [], [], [], [], []
+for _ in range(60):
+    m = quiet(lambda: QP(n_components=5, svd_solver='full').fit(Xp.copy(), estimate_all=True, eps=0.5, delta=0.25,
+                                                                 theta_major=theta, true_tomography=True))
+    topk.append(m.topk)
+    est_sv.append(np.pad(m.estimate_s_values, (0, 5 - len(m.estimate_s_values)), constant_values=np.nan))
+    right_err.extend(np.linalg.norm(m.estimate_right_sv - m.topk_right_singular_vectors, axis=1))
+    lv = m.topk_left_singular_vectors
+    left_err.extend(np.linalg.norm(m.estimate_left_sv - lv / np.linalg.norm(lv, axis=1, keepdims=True), axis=1))
+    r = quiet(m.transform, Xp[:30], classic_transform=False, epsilon_delta=0.3, quantum_representation=True,
+              norm='est_representation')
+    Y = m.transform(Xp[:30]) if False else (Xp[:30] - m.mean_) @ m.components_.T
+    A = r['quantum_representation_results'][0]
+    frep.extend(np.linalg.norm(A - Y / np.linalg.norm(Y, axis=1, keepdims=True), axis=1))
+qp["theta"] = np.asarray([theta])
+qp["topk"] = np.asarray(topk)
+qp["est_sv"] = np.asarray(est_sv)
+qp["right_err"], qp["left_err"], qp["rep_err"] = np.sort(right_err), np.sort(left_err), np.sort(frep)
+p_est = [quiet(m.quantum_factor_score_ratio_sum, 0.05, theta / m.muA, 0.05) for _ in range(200)]
+qp["p_est"] = np.sort(p_est)
+np.savez_compressed(os.path.join(HERE, "qpca_reference.npz"), **qp)
+print("qPCA fixtures written")
