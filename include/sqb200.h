@@ -62,6 +62,15 @@ int sq_tomography_batched(const double* V, long long B, int d, double delta, int
                           unsigned long long vec_offset, double* est, double* n_used, double* err, double* trace,
                           int* attempts, void* stream);
 
+/* Same routine for any d up to 4M: vectors longer than sq_tomography_max_fused_dim() are cut into
+ * blocks that the whole grid works on, with scratch in (ws, ws_bytes) sized by
+ * sq_tomography_workspace_bytes (0 when d fits the fused path; B <= 65535 beyond it).      */
+size_t sq_tomography_workspace_bytes(long long B, int d);
+int sq_tomography_batched_ws(const double* V, long long B, int d, double delta, int norm_inf, int stop,
+                             const double* sched_host, int sched_len, unsigned long long seed,
+                             unsigned long long vec_offset, double* est, double* n_used, double* err, void* ws,
+                             size_t ws_bytes, void* stream);
+
 /* ---- q-means E-step ------------------------------------------------------ *
  * labels_estimation (sklearn/cluster/_dmeans.py:732-777) with ipe /
  * amplitude_estimation / median_evaluation (Utility.py:697-737, :442-531,

@@ -176,6 +176,196 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
     if (tid == 0) { a.n_used[b] = n_last; a.err[b] = err_last; if (a.attempts) a.attempts[b] = n_att; }
 }
 
+
+// ---------------------------------------------------------------------------
+// Long vectors (d > 4096): the same algorithm split over the grid.
+// A vector is cut into blocks of TB leaves.  Per attempt: block masses -> one CTA splits N over the
+// blocks (top tree) -> every block splits its share over its leaves in shared memory; twice (stage 1,
+// stage 2), then the error is reduced and the stop rule applied.  Scratch lives in the caller's
+// workspace; the stage-1 estimate P is parked in `est` between the two stages.
+// ---------------------------------------------------------------------------
+static const int TB = 1024;       // leaves per block
+static const int TB_LOG = 10;
+
+struct TomoBigArgs {
+    const double* V;
+    double* est;
+    double* n_used;
+    double* err;
+    const double* sumsq;   // [B] ||V||^2
+    double* bm_a;          // [B, nblk] stage-1 mass, then stage-2 '+' mass of every block
+    double* bm_b;          // [B, nblk] stage-2 '-' mass
+    double* bcnt;          // [B, nblk] measurements that fall in the block
+    double* errp;          // [B, nblk] per-block error partial
+    int* done;             // [B]
+    long long B;
+    int d, nblk, NB, logNB;
+    double N;
+    int at, norm_inf, stop;
+    double delta;
+    unsigned long long seed, vec_offset;
+};
+
+__device__ __forceinline__ double big_scale(double sumsq, bool& zero) {
+    double nrm = sqrt(sumsq);
+    zero = !(nrm > 0.0);
+    bool keep = fabs(nrm - 1.0) <= (1e-8 + 1e-2);
+    return keep ? 1.0 : nrm;   // divisor
+}
+
+__global__ void tomo_big_init_kernel(TomoBigArgs a) {
+    long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= a.B) return;
+    a.done[b] = (a.sumsq[b] > 0.0) ? 0 : 1;
+    a.n_used[b] = 0.0;
+    a.err[b] = 0.0;
+}
+
+// block masses of stage 1 (and zero output for zero vectors)
+__global__ void tomo_big_mass_kernel(TomoBigArgs a) {
+    __shared__ double red[32];
+    const long long b = blockIdx.y;
+    const int blk = blockIdx.x, tid = threadIdx.x;
+    bool zero;
+    const double div = big_scale(a.sumsq[b], zero);
+    if (zero) {
+        for (int i = tid; i < TB; i += blockDim.x) { int g = blk * TB + i; if (g < a.d) a.est[b * (long long)a.d + g] = 0.0; }
+        return;
+    }
+    if (a.done[b]) return;
+    double s = 0.0;
+    for (int i = tid; i < TB; i += blockDim.x) {
+        int g = blk * TB + i;
+        double x = (g < a.d) ? a.V[b * (long long)a.d + g] / div : 0.0;
+        s += x * x;
+    }
+    s = block_sum(s, red, tid, blockDim.x);
+    if (tid == 0) a.bm_a[b * a.nblk + blk] = s;
+}
+
+// one CTA per vector: split the attempt's measurements over the blocks
+__global__ void tomo_big_top_kernel(TomoBigArgs a, int stage) {
+    extern __shared__ double sm[];
+    const long long b = blockIdx.x;
+    if (a.done[b]) return;
+    const int tid = threadIdx.x, T = blockDim.x, NB = a.NB;
+    double* mass = sm;            // [2 NB]
+    double* cnt = mass + 2 * NB;  // [2 NB]
+    double* red = cnt + 2 * NB;   // [32]
+    const unsigned long long vec = a.vec_offset + (unsigned long long)b;
+    double sminus = 0.0;
+    for (int i = tid; i < NB; i += T) {
+        mass[NB + i] = (i < a.nblk) ? a.bm_a[b * a.nblk + i] : 0.0;
+        if (stage == 2 && i < a.nblk) sminus += a.bm_b[b * a.nblk + i];
+    }
+    if (stage == 2) sminus = block_sum(sminus, red, tid, T);
+    build_tree(mass, NB, a.logNB, tid, T);
+    if (tid == 0) {
+        if (stage == 1) cnt[1] = a.N;
+        else {
+            Philox rng(a.seed, vec, (unsigned)(4 * a.at + 2), 0u);
+            cnt[1] = binomial_split(a.N, mass[1], sminus, rng);
+        }
+    }
+    split_tree(mass, cnt, a.logNB, tid, T, a.seed, vec, (unsigned)(4 * a.at + (stage == 1 ? 0 : 2)));
+    for (int i = tid; i < a.nblk; i += T) a.bcnt[b * a.nblk + i] = cnt[NB + i];
+}
+
+// one CTA per block: split the block's share over its leaves
+__global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
+    extern __shared__ double sm[];
+    const long long b = blockIdx.y;
+    if (a.done[b]) return;
+    const int blk = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+    double* v = sm;               // [TB]
+    double* P = v + TB;           // [TB]
+    double* mass = P + TB;        // [2 TB]
+    double* cnt = mass + 2 * TB;  // [2 TB]
+    double* red = cnt + 2 * TB;   // [32]
+    bool zero;
+    const double div = big_scale(a.sumsq[b], zero);
+    const unsigned long long vec = a.vec_offset + (unsigned long long)b;
+    const long long base = b * (long long)a.d + (long long)blk * TB;
+    for (int i = tid; i < TB; i += T) {
+        int g = blk * TB + i;
+        double x = (g < a.d) ? a.V[base + i] / div : 0.0;
+        v[i] = x;
+        if (stage == 1) mass[TB + i] = x * x;
+        else {
+            double p = (g < a.d) ? a.est[base + i] : 0.0;
+            P[i] = p;
+            double ap = 0.5 * (x + p);
+            mass[TB + i] = ap * ap;
+        }
+    }
+    build_tree(mass, TB, TB_LOG, tid, T);
+    if (tid == 0) cnt[1] = a.bcnt[b * a.nblk + blk];
+    // node ids are offset by the block so that every (vector, block, node) owns its own Philox stream
+    {
+        for (int lev = 0; lev < TB_LOG; ++lev) {
+            __syncthreads();
+            int first = 1 << lev;
+            for (int i = first + tid; i < 2 * first; i += T) {
+                double n = cnt[i];
+                double left = 0.0;
+                if (n > 0.0) {
+                    Philox rng(a.seed, vec, (unsigned)(4 * a.at + (stage == 1 ? 1 : 3)), (unsigned)(blk * (2 * TB) + i));
+                    left = binomial_split(n, mass[2 * i], mass[2 * i + 1], rng);
+                }
+                cnt[2 * i] = left;
+                cnt[2 * i + 1] = n - left;
+            }
+        }
+        __syncthreads();
+    }
+    if (stage == 1) {
+        double sp = 0.0, smn = 0.0;
+        for (int i = tid; i < TB; i += T) {
+            int g = blk * TB + i;
+            double p = sqrt(cnt[TB + i] / a.N);
+            if (g < a.d) a.est[base + i] = p;
+            double ap = 0.5 * (v[i] + p), am = 0.5 * (v[i] - p);
+            sp += ap * ap;
+            smn += am * am;
+        }
+        sp = block_sum(sp, red, tid, T);
+        smn = block_sum(smn, red, tid, T);
+        if (tid == 0) { a.bm_a[b * a.nblk + blk] = sp; a.bm_b[b * a.nblk + blk] = smn; }
+    } else {
+        double e = 0.0;
+        for (int i = tid; i < TB; i += T) {
+            int g = blk * TB + i;
+            double p = P[i];
+            double est = (cnt[TB + i] > 0.4 * p * p * a.N) ? p : -p;
+            if (g < a.d) {
+                a.est[base + i] = est;
+                double df = v[i] - est;
+                e = a.norm_inf ? fmax(e, fabs(df)) : e + df * df;
+            }
+        }
+        e = a.norm_inf ? block_max(e, red, tid, T) : block_sum(e, red, tid, T);
+        if (tid == 0) a.errp[b * a.nblk + blk] = e;
+    }
+}
+
+__global__ void tomo_big_finish_kernel(TomoBigArgs a) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x;
+    if (a.done[b]) return;
+    const int tid = threadIdx.x;
+    double e = 0.0;
+    for (int i = tid; i < a.nblk; i += blockDim.x) {
+        double p = a.errp[b * a.nblk + i];
+        e = a.norm_inf ? fmax(e, p) : e + p;
+    }
+    e = a.norm_inf ? block_max(e, red, tid, blockDim.x) : sqrt(block_sum(e, red, tid, blockDim.x));
+    if (tid == 0) {
+        a.n_used[b] = a.N;
+        a.err[b] = e;
+        if (a.stop && e <= a.delta) a.done[b] = 1;
+    }
+}
+
 }  // namespace sq
 
 // ---------------------------------------------------------------------------
@@ -225,6 +415,83 @@ extern "C" int sq_tomography_batched(const double* V, long long B, int d, double
         tomo_fused_kernel<<<(unsigned)nb, threads, smem, stream>>>(c);
         SQ_LAUNCH_CHECK("tomo_fused_kernel");
         done += nb;
+    }
+    return SQ_OK;
+}
+
+// ---- long vectors ------------------------------------------------------------
+extern "C" int sq_row_sqnorms(const double* X, long long n, int d, double* out, void* stream);
+
+static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, size_t off[6], size_t* total) {
+    int nb = (d + TB - 1) / TB;
+    int p2 = 2, lg = 1;
+    while (p2 < nb) { p2 <<= 1; ++lg; }
+    *nblk = nb; *NB = p2; *logNB = lg;
+    size_t o = 0;
+    size_t per = align_up((size_t)B * nb * sizeof(double), 256);
+    off[0] = o; o += align_up((size_t)B * sizeof(double), 256);   // sumsq
+    off[1] = o; o += per;                                         // bm_a
+    off[2] = o; o += per;                                         // bm_b
+    off[3] = o; o += per;                                         // bcnt
+    off[4] = o; o += per;                                         // errp
+    off[5] = o; o += align_up((size_t)B * sizeof(int), 256);      // done
+    *total = o;
+}
+
+extern "C" size_t sq_tomography_workspace_bytes(long long B, int d) {
+    if (d <= sq_tomography_max_fused_dim() || B <= 0) return 0;
+    int nblk, NB, logNB;
+    size_t off[6], total;
+    tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
+    return total;
+}
+
+extern "C" int sq_tomography_batched_ws(const double* V, long long B, int d, double delta, int norm_inf, int stop,
+                                        const double* sched_host, int sched_len, unsigned long long seed,
+                                        unsigned long long vec_offset, double* est, double* n_used, double* err,
+                                        void* ws, size_t ws_bytes, void* stream_) {
+    if (d <= sq_tomography_max_fused_dim())
+        return sq_tomography_batched(V, B, d, delta, norm_inf, stop, sched_host, sched_len, seed, vec_offset, est,
+                                     n_used, err, nullptr, nullptr, stream_);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(V && est && n_used && err && sched_host, "sq_tomography_batched_ws: null pointer");
+    SQ_REQUIRE(B >= 0 && B <= 65535, "sq_tomography_batched_ws: B=%lld outside [0, 65535] for d > %d", B,
+               sq_tomography_max_fused_dim());
+    SQ_REQUIRE(sched_len >= 1 && sched_len <= 128, "sq_tomography_batched_ws: sched_len=%d outside [1,128]", sched_len);
+    SQ_REQUIRE(delta > 0.0, "sq_tomography_batched_ws: delta must be > 0");
+    if (B == 0) return SQ_OK;
+    int nblk, NB, logNB;
+    size_t off[6], total;
+    tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
+    if (NB > 4096) { set_error("sq_tomography_batched_ws: d=%d exceeds the supported %d", d, 4096 * TB); return SQ_ERR_UNSUPPORTED; }
+    if (!ws || ws_bytes < total) { set_error("sq_tomography_batched_ws: workspace needs %zu bytes, got %zu", total, ws_bytes); return SQ_ERR_WORKSPACE; }
+    char* w = (char*)ws;
+    TomoBigArgs a;
+    a.V = V; a.est = est; a.n_used = n_used; a.err = err;
+    a.sumsq = (double*)(w + off[0]); a.bm_a = (double*)(w + off[1]); a.bm_b = (double*)(w + off[2]);
+    a.bcnt = (double*)(w + off[3]); a.errp = (double*)(w + off[4]); a.done = (int*)(w + off[5]);
+    a.B = B; a.d = d; a.nblk = nblk; a.NB = NB; a.logNB = logNB; a.norm_inf = norm_inf; a.stop = stop; a.delta = delta;
+    a.seed = seed; a.vec_offset = vec_offset;
+    int rc = sq_row_sqnorms(V, B, d, (double*)(w + off[0]), stream_);
+    if (rc) return rc;
+    tomo_big_init_kernel<<<(unsigned)((B + 255) / 256), 256, 0, stream>>>(a);
+    SQ_LAUNCH_CHECK("tomo_big_init_kernel");
+    size_t sm_top = (size_t)(4 * NB + 32) * sizeof(double);
+    size_t sm_blk = (size_t)(6 * TB + 32) * sizeof(double);
+    SQ_CUDA(cudaFuncSetAttribute(tomo_big_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_top));
+    SQ_CUDA(cudaFuncSetAttribute(tomo_big_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_blk));
+    dim3 gblk(nblk, (unsigned)B);
+    int ttop = NB < 64 ? 64 : (NB > 512 ? 512 : NB);   // register budget: ~96 per thread
+    for (int at = 0; at < sched_len; ++at) {
+        SQ_REQUIRE(sched_host[at] >= 1.0 && sched_host[at] < 9.0e15, "sq_tomography_batched_ws: schedule entry out of range");
+        a.at = at; a.N = sched_host[at];
+        tomo_big_mass_kernel<<<gblk, 256, 0, stream>>>(a);
+        tomo_big_top_kernel<<<(unsigned)B, ttop, sm_top, stream>>>(a, 1);
+        tomo_big_block_kernel<<<gblk, 256, sm_blk, stream>>>(a, 1);
+        tomo_big_top_kernel<<<(unsigned)B, ttop, sm_top, stream>>>(a, 2);
+        tomo_big_block_kernel<<<gblk, 256, sm_blk, stream>>>(a, 2);
+        tomo_big_finish_kernel<<<(unsigned)B, 256, 0, stream>>>(a);
+        SQ_LAUNCH_CHECK("tomo_big kernels");
     }
     return SQ_OK;
 }

@@ -244,6 +244,21 @@ def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, v
     att = dv.empty((B,), dtype=torch.int32) if trace else None
     if seed_ is None:
         seed_, vec_offset = _take_streams(B)
+    if d > _cabi.lib.sq_tomography_max_fused_dim():
+        if trace:
+            raise NotImplementedError("the per-attempt trace is kept only for d <= %d"
+                                      % _cabi.lib.sq_tomography_max_fused_dim())
+        # long vectors: grid-wide path with caller workspace; at most 65535 vectors per call
+        for b0 in range(0, B, 65535):
+            b1 = min(B, b0 + 65535)
+            nb = _cabi.lib.sq_tomography_workspace_bytes(b1 - b0, d)
+            ws = dv.workspace(nb)
+            _cabi.check(_cabi.lib.sq_tomography_batched_ws(
+                dv.ptr(V[b0:b1]), b1 - b0, d, float(delta), 1 if norm == 'inf' else 0,
+                1 if (stop and incremental) else 0, sched.ctypes.data, len(sched), seed_, vec_offset + b0,
+                dv.ptr(est[b0:b1]), dv.ptr(n_used[b0:b1]), dv.ptr(err[b0:b1]), dv.ptr(ws), nb, dv.stream_ptr()),
+                "sq_tomography_batched_ws")
+        return est, n_used, err, tr, att, sched
     _cabi.check(_cabi.lib.sq_tomography_batched(
         dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, 1 if (stop and incremental) else 0,
         sched.ctypes.data, len(sched), seed_, vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err),
@@ -261,6 +276,11 @@ def real_tomography(V, N=None, delta=None, stop_when_reached_accuracy=True, norm
     if norm not in ('L2', 'inf'):
         raise ValueError("norm must be 'L2' or 'inf'")
     Vd = dv.to_device(np.asarray(V, dtype=np.float64).reshape(1, -1))
+    if Vd.shape[1] > _cabi.lib.sq_tomography_max_fused_dim():
+        # long vectors: only the returned attempt is kept (its estimate alone is d doubles per attempt)
+        est, n_used, err, _, _, _ = _tomography_device(
+            Vd, delta, N, norm, stop_when_reached_accuracy, incremental_measure, faster_measure_increment)
+        return {int(n_used.item()): list(est[0].cpu().numpy())}
     est, n_used, err, tr, att, sched = _tomography_device(
         Vd, delta, N, norm, stop_when_reached_accuracy, incremental_measure, faster_measure_increment, trace=True)
     n_att = int(att.item())

@@ -178,3 +178,85 @@ def test_trace_and_public_api(cuda, golden_stoch):
     assert np.abs(g - v).max() <= 0.3 / 4
     single = Q.real_tomography(v, delta=0.3, incremental_measure=False)
     assert list(single.keys()) == [qu.tomography_N(16, 0.3)]
+
+
+def _big(V, delta, sched, norm_inf=0, stop=0, seed=1, vec_offset=0):
+    import torch
+    from sqlearn import _cabi, _device as dv
+    Vd = torch.as_tensor(np.ascontiguousarray(np.atleast_2d(V))).cuda()
+    B, d = Vd.shape
+    sched = np.ascontiguousarray(sched, dtype=np.float64)
+    est = torch.empty_like(Vd)
+    n_used = torch.empty(B, dtype=torch.float64, device="cuda")
+    err = torch.empty(B, dtype=torch.float64, device="cuda")
+    nb = _cabi.lib.sq_tomography_workspace_bytes(B, d)
+    ws = torch.empty(max(nb, 8), dtype=torch.uint8, device="cuda")
+    _cabi.check(_cabi.lib.sq_tomography_batched_ws(Vd.data_ptr(), B, d, float(delta), norm_inf, stop, sched.ctypes.data,
+                                                   len(sched), seed, vec_offset, est.data_ptr(), n_used.data_ptr(),
+                                                   err.data_ptr(), ws.data_ptr(), nb, dv.stream_ptr()), "tomo_ws")
+    torch.cuda.synchronize()
+    return est.cpu().numpy(), n_used.cpu().numpy(), err.cpu().numpy()
+
+
+@pytest.mark.parametrize("d", [4097, 5000, 20000, 131072, 1000000])
+def test_long_vectors(cuda, d):
+    """d beyond the fused path: unit-norm output, the stop rule holds, results do not depend on batching"""
+    from oracle import quantum_utility as qu
+    rs = np.random.RandomState(d % 1000)
+    B = 3 if d <= 131072 else 1
+    V = rs.uniform(-1, 1, (B, d))
+    V[0] *= 3.0                                      # gets normalised (Utility.py:301-304)
+    Vn = V / np.linalg.norm(V, axis=1, keepdims=True)
+    delta = 0.3
+    N = qu.tomography_N(d, delta)
+    est, n_used, err = _big(V, delta, [N], seed=5, vec_offset=10)
+    assert (n_used == N).all()
+    np.testing.assert_allclose(np.linalg.norm(est, axis=1), 1.0, atol=1e-9)
+    np.testing.assert_allclose(err, np.linalg.norm(Vn - est, axis=1), rtol=1e-10)
+    assert (err < delta).all() and (err > 0).all()
+    # squared estimates are counts / N
+    np.testing.assert_allclose((est ** 2).sum(axis=1), 1.0, atol=1e-9)
+    sched = qu.schedule(N).astype(float)
+    e2, n2, r2 = _big(V, delta, sched, stop=1, seed=6, vec_offset=10)
+    assert (r2 <= delta).all() and (n2 < N).all()
+    np.testing.assert_allclose(r2, np.linalg.norm(Vn - e2, axis=1), rtol=1e-10)
+    if B > 1:
+        a = _big(V[:1], delta, sched, stop=1, seed=6, vec_offset=10)
+        b = _big(V[1:], delta, sched, stop=1, seed=6, vec_offset=11)
+        assert np.array_equal(np.vstack([a[0], b[0]]), e2) and np.array_equal(np.concatenate([a[1], b[1]]), n2)
+    # L-infinity
+    Ni = qu.tomography_N(d, 0.05, "inf")
+    e3, _, r3 = _big(V, 0.05, [Ni], norm_inf=1, seed=7)
+    np.testing.assert_allclose(r3, np.abs(Vn - e3).max(axis=1), rtol=1e-10)
+    assert (r3 < 0.05).all()
+
+
+def test_long_vector_law_matches_oracle(cuda):
+    """d = 5000 at a small N: error and one component's estimate follow the oracle's law"""
+    from oracle import quantum_utility as qu
+    rs = np.random.RandomState(9)
+    d, N, B = 5000, 20000, 400
+    v = rs.uniform(-1, 1, d)
+    v /= np.linalg.norm(v)
+    big = np.argmax(np.abs(v))
+    est, _, err = _big(np.repeat(v[None], B, axis=0), 0.5, [float(N)], seed=8)
+    rng = np.random.default_rng(1)
+    o = np.array([qu.tomography_attempt(v, N, rng) for _ in range(B)])
+    oerr = np.linalg.norm(v[None] - o, axis=1)
+    assert stats.ks_2samp(err, oerr).pvalue > P_MIN
+    assert stats.ks_2samp(est[:, big], o[:, big]).pvalue > P_MIN
+    wrong, owrong = np.sum(np.sign(est) != np.sign(v)[None]), np.sum(np.sign(o) != np.sign(v)[None])
+    assert abs(wrong - owrong) < 6 * np.sqrt(wrong + owrong)
+
+
+def test_long_vector_public_api(cuda):
+    from sqlearn import QuantumUtility as Q
+    rs = np.random.RandomState(3)
+    v = rs.uniform(-1, 1, 6000)
+    Q.seed(4)
+    out = Q.tomography(np.stack([v, -2 * v]), 0.4)
+    vn = v / np.linalg.norm(v)
+    assert out.shape == (2, 6000)
+    assert np.linalg.norm(out[0] - vn) <= 0.4 and np.linalg.norm(out[1] + vn) <= 0.4
+    res = Q.real_tomography(v, delta=0.4)
+    assert len(res) == 1 and np.linalg.norm(np.asarray(list(res.values())[0]) - vn) <= 0.4
