@@ -10,111 +10,129 @@
 //
 //     p(j) = sin^2(pi*t) / (M^2 * sin^2(pi*(j - x)/M)),   x = M*w, t = frac(x)
 //
-// and sum_j p(j) = 1 exactly (Fejer kernel identity).  We enumerate the four
-// grid points around x exactly (>= 87% of the mass) and sample the two tails
-// by rejection from a 1/z^2 envelope (sin(pi*y) >= 2y on [0, 1/2]).  For tiny
-// M the O(M) inversion is used; it is also the truth the tests compare with.
+// and sum_j p(j) = 1 exactly (Fejer kernel identity).  The eight grid points
+// around x are enumerated exactly (>= 95% of the mass) and the two tails are
+// sampled by rejection from a 1/z^2 envelope (sin(pi*y) >= 2y on [0, 1/2]).
+// The table is built once per (M, x) and reused for repeated draws (the
+// median of 13 in inner-product estimation).  For tiny M the O(M) inversion
+// is used; it is also the truth the tests compare with.
 #pragma once
 #include "common.cuh"
 
 namespace sq {
 
-// exact pmf of offset m (grid point j = floor(x) + m), given s2 = sin^2(pi t)
-__host__ __device__ inline double fejer_pmf(double M, double t, double s2, double m) {
-    double y = (m - t) / M;
+__host__ __device__ inline double sq_sinpi(double y) {
 #ifdef __CUDA_ARCH__
-    double s = sinpi(y);
+    return sinpi(y);
 #else
-    double s = sin(3.14159265358979323846 * y);
+    return sin(3.14159265358979323846 * y);
 #endif
-    double ms = M * s;
-    return s2 / (ms * ms);
+}
+
+static constexpr int FEJER_W = 4;  // window offsets -3 .. 4
+
+struct FejerTable {
+    double M, j0, t, s2;
+    double cum[2 * FEJER_W];  // cumulative mass of offsets 0, 1, -1, 2, -2, 3, -3, 4
+    double eR, eL;            // envelope masses of the right / left tail (common factor dropped)
+    double zminR, zmaxR, zminL, zmaxL;
+    bool exact;               // x is a grid point: the draw is deterministic
+    bool brute;               // M too small for window + tails
+};
+
+__host__ __device__ inline double fejer_offset(int i) {
+    // 0, 1, -1, 2, -2, 3, -3, 4
+    return (i & 1) ? (double)((i + 1) >> 1) : -(double)(i >> 1);
+}
+
+__host__ __device__ inline void fejer_setup(FejerTable& T, double M, double x) {
+    T.M = M;
+    double j0 = floor(x);
+    T.t = x - j0;
+    if (j0 >= M) j0 -= M;
+    T.j0 = j0;
+    T.exact = (T.t == 0.0);
+    T.brute = (M <= 2.0 * FEJER_W + 1.0);
+    double st = sq_sinpi(T.t);
+    T.s2 = st * st;
+    if (T.exact || T.brute) return;
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < 2 * FEJER_W; ++i) {
+        double ms = M * sq_sinpi((fejer_offset(i) - T.t) / M);
+        acc += T.s2 / (ms * ms);
+        T.cum[i] = acc;
+    }
+    // tails: right m in [W+1, mhi], left m in [mlo, -W], mhi - mlo + 1 = M, |m - t| <= M/2 everywhere
+    double half = floor((M - 1.0) * 0.5);
+    double mlo = -half;
+    if (T.t > 0.5 && fmod(M, 2.0) != 0.0) mlo += 1.0;
+    double mhi = mlo + M - 1.0;
+    T.zminR = FEJER_W - T.t;        T.zmaxR = mhi - T.t;
+    T.zminL = FEJER_W - 1.0 + T.t;  T.zmaxL = T.t - mlo;
+    T.eR = (T.zmaxR > T.zminR) ? (1.0 / T.zminR - 1.0 / T.zmaxR) : 0.0;
+    T.eL = (T.zmaxL > T.zminL) ? (1.0 / T.zminL - 1.0 / T.zmaxL) : 0.0;
+}
+
+__host__ __device__ inline double fejer_wrap(const FejerTable& T, double m) {
+    double j = T.j0 + m;
+    if (j < 0.0) j += T.M;
+    if (j >= T.M) j -= T.M;
+    return j;
+}
+
+// window lookup for a uniform u; returns false when u falls in the tails
+__host__ __device__ inline bool fejer_window(const FejerTable& T, double u, double& j) {
+#pragma unroll
+    for (int i = 0; i < 2 * FEJER_W; ++i) {
+        if (u < T.cum[i]) { j = fejer_wrap(T, fejer_offset(i)); return true; }
+    }
+    return false;
+}
+
+// one draw from the tails (conditional law), by rejection
+__host__ __device__ inline double fejer_tail(const FejerTable& T, Philox& rng) {
+    if (!(T.eR + T.eL > 0.0)) return fejer_wrap(T, 0.0);  // no tail cells (rounding put u past the window)
+    for (int it = 0; it < 1000; ++it) {
+        double a, b;
+        rng.uniform2(a, b);
+        // a picks the side and the position inside it (one uniform, rescaled), b accepts
+        double tot = T.eR + T.eL;
+        bool right = a * tot < T.eR;
+        double a2 = right ? (a * tot) / T.eR : (a * tot - T.eR) / T.eL;
+        double zmin = right ? T.zminR : T.zminL, zmax = right ? T.zmaxR : T.zmaxL;
+        double z = 1.0 / (1.0 / zmin - a2 * (1.0 / zmin - 1.0 / zmax));   // density ~ 1/z^2 on [zmin, zmax]
+        double dist = right ? ceil(z + T.t) - T.t : ceil(z - T.t) + T.t;  // |m - t| of the cell (dist-1, dist] holding z
+        if (dist - 1.0 < zmin) dist = zmin + 1.0;
+        if (dist > zmax) dist = zmax;
+        double env = 0.25 * (1.0 / (dist - 1.0) - 1.0 / dist);
+        double ms = T.M * sq_sinpi(dist / T.M);
+        if (b * env * ms * ms <= 1.0) return fejer_wrap(T, rint(right ? dist + T.t : T.t - dist));
+    }
+    return fejer_wrap(T, 0.0);  // unreachable in practice (acceptance >= 4/pi^2 * 3/4)
+}
+
+__host__ __device__ inline double fejer_brute(const FejerTable& T, double u) {
+    double acc = 0.0;
+    int Mi = (int)T.M;
+    for (int m = 0; m < Mi; ++m) {
+        double ms = T.M * sq_sinpi(((double)m - T.t) / T.M);
+        acc += T.s2 / (ms * ms);
+        if (u < acc || m == Mi - 1) return fejer_wrap(T, (double)m);
+    }
+    return T.j0;
 }
 
 // Draw j in [0, M) from p(j) above.  x = M*w must lie in [0, M].
 __host__ __device__ inline double fejer_sample(double M, double x, Philox& rng) {
-    double j0 = floor(x);
-    double t = x - j0;
-    if (j0 >= M) j0 -= M;
-    if (t == 0.0) return j0;  // reference: weight 1 at distance 0, ~1e-32 elsewhere
-#ifdef __CUDA_ARCH__
-    double st = sinpi(t);
-#else
-    double st = sin(3.14159265358979323846 * t);
-#endif
-    double s2 = st * st;
-    double u, v;
-    rng.uniform2(u, v);
-
-    if (M <= 16.0) {
-        // brute-force inversion over offsets m = 0..M-1 (periodic, any window of M works)
-        double acc = 0.0;
-        int Mi = (int)M;
-        for (int m = 0; m < Mi; ++m) {
-            acc += fejer_pmf(M, t, s2, (double)m);
-            if (u < acc || m == Mi - 1) {
-                double j = j0 + m;
-                return j >= M ? j - M : j;
-            }
-        }
-    }
-
-    // window m in {0, 1, -1, 2}, ordered by typical mass
-    double m_sel;
-    bool found = false;
-    double acc = 0.0;
-    const double wm[4] = {0.0, 1.0, -1.0, 2.0};
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        acc += fejer_pmf(M, t, s2, wm[i]);
-        if (!found && u < acc) { m_sel = wm[i]; found = true; }
-    }
-    if (!found) {
-        // tails: right m in [3, mhi], left m in [mlo, -2], mhi - mlo + 1 = M,
-        // chosen so |m - t| <= M/2 everywhere.
-        double half = floor((M - 1.0) * 0.5);
-        double mlo = -half;
-        if (t > 0.5 && fmod(M, 2.0) != 0.0) mlo += 1.0;  // keeps t - mlo <= M/2 for odd M
-        double mhi = mlo + M - 1.0;
-        // envelope masses (common factor s2/4 dropped): integral of 1/z^2
-        double eR = (mhi >= 3.0) ? (1.0 / (2.0 - t) - 1.0 / (mhi - t)) : 0.0;
-        double eL = (mlo <= -2.0) ? (1.0 / (1.0 + t) - 1.0 / (t - mlo)) : 0.0;
-        // v decides the side on the first try; later tries draw fresh numbers
-        double side_u = v;
-        for (int it = 0; it < 1000; ++it) {
-            double a, b;
-            rng.uniform2(a, b);
-            bool right = side_u * (eR + eL) < eR;
-            double zmin = right ? (2.0 - t) : (1.0 + t);
-            double zmax = right ? (mhi - t) : (t - mlo);
-            double inv = 1.0 / zmin - a * (1.0 / zmin - 1.0 / zmax);
-            double z = 1.0 / inv;               // z in [zmin, zmax], density ~ 1/z^2
-            double dist = right ? ceil(z + t) - t : ceil(z - t) + t;  // |m - t| of the cell holding z
-            // cell is (dist-1, dist]; its envelope mass is 1/(dist-1) - 1/dist
-            if (dist - 1.0 < zmin) dist = zmin + 1.0;
-            if (dist > zmax) dist = zmax;
-            double env = 0.25 * (1.0 / (dist - 1.0) - 1.0 / dist);
-            double y = dist / M;
-#ifdef __CUDA_ARCH__
-            double s = sinpi(y);
-#else
-            double s = sin(3.14159265358979323846 * y);
-#endif
-            double p = 1.0 / (M * s * M * s);
-            if (b * env <= p) {
-                m_sel = right ? (dist + t) : (t - dist);
-                m_sel = rint(m_sel);
-                found = true;
-                break;
-            }
-            side_u = rng.uniform();
-        }
-        if (!found) m_sel = 0.0;  // unreachable in practice (acceptance >= 4/pi^2 * 1/2)
-    }
-    double j = j0 + m_sel;
-    if (j < 0.0) j += M;
-    if (j >= M) j -= M;
-    return j;
+    FejerTable T;
+    fejer_setup(T, M, x);
+    if (T.exact) return T.j0;  // reference: weight 1 at distance 0, ~1e-32 elsewhere
+    double u = rng.uniform();
+    if (T.brute) return fejer_brute(T, u);
+    double j;
+    if (fejer_window(T, u, j)) return j;
+    return fejer_tail(T, rng);
 }
 
 }  // namespace sq

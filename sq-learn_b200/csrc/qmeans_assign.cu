@@ -84,18 +84,46 @@ __device__ __noinline__ double ipe_distance(double dot, double xn, double cn, do
     double eps_a = eps * fmax(1.0, fabs(dot)) / S;
     double M = ceil((PI / (2.0 * eps_a)) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
     double x = M * (asin(sqrt(a)) / PI);
-    // median of Q = 13 draws (median_evaluation with gamma = 0.1)
-    double s[13];
+    // median of Q = 13 draws (median_evaluation with gamma = 0.1).  a_tilde = sin^2(pi j / M) is
+    // increasing in r = min(j, M - j), so the median is taken over r and one sine is evaluated.
+    FejerTable T;
+    fejer_setup(T, M, x);
+    double med;
+    if (T.exact) {
+        med = fmin(T.j0, M - T.j0);
+    } else {
+        double r[13];
+        int ntail = 0, nr = 0;
+        // window draws first (no divergence), the few tail draws afterwards
 #pragma unroll 1
-    for (int q = 0; q < 13; ++q) {
-        double j = fejer_sample(M, x, rng);
-        double sn = sinpi(j / M);
-        double val = sn * sn;
-        int p = q;
-        while (p > 0 && s[p - 1] > val) { s[p] = s[p - 1]; --p; }
-        s[p] = val;
+        for (int q = 0; q < 13; q += 2) {
+            double u[2];
+            rng.uniform2(u[0], u[1]);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (q + h >= 13) break;
+                double j;
+                bool in = T.brute ? (j = fejer_brute(T, u[h]), true) : fejer_window(T, u[h], j);
+                if (in) {
+                    double v = fmin(j, M - j);
+                    int p = nr++;
+                    while (p > 0 && r[p - 1] > v) { r[p] = r[p - 1]; --p; }
+                    r[p] = v;
+                } else ++ntail;
+            }
+        }
+#pragma unroll 1
+        for (int q = 0; q < ntail; ++q) {
+            double j = fejer_tail(T, rng);
+            double v = fmin(j, M - j);
+            int p = nr++;
+            while (p > 0 && r[p - 1] > v) { r[p] = r[p - 1]; --p; }
+            r[p] = v;
+        }
+        med = r[6];
     }
-    return 2.0 * S * s[6];
+    double sn = sinpi(med / M);
+    return 2.0 * S * sn * sn;
 }
 
 // ---- TMA / mbarrier helpers (sm_90+ PTX; SASS: UTMALDG, SYNCS) -----------------
