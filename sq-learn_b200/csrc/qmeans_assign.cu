@@ -126,6 +126,13 @@ __device__ __noinline__ double ipe_distance(double dot, double xn, double cn, do
     return 2.0 * S * sn * sn;
 }
 
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ double dmin(double a, double b) { return b < a ? b : a; }  // no NaN handling needed here
+
 // ---- TMA / mbarrier helpers (sm_90+ PTX; SASS: UTMALDG, SYNCS) -----------------
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
@@ -165,7 +172,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     double* wmin = stages + STAGES * Cfg::STAGE_DOUBLES;     // [BM][WN_CNT] per-warp row minima
     double* xn_s = wmin + BM * WN_CNT;                       // [BM] ||x||^2 of the tile's rows
     double* thr_s = xn_s + BM;                               // [BM] precomputed row minimum (WINDOW, k > BN)
-    double* run_m1 = thr_s + BM;                             // [BM] running minimum over centroid tiles
+    double* rowmin_s = thr_s + BM;                           // [BM] this tile's row minimum over all warps
+    double* run_m1 = rowmin_s + BM;                          // [BM] running minimum over centroid tiles
     unsigned long long* cand = (unsigned long long*)(run_m1 + BM);  // [BM] (priority << 32 | col), WINDOW
     int* cnt = (int*)(cand + BM);                            // [BM] candidates found in the row
     int* first = cnt + BM;                                   // [BM] lowest candidate column
@@ -191,7 +199,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     // tiles owned by this CTA: blockIdx.x, + gridDim.x, ...
     const int my_tiles = (a.num_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     const int per_tile = a.NT * a.KC;
-    const long long total = (long long)my_tiles * per_tile;
+    const int total = my_tiles * per_tile;   // < 2^31: checked on the host
 
     // ---- loader state: every thread copies the same (row offset, k offset) piece of each pass ----
     constexpr int PPR = VEC16 ? Cfg::BK / 2 : Cfg::BK;  // pieces per row per chunk
@@ -205,7 +213,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     const int dstA0 = ((kb_t * BM + (r_t ^ kb_t)) << 2) + (kk & 3);
     const int dstB0 = BM * Cfg::BK + ((kb_t * BN + (r_t ^ kb_t)) << 2) + (kk & 3);
     const long long rpi_d = (long long)RPI * a.d;
-    long long p_left = total;
+    int p_left = total;
     long long p_tile = blockIdx.x;
     int p_nt = 0, p_kc = 0, p_stage = 0;
     const double* a_ptr = a.X + (p_tile * BM + r_t) * (long long)a.d + kk;
@@ -217,7 +225,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
         if (TMA) {
             // one thread hands the whole chunk to the TMA unit: per k-block of 4 one box {4, rows} for X and
             // one for C, landing as dense [k/4][row][4] slabs; rows / columns past the end arrive as zeros
-            if (tid == 0 && p_left > 0) {
+            if (warp == 0 && tid == 0 && p_left > 0) {
                 double* st = stages + p_stage * Cfg::STAGE_DOUBLES;
                 mbar_expect_tx(&full_bar[p_stage], Cfg::STAGE_DOUBLES * 8);
                 const int k0 = p_kc * Cfg::BK;
@@ -291,23 +299,25 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
 
     int kc = 0, nt = 0, tl = 0, c_stage = 0;
     unsigned c_phase = 0;
-    for (long long q = 0; q < total; ++q) {
+    const unsigned stages_u32 = (unsigned)__cvta_generic_to_shared(stages);
+    for (int q = 0; q < total; ++q) {
         if (TMA) mbar_wait(&full_bar[c_stage], c_phase);
         else cp_async_wait<STAGES - 2>();
         __syncthreads();
         issue();
 
-        const double* St = stages + c_stage * Cfg::STAGE_DOUBLES;
+        const unsigned st_u32 = stages_u32 + (unsigned)c_stage * (Cfg::STAGE_DOUBLES * 8);
+        const unsigned fa_u32 = st_u32 + fragA * 8, fb_u32 = st_u32 + fragB * 8;
         if (++c_stage == STAGES) { c_stage = 0; c_phase ^= 1; }
 #pragma unroll
         for (int kb = 0; kb < Cfg::KB; ++kb) {
             double af[MI], bf[NI];
             // (row ^ kb) with row = base + 8*i + lq: only lq's low two bits change
-            const int swz = TMA ? 0 : ((lq ^ kb) - lq) << 2;   // TMA slabs are dense, cp.async slabs are XOR-swizzled
+            const int swz = TMA ? 0 : ((lq ^ kb) - lq) << 5;   // bytes; TMA slabs are dense, cp.async slabs XOR-swizzled
 #pragma unroll
-            for (int i = 0; i < MI; ++i) af[i] = St[fragA + swz + ((kb * BM + i * 8) << 2)];
+            for (int i = 0; i < MI; ++i) af[i] = lds_f64(fa_u32 + swz + ((kb * BM + i * 8) << 5));
 #pragma unroll
-            for (int j = 0; j < NI; ++j) bf[j] = St[fragB + swz + ((kb * BN + j * 8) << 2)];
+            for (int j = 0; j < NI; ++j) bf[j] = lds_f64(fb_u32 + swz + ((kb * BN + j * 8) << 5));
 #pragma unroll
             for (int i = 0; i < MI; ++i)
 #pragma unroll
@@ -393,22 +403,32 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
             }
 #pragma unroll
             for (int i = 0; i < MI; ++i) {
-                double m = fmin(acc[i][0][0], acc[i][0][1]);
+                double m = dmin(acc[i][0][0], acc[i][0][1]);
 #pragma unroll
-                for (int j = 1; j < NI; ++j) m = fmin(m, fmin(acc[i][j][0], acc[i][j][1]));
-                m = fmin(m, __shfl_xor_sync(0xffffffffu, m, 1));
-                m = fmin(m, __shfl_xor_sync(0xffffffffu, m, 2));
+                for (int j = 1; j < NI; ++j) m = dmin(m, dmin(acc[i][j][0], acc[i][j][1]));
+                m = dmin(m, __shfl_xor_sync(0xffffffffu, m, 1));
+                m = dmin(m, __shfl_xor_sync(0xffffffffu, m, 2));
                 if (lr4 == 0) wmin[(wm * Cfg::WM + i * 8 + lq) * WN_CNT + wn] = m;
             }
             __syncthreads();
-            // ---- phase B: row minimum over the warps, candidates ----
+            // ---- phase B: row minimum over the warps (one entry per thread, segmented shuffle), candidates ----
+            {
+                constexpr int ENTRIES = BM * WN_CNT;
+                static_assert((WN_CNT & (WN_CNT - 1)) == 0 && WN_CNT <= 32, "warps along N must be a power of two");
+                for (int e0 = 0; e0 < ENTRIES; e0 += Cfg::THREADS) {
+                    int e = e0 + tid;
+                    double m = (e < ENTRIES) ? wmin[e] : INFINITY;
+#pragma unroll
+                    for (int o = 1; o < WN_CNT; o <<= 1) m = dmin(m, __shfl_xor_sync(0xffffffffu, m, o));
+                    if (e < ENTRIES && (e % WN_CNT) == 0) rowmin_s[e / WN_CNT] = m;
+                }
+            }
+            __syncthreads();
             bool have_multi = false;
 #pragma unroll
             for (int i = 0; i < MI; ++i) {
                 const int row = wm * Cfg::WM + i * 8 + lq;
-                double tmin = wmin[row * WN_CNT];
-#pragma unroll
-                for (int w = 1; w < WN_CNT; ++w) tmin = fmin(tmin, wmin[row * WN_CNT + w]);
+                const double tmin = rowmin_s[row];
                 double thr;
                 if (MODE == MODE_WINDOW) thr = (a.rowmin_in ? thr_s[row] : tmin) + a.delta;
                 else if (MODE == MODE_EXACT) thr = tmin + fmax(a.tie_tol, 0.0) * (xn_s[row] + 2.0 * fabs(tmin));
@@ -440,8 +460,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                             const int row = wm * Cfg::WM + i * 8 + lq;
                             if (cnt[row] <= 1 && a.NT == 1) continue;
                             const long long gr = r0 + row;
-                            double tmin = wmin[row * WN_CNT];
-                            for (int w = 1; w < WN_CNT; ++w) tmin = fmin(tmin, wmin[row * WN_CNT + w]);
+                            const double tmin = rowmin_s[row];
                             const double thr = (a.rowmin_in ? thr_s[row] : tmin) + a.delta;
                             unsigned long long best = ~0ull;
 #pragma unroll
@@ -469,8 +488,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
             if (tid < BM) {
                 const int row = tid;
                 const long long gr = r0 + row;
-                double tmin = wmin[row * WN_CNT];
-                for (int w = 1; w < WN_CNT; ++w) tmin = fmin(tmin, wmin[row * WN_CNT + w]);
+                const double tmin = rowmin_s[row];
                 const double xn = xn_s[row];
                 if (MODE == MODE_WINDOW) {
                     if (last_nt && gr < a.n) {
@@ -682,7 +700,7 @@ static size_t assign_ws_layout(long long n, int k, AssignWs* w, char* base) {
 template <class Cfg>
 static size_t assign_smem_bytes() {
     return (size_t)Cfg::STAGES * Cfg::STAGE_DOUBLES * 8 + (size_t)Cfg::BM * Cfg::WARPS_N * 8 +
-           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4 * 4) + 64;  // + NT*BN centroid norms, added at launch
+           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 8 + 4 * 4) + 64;  // + NT*BN centroid norms, added at launch
 }
 
 // optional timing of the main kernel alone (bench.py's roofline leg): events are
