@@ -174,8 +174,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     double* thr_s = xn_s + BM;                               // [BM] precomputed row minimum (WINDOW, k > BN)
     double* rowmin_s = thr_s + BM;                           // [BM] this tile's row minimum over all warps
     double* run_m1 = rowmin_s + BM;                          // [BM] running minimum over centroid tiles
-    unsigned long long* cand = (unsigned long long*)(run_m1 + BM);  // [BM] (priority << 32 | col), WINDOW
-    int* cnt = (int*)(cand + BM);                            // [BM] candidates found in the row
+    int* candcols = (int*)(run_m1 + BM);                     // [BM][4] first candidate columns of the row, WINDOW
+    int* cnt = candcols + 4 * BM;                            // [BM] candidates found in the row
     int* first = cnt + BM;                                   // [BM] lowest candidate column
     int* run_a1 = first + BM;                                // [BM]
     int* run_cnt = run_a1 + BM;                              // [BM]
@@ -366,7 +366,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 long long gr = r0 + tid;
                 xn_s[tid] = (gr < a.n) ? a.xnorm[gr] : 0.0;
                 if (MODE == MODE_WINDOW && a.rowmin_in) thr_s[tid] = (gr < a.n) ? a.rowmin_in[gr] : 0.0;
-                if (MODE != MODE_WINDOW || nt == 0) { cnt[tid] = 0; first[tid] = 0x7fffffff; cand[tid] = ~0ull; }
+                if (MODE != MODE_WINDOW || nt == 0) { cnt[tid] = 0; first[tid] = 0x7fffffff; }
             }
             if (MODE == MODE_IPE) {
                 __syncthreads();  // xn_s
@@ -424,7 +424,6 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 }
             }
             __syncthreads();
-            bool have_multi = false;
 #pragma unroll
             for (int i = 0; i < MI; ++i) {
                 const int row = wm * Cfg::WM + i * 8 + lq;
@@ -439,51 +438,22 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
 #pragma unroll
                     for (int e = 0; e < 2; ++e) mask |= (acc[i][j][e] <= thr ? 1u : 0u) << (j * 2 + e);
                 if (mask) {
-                    int b0 = __ffs(mask) - 1;
-                    atomicAdd(&cnt[row], __popc(mask));
-                    atomicMin(&first[row], colbase + (b0 >> 1) * 8 + (b0 & 1));
-                }
-                if (MODE == MODE_WINDOW) {
-                    // keep the mask for the rare multi-candidate path (bits 8*i .. 8*i + 2*NI - 1 of a 64-bit word
-                    // would not fit for NI = 4 and MI = 4: recomputed there instead)
+                    if (MODE == MODE_WINDOW) {
+                        // remember up to four candidate columns per row; rows with more go to the fix-up list
+                        while (mask) {
+                            int b0 = __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            int slot = atomicAdd(&cnt[row], 1);
+                            if (slot < 4) candcols[row * 4 + slot] = colbase + (b0 >> 1) * 8 + (b0 & 1);
+                        }
+                    } else {
+                        int b0 = __ffs(mask) - 1;
+                        atomicAdd(&cnt[row], __popc(mask));
+                        atomicMin(&first[row], colbase + (b0 >> 1) * 8 + (b0 & 1));
+                    }
                 }
             }
             __syncthreads();
-            if (MODE == MODE_WINDOW) {
-                // rows with several candidates: uniform pick = smallest random priority
-#pragma unroll
-                for (int i = 0; i < MI; ++i) have_multi |= (cnt[wm * Cfg::WM + i * 8 + lq] > 1) || (a.NT > 1);
-                if (__syncthreads_or(have_multi)) {
-                    if (have_multi) {
-#pragma unroll 1
-                        for (int i = 0; i < MI; ++i) {
-                            const int row = wm * Cfg::WM + i * 8 + lq;
-                            if (cnt[row] <= 1 && a.NT == 1) continue;
-                            const long long gr = r0 + row;
-                            const double tmin = rowmin_s[row];
-                            const double thr = (a.rowmin_in ? thr_s[row] : tmin) + a.delta;
-                            unsigned long long best = ~0ull;
-#pragma unroll
-                            for (int j = 0; j < NI; ++j)
-#pragma unroll
-                                for (int e = 0; e < 2; ++e) {
-                                    double v = (i == 0) ? acc[0][j][e] : (i == 1 && MI > 1) ? acc[MI > 1 ? 1 : 0][j][e]
-                                             : (i == 2 && MI > 2) ? acc[MI > 2 ? 2 : 0][j][e] : acc[MI - 1][j][e];
-                                    int col = colbase + j * 8 + e;
-                                    if (v <= thr && col < a.k) {
-                                        Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, (unsigned)col);
-                                        unsigned r[4];
-                                        rng.block(r);
-                                        unsigned long long key = ((unsigned long long)r[0] << 32) | (unsigned)col;
-                                        best = key < best ? key : best;
-                                    }
-                                }
-                            if (best != ~0ull) atomicMin(&cand[row], best);
-                        }
-                    }
-                    __syncthreads();
-                }
-            }
             // ---- phase C: one thread per row folds the tile into the running state and writes out ----
             if (tid < BM) {
                 const int row = tid;
@@ -492,8 +462,30 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 const double xn = xn_s[row];
                 if (MODE == MODE_WINDOW) {
                     if (last_nt && gr < a.n) {
-                        const unsigned long long c = cand[row];
-                        a.labels[gr] = (c != ~0ull) ? (int)(unsigned)(c & 0xffffffffu) : first[row];
+                        // uniform pick among the candidates (reference: random.choice, _dmeans.py:2252-2257)
+                        const int c = cnt[row];
+                        int c0 = candcols[row * 4], c1 = candcols[row * 4 + 1], c2 = candcols[row * 4 + 2],
+                            c3 = candcols[row * 4 + 3];
+                        int label = c0;
+                        if (c > 4) {
+                            int slot = atomicAdd(a.flag_count, 1);
+                            a.flag_rows[slot] = (int)gr;          // redone by qmeans_window_fixup_kernel
+                        } else if (c > 1) {
+                            // arrival order in the slots is arbitrary: sort, then take the r-th
+                            if (c < 4) c3 = 0x7fffffff;
+                            if (c < 3) c2 = 0x7fffffff;
+                            int t;
+                            if (c0 > c1) { t = c0; c0 = c1; c1 = t; }
+                            if (c2 > c3) { t = c2; c2 = c3; c3 = t; }
+                            if (c0 > c2) { t = c0; c0 = c2; c2 = t; }
+                            if (c1 > c3) { t = c1; c1 = c3; c3 = t; }
+                            if (c1 > c2) { t = c1; c1 = c2; c2 = t; }
+                            Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, 0u);
+                            int r = (int)(rng.uniform() * c);
+                            if (r >= c) r = c - 1;
+                            label = r == 0 ? c0 : r == 1 ? c1 : r == 2 ? c2 : c3;
+                        }
+                        a.labels[gr] = label;
                         const double base = a.rowmin_in ? thr_s[row] : tmin;
                         a.mindist[gr] = fmax(xn + base, 0.0);
                     }
@@ -624,6 +616,67 @@ __global__ void qmeans_fixup_kernel(AssignArgs a) {
     }
 }
 
+// ---- delta-window rows with more than four candidates ------------------------------
+// Rare (wide windows): one warp recomputes the row's |c|^2 - 2 x.c, finds the candidates
+// {v <= min + delta} and picks one uniformly (labels_estimation's delta_means1, _dmeans.py:742-748).
+__device__ __forceinline__ double fixup_v(const double* x, const double* c, double cn, int d) {
+    double s = 0.0;
+    for (int t = 0; t < d; ++t) s = fma(x[t], c[t], s);
+    return cn - 2.0 * s;
+}
+__global__ void qmeans_window_fixup_kernel(AssignArgs a) {
+    const int nflag = *a.flag_count;
+    const int lane = threadIdx.x & 31;
+    const int wglobal = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (int f = wglobal; f < nflag; f += nwarps) {
+        const long long gr = a.flag_rows[f];
+        const double* x = a.X + gr * (long long)a.d;
+        double vmin = INFINITY;
+        int amin = 0;
+        for (int j = lane; j < a.k; j += 32) {
+            double v = fixup_v(x, a.C + (long long)j * a.d, a.cnorm[j], a.d);
+            if (v < vmin) { vmin = v; amin = j; }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            double ov = __shfl_xor_sync(0xffffffffu, vmin, o);
+            int oa = __shfl_xor_sync(0xffffffffu, amin, o);
+            if (ov < vmin || (ov == vmin && oa < amin)) { vmin = ov; amin = oa; }
+        }
+        const double base = a.rowmin_in ? a.rowmin_in[gr] : vmin;
+        const double thr = base + a.delta;
+        int total = 0;
+        for (int j0 = 0; j0 < a.k; j0 += 32) {
+            int j = j0 + lane;
+            bool hit = j < a.k && fixup_v(x, a.C + (long long)j * a.d, a.cnorm[j], a.d) <= thr;
+            total += __popc(__ballot_sync(0xffffffffu, hit));
+        }
+        int label = amin;
+        if (total > 0) {
+            Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, 1u);
+            int pick = (int)(rng.uniform() * total);
+            if (pick >= total) pick = total - 1;
+            int seen = 0;
+            bool found = false;
+            for (int j0 = 0; j0 < a.k && !found; j0 += 32) {
+                int j = j0 + lane;
+                bool hit = j < a.k && fixup_v(x, a.C + (long long)j * a.d, a.cnorm[j], a.d) <= thr;
+                unsigned m = __ballot_sync(0xffffffffu, hit);
+                int c = __popc(m);
+                if (pick < seen + c) {
+                    int want = pick - seen;
+                    for (int b = 0; b < 32; ++b)
+                        if (m >> b & 1) { if (want == 0) { label = j0 + b; break; } --want; }
+                    found = true;
+                }
+                seen += c;
+            }
+        }
+        if (lane == 0) a.labels[gr] = label;
+    }
+}
+
 // ---- ||row||^2 of a row-major matrix (row_norms(X, squared=True), extmath.py:49-78)
 __global__ void row_sqnorm_kernel(const double* __restrict__ X, long long n, int d, double* __restrict__ out) {
     const int lane = threadIdx.x & 31;
@@ -700,7 +753,7 @@ static size_t assign_ws_layout(long long n, int k, AssignWs* w, char* base) {
 template <class Cfg>
 static size_t assign_smem_bytes() {
     return (size_t)Cfg::STAGES * Cfg::STAGE_DOUBLES * 8 + (size_t)Cfg::BM * Cfg::WARPS_N * 8 +
-           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 8 + 4 * 4) + 64;  // + NT*BN centroid norms, added at launch
+           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4 * 4 + 4 * 4) + 64;  // + NT*BN centroid norms, added at launch
 }
 
 // optional timing of the main kernel alone (bench.py's roofline leg): events are
@@ -891,6 +944,10 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
         int fb = device_sm_count() * 4;
         qmeans_fixup_kernel<<<fb, 256, 0, stream>>>(a);
         SQ_LAUNCH_CHECK("qmeans_fixup_kernel");
+    } else if (mode == MODE_WINDOW) {
+        int fb = device_sm_count() * 4;
+        qmeans_window_fixup_kernel<<<fb, 256, 0, stream>>>(a);
+        SQ_LAUNCH_CHECK("qmeans_window_fixup_kernel");
     }
     rc = sq_sum_f64(a.mindist, n, inertia, w.partial, SUM_BLOCKS * sizeof(double), stream);
     if (rc) return rc;

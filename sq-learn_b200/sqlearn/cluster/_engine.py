@@ -80,7 +80,7 @@ class QMeansEngine:
             seed, offset, dv.ptr(self.labels), dv.ptr(self.mindist), dv.ptr(self.inertia), dv.ptr(self.n_fixed),
             dv.ptr(self.ws_a), self.ws_a_bytes, dv.stream_ptr()), "sq_qmeans_assign")
         # memset, centre norms, assign, (fix-up), 2 x sum
-        self.launches += 5 if mode == MODE_EXACT else 4
+        self.launches += 4 if mode == MODE_IPE else 5
 
     # ---- M-step (K3) -------------------------------------------------------
     def accumulate(self):
