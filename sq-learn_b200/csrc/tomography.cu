@@ -42,6 +42,15 @@ struct TomoArgs {
     unsigned long long vec_offset;  // global id of vector 0 (sharding / call offset)
 };
 
+__device__ __forceinline__ double warp_scan_incl(double v) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        double y = __shfl_up_sync(0xffffffffu, v, o);
+        if ((threadIdx.x & 31) >= o) v += y;
+    }
+    return v;
+}
+
 __device__ __forceinline__ double block_sum(double v, double* red, int tid, int nthreads) {
     v = warp_sum(v);
     __syncthreads();  // red may still be read by a previous reduction
@@ -93,6 +102,48 @@ __device__ __forceinline__ void split_tree(const double* mass, double* cnt, int 
     __syncthreads();
 }
 
+// inclusive prefix sums of src[0..L) into dst[0..L) (L a power of two >= 2); every thread scans a
+// contiguous chunk, the chunk totals are scanned by warp 0.  Fixed order: deterministic.
+__device__ __forceinline__ void block_scan(const double* src, double* dst, int L, double* red, int tid, int T) {
+    const int per = (L + T - 1) / T;
+    const int i0 = tid * per, i1 = min(L, i0 + per);
+    double s = 0.0;
+    for (int i = i0; i < i1; ++i) { s += src[i]; dst[i] = s; }
+    __syncthreads();                      // red may still be read by an earlier reduction
+    // chunk totals -> exclusive offsets (T <= 512: at most 16 warps)
+    double w = warp_scan_incl(s);
+    if ((tid & 31) == 31) red[tid >> 5] = w;
+    __syncthreads();
+    double off = w - s;
+    for (int k = 0; k < (tid >> 5); ++k) off += red[k];
+    for (int i = i0; i < i1; ++i) dst[i] += off;
+    __syncthreads();
+}
+
+// N independent categorical draws from the CDF cdf[0..L) with total mass tot (draws >= cdf[L-1] fall in
+// the lumped remainder and are dropped); counts accumulate in cnt_i[0..L).  Sample s uses the Philox
+// stream (vec, stream, s/2), so the counts do not depend on the thread count.
+__device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL, double tot, int* cnt_i, long long N,
+                                              int tid, int T, unsigned long long seed, unsigned long long vec,
+                                              unsigned stream) {
+    const long long pairs = (N + 1) >> 1;
+    for (long long p = tid; p < pairs; p += T) {
+        Philox rng(seed, vec, stream, (unsigned)p);
+        double u[2];
+        rng.uniform2(u[0], u[1]);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (2 * p + h >= N) break;
+            const double target = u[h] * tot;
+            if (target >= cdf[L - 1]) continue;
+            int lo = 0;                        // smallest i with target < cdf[i]
+            for (int step = L >> 1; step > 0; step >>= 1)
+                if (cdf[lo + step - 1] <= target) lo += step;
+            atomicAdd(&cnt_i[lo], 1);
+        }
+    }
+}
+
 __global__ void tomo_fused_kernel(TomoArgs a) {
     extern __shared__ double sm[];
     const int L = a.L, d = a.d, tid = threadIdx.x, T = blockDim.x;
@@ -131,6 +182,34 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
     int n_att = 0;
     for (int at = 0; at < a.sched_len; ++at) {
         const double N = a.sched[at];
+        // Few measurements: draw them one by one (N/T categorical draws per thread, log2(d) probes each)
+        // instead of walking the tree, whose log2(d) dependent binomial draws cost more than that.
+        const bool direct = N <= 64.0 * T;
+        int* cnt_i = reinterpret_cast<int*>(cnt);
+        if (direct) {
+            for (int i = tid; i < L; i += T) { P[i] = v[i] * v[i]; cnt_i[i] = 0; }
+            __syncthreads();
+            block_scan(P, mass, L, red, tid, T);                 // stage-1 CDF in mass[0..L)
+            sample_direct(mass, L, a.logL, mass[L - 1], cnt_i, (long long)N, tid, T, a.seed, vec, (unsigned)(2 * at));
+            __syncthreads();
+            double sminus = 0.0;
+            for (int i = tid; i < L; i += T) {
+                double p = sqrt((double)cnt_i[i] / N);
+                P[i] = p;
+                double ap = 0.5 * (v[i] + p), am = 0.5 * (v[i] - p);
+                mass[L + i] = ap * ap;
+                sminus += am * am;
+            }
+            sminus = block_sum(sminus, red, tid, T);
+            __syncthreads();
+            for (int i = tid; i < L; i += T) cnt_i[i] = 0;
+            block_scan(mass + L, mass, L, red, tid, T);          // stage-2 '+' CDF; the '-' outcomes are one lump
+            sample_direct(mass, L, a.logL, mass[L - 1] + sminus, cnt_i, (long long)N, tid, T, a.seed, vec,
+                          (unsigned)(2 * at + 1));
+            __syncthreads();
+            for (int i = tid; i < L; i += T) cnt[L + i] = (double)cnt_i[i];   // the sign rule below reads cnt[L + i]
+            __syncthreads();
+        } else {
         // ---- stage 1 ----
         for (int i = tid; i < L; i += T) mass[L + i] = v[i] * v[i];
         build_tree(mass, L, a.logL, tid, T);
@@ -152,6 +231,7 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
             cnt[1] = binomial_split(N, mass[1], sminus, rng);
         }
         split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at + 1));
+        }
         // ---- sign rule + error ----
         double e = 0.0;
         for (int i = tid; i < L; i += T) {
