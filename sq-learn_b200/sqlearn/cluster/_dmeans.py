@@ -482,7 +482,7 @@ class qMeans_(BaseEstimator):
             X += X_mean
         best_centers = best_centers + X_mean_dev
         self._labels = best_labels.cpu().numpy()
-        distinct = len(np.unique(self._labels))
+        distinct = int((torch.bincount(best_labels.to(torch.int64), minlength=self.n_clusters) > 0).sum().item())
         if world == 1 and distinct < self.n_clusters:
             warnings.warn("Number of distinct clusters ({}) found smaller than n_clusters ({}). Possibly due to "
                           "duplicate points in X.".format(distinct, self.n_clusters), ConvergenceWarning,
