@@ -364,6 +364,60 @@ def extra_measurements(eng, centers, D, Q, _cabi, torch):
                       "ms": ms, "vectors_per_s": B / (ms * 1e-3), "simulated_measurements_per_s": 2 * n_used / (ms * 1e-3),
                       "algorithmic_GBps": 16.0 * B * d / (ms * 1e-3) / 1e9})
     out["tomography_sweep"] = sweep
+    out["qpca_config2"] = qpca_config2(torch)
+    return out
+
+
+def qpca_config2(torch):
+    """BASELINE.json config 2: qPCA top-50 on synthetic 70,000 x 784, singular-value estimation eps = 0.05,
+    L2 tomography delta = 0.1 (single-shot, qPCA's default).  Phases timed on the device after one warm-up."""
+    import warnings
+    from sqlearn import _cabi, _device as dv
+    from sqlearn.decomposition import qPCA
+    from sqlearn.QuantumUtility import Utility as U
+    n, d, k = 70000, 784, 50
+    g = torch.Generator(device="cuda")
+    g.manual_seed(1234)
+    cen = torch.randn((10, d), generator=g, device="cuda", dtype=torch.float64) * 3.0
+    X = cen[torch.randint(0, 10, (n,), generator=g, device="cuda")] + torch.randn((n, d), generator=g, device="cuda",
+                                                                                dtype=torch.float64)
+    Xh = X.cpu().numpy()
+    out = {"shape": [n, d], "n_components": k}
+    # kernels alone
+    G = dv.empty((d, d))
+    nb = _cabi.lib.sq_gram_workspace_bytes(n, d)
+    ws = dv.workspace(nb)
+    ms = _timed(torch, lambda: _cabi.check(_cabi.lib.sq_gram_centered(dv.ptr(X), n, d, None, dv.ptr(G), dv.ptr(ws), nb,
+                                                                      dv.stream_ptr()), "gram"), 3)
+    out["gram_ms"] = ms
+    out["gram_tflops"] = 2.0 * n * d * d / (ms * 1e-3) / 1e12          # full (non-symmetric) flop count
+    Vt = torch.linalg.eigh(G)[1].T.contiguous()
+    keys = torch.zeros((d,), dtype=torch.int64, device="cuda")
+    zeros = torch.zeros((d,), dtype=torch.float64, device="cuda")
+    ms = _timed(torch, lambda: _cabi.check(_cabi.lib.sq_project_absmax(dv.ptr(X), n, d, dv.ptr(Vt), d, dv.ptr(zeros),
+                                                                       dv.ptr(keys), dv.stream_ptr()), "absmax"), 3)
+    out["project_absmax_ms"] = ms
+    out["project_absmax_tflops"] = 2.0 * n * d * d / (ms * 1e-3) / 1e12
+    ms = _timed(torch, lambda: U.best_mu(X, start=0, step=0.1), 2)
+    out["best_mu_11pt_ms"] = ms
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        m = qPCA(n_components=k, svd_solver='full').fit(Xh)
+        theta = float(m.singular_values_[-1]) * 0.5
+        U.seed(3)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        m = qPCA(n_components=k, svd_solver='full').fit(Xh, estimate_all=True, eps=0.05, delta=0.1, theta_major=theta,
+                                                      true_tomography=True, norm='L2')
+        torch.cuda.synchronize()
+        out["fit_estimate_all_s"] = time.perf_counter() - t0
+        out["topk"] = int(m.topk)
+        t0 = time.perf_counter()
+        r = m.transform(Xh, classic_transform=False, epsilon_delta=0.1, quantum_representation=True,
+                        norm='est_representation')
+        torch.cuda.synchronize()
+        out["transform_quantum_representation_s"] = time.perf_counter() - t0
+        out["transform_rows"] = int(r['quantum_representation_results'][0].shape[0])
     return out
 
 

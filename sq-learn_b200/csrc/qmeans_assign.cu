@@ -57,7 +57,6 @@ struct AssignArgs {
     double delta;
     double tie_tol;        // relative rounding bound for the near-tie test
     unsigned long long seed, offset;
-    int dbg;               // SQ_ASSIGN_DBG experiments: 1 = no loads, 2 = no epilogue (timing only, wrong results)
 };
 
 template <int BM_, int BN_, int WARPS_M_, int WARPS_N_, int STAGES_, int BK_ = 16, int MIN_CTAS_ = 1>
@@ -243,7 +242,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
             }
             return;
         }
-        if (p_left > 0 && !(a.dbg & 1)) {
+        if (p_left > 0) {
             double* st = stages + p_stage * Cfg::STAGE_DOUBLES;
             const int koff = p_kc * Cfg::BK;
             const bool kok = koff + kk < a.d;
@@ -324,13 +323,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 for (int j = 0; j < NI; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
         }
 
-        if (kc == a.KC - 1 && (a.dbg & 2)) {
-            if (acc[0][0][0] == 12345.678) a.mindist[0] = acc[MI - 1][NI - 1][1];
-#pragma unroll
-            for (int i = 0; i < MI; ++i)
-#pragma unroll
-                for (int j = 0; j < NI; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
-        } else if (kc == a.KC - 1 && MODE == MODE_COLABS) {
+        if (kc == a.KC - 1 && MODE == MODE_COLABS) {
             // column-wise |max| of Y = X V^T - mu V^T (svd_flip's arg-max over all rows); NT must be 1
             const long long tile = (long long)blockIdx.x + (long long)tl * gridDim.x;
             const long long r0 = tile * BM;
@@ -803,7 +796,7 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
     CUtensorMap tmA, tmB;
     memset(&tmA, 0, sizeof(tmA));
     memset(&tmB, 0, sizeof(tmB));
-    bool use_tma = vec16 && !getenv("SQ_ASSIGN_NO_TMA") && !(a.dbg & 1);
+    bool use_tma = vec16 && !getenv("SQ_ASSIGN_NO_TMA");   // (the variable forces the cp.async path, for A/B timing)
     if (use_tma) {
         int r1 = make_tensor_map_2d(&tmA, a.X, (unsigned long long)a.d, (unsigned long long)a.n, 4, Cfg::BM);
         int r2 = make_tensor_map_2d(&tmB, a.C, (unsigned long long)a.d, (unsigned long long)a.k, 4, Cfg::BN);
@@ -928,7 +921,6 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     a.n = n; a.d = d; a.k = k; a.mode = mode; a.delta = delta;
     a.tie_tol = 16.0 * (d + 8) * 1.1102230246251565e-16;
     a.seed = seed; a.offset = offset;
-    { const char* e = getenv("SQ_ASSIGN_DBG"); a.dbg = e ? atoi(e) : 0; }
     int bn = 0;
     if (mode == MODE_WINDOW && k > 256) {
         // the window needs the row minimum over all k before candidates can be drawn

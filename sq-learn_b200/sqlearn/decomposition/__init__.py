@@ -1,4 +1,7 @@
-"""Quantum decomposition (reference: sklearn/decomposition/__init__.py:22)."""
+"""Quantum decomposition (reference: sklearn/decomposition/__init__.py:22).  ``PCA`` is an alias of
+``qPCA``: the quantum knobs are keyword arguments of ``fit`` / ``transform``."""
 from ._qPCA import qPCA  # noqa: F401
 
-__all__ = ['qPCA']
+PCA = qPCA
+
+__all__ = ['qPCA', 'PCA']

@@ -221,3 +221,16 @@ def test_qmeans_fit_end_to_end(cuda, golden_qmeans):
         e3 = qMeans_(n_clusters=5, init='k-means++', n_init=2, max_iter=3, delta=0.5, algorithm='full',
                      random_state=0).fit(X)
         assert len(e3.labels_) == len(X) and np.isfinite(e3.inertia_)
+
+
+def test_kmeans_alias_reaches_the_quantum_branch(cuda, golden_qmeans):
+    from sqlearn.cluster import KMeans
+    g = golden_qmeans
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        est = KMeans(n_clusters=5, init=g["a_C0"], n_init=1, max_iter=8, tol=0, delta=0).fit(g["a_X"])
+        assert est.labels_ == [int(v) for v in g["a_labels"]]
+        noisy = KMeans(n_clusters=5, init=g["a_C0"], n_init=1, max_iter=2, delta=0.5, true_distance_estimate=False,
+                       intermediate_error=True).fit(g["a_X"])
+        assert len(noisy.labels_) == len(g["a_X"])
+    assert KMeans(n_clusters=3, delta=0.1).get_params()["algorithm"] == "full"
