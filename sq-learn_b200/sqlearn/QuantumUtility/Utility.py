@@ -240,6 +240,8 @@ def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, v
     est = torch.empty_like(V)
     n_used = dv.empty((B,))
     err = dv.empty((B,))
+    if B == 0:
+        return est, n_used, err, None, None, sched
     tr = dv.empty((B, len(sched), d)) if trace else None
     att = dv.empty((B,), dtype=torch.int32) if trace else None
     if seed_ is None:
