@@ -125,6 +125,10 @@ int sq_centroid_accumulate(const double* X, const int* labels, long long n, int 
  * no rows keeps c_old (the reference leaves that row uninitialised).        */
 int sq_centroid_finalize(const double* sums, const double* counts, const double* c_old, int k, int d,
                          double* c_new, void* stream);
+/* euclidean_distances(X[cand], X, squared=True) of _kmeans_plusplus (_dmeans.py:209-211, :228-229):
+ * out[t, i] = max(|x_i|^2 + |x_cand[t]|^2 - 2 x_i.x_cand[t], 0), T <= 16 candidates in one pass over X. */
+int sq_rows_sqdist(const double* X, const double* xnorm, long long n, int d, const int* cand, int T, double* out,
+                   void* stream);
 /* squared_norm(a - b) (_dmeans.py:651), single deterministic reduction      */
 int sq_sqdiff_sum(const double* a, const double* b, long long n, double* out, void* stream);
 

@@ -122,6 +122,46 @@ def _kmeans_plusplus(X, n_clusters, x_squared_norms, random_state, n_local_trial
     return centers, indices
 
 
+def _kmeans_plusplus_device(engine, n_clusters, random_state, n_local_trials=None):
+    """k-means++ seeding with X on the device (same algorithm and same consumption of
+    ``random_state`` as :func:`_kmeans_plusplus` / the reference's _dmeans.py:153-247).  Per step one
+    pass over X gives the squared distances to all candidates (``sq_rows_sqdist``); the prefix sum,
+    the binary search and the reductions over n run as device tensor ops.  Returns device centres."""
+    from .. import _cabi
+    X, n, d = engine.X, engine.n, engine.d
+    if n_local_trials is None:
+        n_local_trials = 2 + int(np.log(n_clusters))
+    T = n_local_trials
+    if T > 16:
+        raise ValueError("n_local_trials=%d exceeds the 16 candidates one pass handles" % T)
+    dev = X.device
+    centers = torch.empty((n_clusters, d), dtype=torch.float64, device=dev)
+    dist = torch.empty((T, n), dtype=torch.float64, device=dev)
+
+    def sqdist(ids):
+        cand = torch.as_tensor(np.asarray(ids, dtype=np.int32), device=dev)
+        _cabi.check(_cabi.lib.sq_rows_sqdist(dv.ptr(X), dv.ptr(engine.xnorm), n, d, dv.ptr(cand), len(ids),
+                                             dv.ptr(dist), dv.stream_ptr()), "sq_rows_sqdist")
+        return dist[:len(ids)]
+
+    center_id = int(random_state.randint(n))
+    centers[0] = X[center_id]
+    closest = sqdist([center_id])[0].clone()
+    current_pot = float(closest.sum().item())
+    for c in range(1, n_clusters):
+        rand_vals = random_state.random_sample(T) * current_pot
+        cum = torch.cumsum(closest, dim=0)
+        cand = torch.searchsorted(cum, torch.as_tensor(rand_vals, device=dev))
+        cand = torch.clamp(cand, max=n - 1).cpu().numpy()
+        d2 = torch.minimum(sqdist(cand), closest[None, :])
+        pots = d2.sum(dim=1)
+        best = int(torch.argmin(pots).item())
+        current_pot = float(pots[best].item())
+        closest = d2[best].clone()
+        centers[c] = X[int(cand[best])]
+    return centers
+
+
 def _mode_of(delta, true_distance_estimate):
     if not delta or delta <= 0:
         return MODE_EXACT
@@ -455,14 +495,18 @@ class qMeans_(BaseEstimator):
             raise TypeError("_kmeans_single_elkan() got an unexpected keyword argument 'delta' "
                             "(use algorithm='full' for q-means, as in the reference)")
 
-        need_host = not hasattr(init, '__array__')
+        device_init = isinstance(init, str) and init == 'k-means++' and world == 1
+        need_host = not hasattr(init, '__array__') and not device_init
         if need_host:
             X -= X_mean                      # our private copy when copy_x=True, as in the reference
             x_sq_host = np.einsum('ij,ij->i', X, X)
         best_inertia = None
         for _ in range(self._n_init):
-            centers_init = self._init_centroids(X, x_sq_host if need_host else None, init, random_state)
-            c_dev = dv.to_device(centers_init)
+            if device_init:
+                c_dev = _kmeans_plusplus_device(engine, self.n_clusters, random_state)
+            else:
+                centers_init = self._init_centroids(X, x_sq_host if need_host else None, init, random_state)
+                c_dev = dv.to_device(centers_init)
             if world > 1:
                 import torch.distributed as dist
                 dist.broadcast(c_dev, src=0)

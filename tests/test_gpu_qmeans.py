@@ -234,3 +234,20 @@ def test_kmeans_alias_reaches_the_quantum_branch(cuda, golden_qmeans):
                        intermediate_error=True).fit(g["a_X"])
         assert len(noisy.labels_) == len(g["a_X"])
     assert KMeans(n_clusters=3, delta=0.1).get_params()["algorithm"] == "full"
+
+
+def test_device_kmeans_plusplus_equals_host_version(cuda):
+    """same candidates, same centres, same consumption of random_state as the reference's seeding"""
+    import torch
+    from sqlearn.cluster._dmeans import _kmeans_plusplus, _kmeans_plusplus_device
+    from sqlearn.cluster._engine import QMeansEngine
+    rs = np.random.RandomState(0)
+    for n, d, k in [(500, 6, 7), (3000, 33, 20), (20000, 128, 40)]:
+        X = rs.randn(n, d) + 3 * rs.randint(0, 5, n)[:, None]
+        xs = np.einsum("ij,ij->i", X, X)
+        r1, r2 = np.random.RandomState(42), np.random.RandomState(42)
+        want, ids = _kmeans_plusplus(X, k, xs, r1)
+        eng = QMeansEngine(torch.as_tensor(X).cuda().contiguous(), k)
+        got = _kmeans_plusplus_device(eng, k, r2).cpu().numpy()
+        np.testing.assert_array_equal(got, want)
+        assert r1.random_sample() == r2.random_sample()      # both generators are in the same state
