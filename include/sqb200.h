@@ -71,6 +71,16 @@ int sq_tomography_batched_ws(const double* V, long long B, int d, double delta, 
                              unsigned long long vec_offset, double* est, double* n_used, double* err, void* ws,
                              size_t ws_bytes, void* stream);
 
+/* Incremental mode with the stop rule, lower latency: `lanes` CTAs per vector try different attempts of the
+ * schedule at the same time and record the first (in schedule order) that meets the accuracy; that attempt
+ * is then replayed to produce the outputs.  Attempts are fresh draws keyed by their index, so est / n_used /
+ * err equal those of sq_tomography_batched with stop = 1, bit for bit.  stop_idx[B] is int scratch.
+ * d <= sq_tomography_max_fused_dim(), B <= 65535.                                                        */
+int sq_tomography_batched_spec(const double* V, long long B, int d, double delta, int norm_inf,
+                               const double* sched_host, int sched_len, int lanes, unsigned long long seed,
+                               unsigned long long vec_offset, double* est, double* n_used, double* err,
+                               int* attempts, int* stop_idx, void* stream);
+
 /* ---- q-means E-step ------------------------------------------------------ *
  * labels_estimation (sklearn/cluster/_dmeans.py:732-777) with ipe /
  * amplitude_estimation / median_evaluation (Utility.py:697-737, :442-531,

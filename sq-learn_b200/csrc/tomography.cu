@@ -29,6 +29,8 @@ struct TomoArgs {
     double* err;          // [B] ||V - est|| of the returned attempt
     double* trace;        // optional [B, sched_len, d]: the estimate of every attempt made
     int* attempts;        // optional [B]: number of attempts made
+    int* stop_idx;        // [B] speculative modes: index of the first attempt that met the accuracy
+    int spec;             // 0: attempts in order; 1: attempt lanes searching for stop_idx; 2: replay stop_idx
     double sched[128];    // attempt sizes N (integers stored as doubles), by value
     long long B;
     int d;
@@ -180,7 +182,19 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
 
     double n_last = 0.0, err_last = 0.0;
     int n_att = 0;
-    for (int at = 0; at < a.sched_len; ++at) {
+    // Speculative search (spec = 1): blockIdx.y is an attempt lane; lane g tries attempts g, g + G, ... and
+    // records the smallest successful index.  Attempts are independent fresh draws keyed by their index, so
+    // replaying the recorded attempt (spec = 2) returns exactly what the in-order loop would have returned.
+    __shared__ int s_cut;
+    int at0 = 0, step = 1, at_end = a.sched_len;
+    if (a.spec == 1) { at0 = blockIdx.y; step = gridDim.y; }
+    if (a.spec == 2) { at0 = min(a.stop_idx[b], a.sched_len - 1); at_end = at0 + 1; }
+    for (int at = at0; at < at_end; at += step) {
+        if (a.spec == 1) {
+            if (tid == 0) s_cut = *((volatile int*)&a.stop_idx[b]);
+            __syncthreads();
+            if (at > s_cut) break;          // an earlier attempt already succeeded
+        }
         const double N = a.sched[at];
         // Few measurements: draw them one by one (N/T categorical draws per thread, log2(d) probes each)
         // instead of walking the tree, whose log2(d) dependent binomial draws cost more than that.
@@ -249,8 +263,14 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
             double* tr = a.trace + (b * a.sched_len + at) * (long long)d;
             for (int i = tid; i < d; i += T) tr[i] = P[i];
         }
+        if (a.spec == 1) {
+            if (e <= a.delta) { if (tid == 0) atomicMin(&a.stop_idx[b], at); break; }
+            continue;
+        }
         if (a.stop && e <= a.delta) break;  // e is identical in every thread
     }
+    if (a.spec == 1) return;
+    if (a.spec == 2) n_att = at0 + 1;
     __syncthreads();
     for (int i = tid; i < d; i += T) a.est[b * (long long)d + i] = P[i];
     if (tid == 0) { a.n_used[b] = n_last; a.err[b] = err_last; if (a.attempts) a.attempts[b] = n_att; }
@@ -471,6 +491,7 @@ extern "C" int sq_tomography_batched(const double* V, long long B, int d, double
     if (B == 0) return SQ_OK;
     TomoArgs a;
     a.V = V; a.est = est; a.n_used = n_used; a.err = err; a.trace = trace; a.attempts = attempts;
+    a.stop_idx = nullptr; a.spec = 0;
     for (int i = 0; i < sched_len; ++i) {
         SQ_REQUIRE(sched_host[i] >= 1.0 && sched_host[i] < 9.0e15, "sq_tomography_batched: schedule entry out of range");
         a.sched[i] = sched_host[i];
@@ -573,5 +594,50 @@ extern "C" int sq_tomography_batched_ws(const double* V, long long B, int d, dou
         tomo_big_finish_kernel<<<(unsigned)B, 256, 0, stream>>>(a);
         SQ_LAUNCH_CHECK("tomo_big kernels");
     }
+    return SQ_OK;
+}
+
+// ---- incremental mode with speculative attempt lanes -----------------------------------------
+__global__ void tomo_fill_int_kernel(int* p, long long n, int v) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+extern "C" int sq_tomography_batched_spec(const double* V, long long B, int d, double delta, int norm_inf,
+                                          const double* sched_host, int sched_len, int lanes, unsigned long long seed,
+                                          unsigned long long vec_offset, double* est, double* n_used, double* err,
+                                          int* attempts, int* stop_idx, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(V && est && n_used && err && sched_host && stop_idx, "sq_tomography_batched_spec: null pointer");
+    SQ_REQUIRE(B >= 0 && B <= 65535 && d >= 1, "sq_tomography_batched_spec: bad shape B=%lld d=%d", B, d);
+    SQ_REQUIRE(sched_len >= 1 && sched_len <= 128, "sq_tomography_batched_spec: sched_len=%d outside [1,128]", sched_len);
+    SQ_REQUIRE(lanes >= 1 && lanes <= 64, "sq_tomography_batched_spec: lanes=%d outside [1,64]", lanes);
+    SQ_REQUIRE(delta > 0.0, "sq_tomography_batched_spec: delta must be > 0");
+    if (d > sq_tomography_max_fused_dim()) {
+        set_error("sq_tomography_batched_spec: d=%d exceeds the fused-path limit %d", d, sq_tomography_max_fused_dim());
+        return SQ_ERR_UNSUPPORTED;
+    }
+    if (B == 0) return SQ_OK;
+    TomoArgs a;
+    a.V = V; a.est = est; a.n_used = n_used; a.err = err; a.trace = nullptr; a.attempts = attempts;
+    a.stop_idx = stop_idx;
+    for (int i = 0; i < sched_len; ++i) {
+        SQ_REQUIRE(sched_host[i] >= 1.0 && sched_host[i] < 9.0e15, "sq_tomography_batched_spec: schedule entry out of range");
+        a.sched[i] = sched_host[i];
+    }
+    a.B = B; a.d = d;
+    int L = 2, logL = 1;
+    while (L < d) { L <<= 1; ++logL; }
+    a.L = L; a.logL = logL; a.sched_len = sched_len; a.norm_inf = norm_inf; a.stop = 1; a.delta = delta;
+    a.seed = seed; a.vec_offset = vec_offset;
+    int threads = L < 32 ? 32 : (L > 512 ? 512 : L);
+    size_t smem = (size_t)(6 * L + 32) * sizeof(double);
+    SQ_CUDA(cudaFuncSetAttribute(tomo_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tomo_fill_int_kernel<<<(unsigned)((B + 255) / 256), 256, 0, stream>>>(stop_idx, B, sched_len);
+    a.spec = 1;
+    tomo_fused_kernel<<<dim3((unsigned)B, lanes), threads, smem, stream>>>(a);
+    a.spec = 2;
+    tomo_fused_kernel<<<(unsigned)B, threads, smem, stream>>>(a);
+    SQ_LAUNCH_CHECK("tomo_fused_kernel (speculative)");
     return SQ_OK;
 }

@@ -261,6 +261,14 @@ def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, v
                 dv.ptr(est[b0:b1]), dv.ptr(n_used[b0:b1]), dv.ptr(err[b0:b1]), dv.ptr(ws), nb, dv.stream_ptr()),
                 "sq_tomography_batched_ws")
         return est, n_used, err, tr, att, sched
+    if stop and incremental and len(sched) > 1 and not trace and B <= 2048:
+        # few vectors: the latency of the attempt-by-attempt search dominates; search 8 attempts at a time
+        scratch = dv.empty((B,), dtype=torch.int32)
+        _cabi.check(_cabi.lib.sq_tomography_batched_spec(
+            dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, sched.ctypes.data, len(sched), 8, seed_,
+            vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err), None, dv.ptr(scratch), dv.stream_ptr()),
+            "sq_tomography_batched_spec")
+        return est, n_used, err, tr, att, sched
     _cabi.check(_cabi.lib.sq_tomography_batched(
         dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, 1 if (stop and incremental) else 0,
         sched.ctypes.data, len(sched), seed_, vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err),

@@ -260,3 +260,31 @@ def test_long_vector_public_api(cuda):
     assert np.linalg.norm(out[0] - vn) <= 0.4 and np.linalg.norm(out[1] + vn) <= 0.4
     res = Q.real_tomography(v, delta=0.4)
     assert len(res) == 1 and np.linalg.norm(np.asarray(list(res.values())[0]) - vn) <= 0.4
+
+
+def test_speculative_lanes_equal_the_in_order_search(cuda):
+    """the attempt-lane search returns exactly what the sequential loop returns"""
+    import torch
+    from oracle import quantum_utility as qu
+    from sqlearn import _cabi, _device as dv
+    import gpu_util as G
+    rs = np.random.RandomState(11)
+    for B, d, delta in [(64, 128, 0.25), (7, 1000, 0.2), (300, 16, 0.3), (5, 3, 0.01)]:
+        V = rs.uniform(-1, 1, (B, d))
+        V[0] = 0.0                                    # a zero vector in the batch
+        sched = qu.schedule(max(qu.tomography_N(d, delta), 50)).astype(float)
+        want = G.tomography(V, delta, sched, stop=1, seed=77, vec_offset=5)
+        Vd = torch.as_tensor(V).cuda()
+        est = torch.empty_like(Vd)
+        n_used = torch.empty(B, dtype=torch.float64, device="cuda")
+        err = torch.empty(B, dtype=torch.float64, device="cuda")
+        att = torch.zeros(B, dtype=torch.int32, device="cuda")
+        scratch = torch.zeros(B, dtype=torch.int32, device="cuda")
+        for lanes in (1, 8, 13):
+            _cabi.check(_cabi.lib.sq_tomography_batched_spec(
+                Vd.data_ptr(), B, d, delta, 0, sched.ctypes.data, len(sched), lanes, 77, 5, est.data_ptr(),
+                n_used.data_ptr(), err.data_ptr(), att.data_ptr(), scratch.data_ptr(), dv.stream_ptr()), "spec")
+            torch.cuda.synchronize()
+            assert np.array_equal(est.cpu().numpy(), want[0])
+            assert np.array_equal(n_used.cpu().numpy(), want[1])
+            assert np.array_equal(err.cpu().numpy(), want[2])
