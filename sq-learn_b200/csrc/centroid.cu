@@ -124,18 +124,38 @@ __global__ void label_scan_kernel(int* __restrict__ hist, int W, int* __restrict
     if (tid == 0) totals[j] = carry_s;
 }
 
-// ---- 3. label bases and item offsets (single block, k small) -----------------
+// ---- 3. label bases and item offsets: two exclusive scans over k in one block ----------------
 __global__ void label_base_kernel(const int* totals, int k, int* base, int* item_off, double* counts, int ITEM_ROWS) {
-    if (threadIdx.x == 0) {
-        int b = 0, it = 0;
-        for (int j = 0; j < k; ++j) {
-            int c = totals[j];
-            base[j] = b; item_off[j] = it;
-            if (counts) counts[j] = (double)c;
-            b += c; it += (c + ITEM_ROWS - 1) / ITEM_ROWS;
+    __shared__ int wsum_c[32], wsum_i[32];
+    __shared__ int carry_c, carry_i;
+    const int tid = threadIdx.x, lane = tid & 31, wl = tid >> 5, nw = blockDim.x >> 5;
+    if (tid == 0) { carry_c = 0; carry_i = 0; }
+    __syncthreads();
+    for (int j0 = 0; j0 < k; j0 += blockDim.x) {
+        const int j = j0 + tid;
+        const int c = (j < k) ? totals[j] : 0;          // read before base[j] is overwritten (totals may alias base)
+        const int it = (c + ITEM_ROWS - 1) / ITEM_ROWS;
+        int xc = c, xi = it;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int yc = __shfl_up_sync(0xffffffffu, xc, o), yi = __shfl_up_sync(0xffffffffu, xi, o);
+            if (lane >= o) { xc += yc; xi += yi; }
         }
-        base[k] = b; item_off[k] = it;
+        if (lane == 31) { wsum_c[wl] = xc; wsum_i[wl] = xi; }
+        __syncthreads();
+        int oc = carry_c, oi = carry_i;
+        for (int w = 0; w < wl; ++w) { oc += wsum_c[w]; oi += wsum_i[w]; }
+        if (j < k) {
+            base[j] = oc + xc - c;
+            item_off[j] = oi + xi - it;
+            if (counts) counts[j] = (double)c;
+        }
+        __syncthreads();
+        if (tid == blockDim.x - 1) { carry_c = oc + xc; carry_i = oi + xi; }
+        __syncthreads();
+        (void)nw;
     }
+    if (tid == 0) { base[k] = carry_c; item_off[k] = carry_i; }
 }
 
 // ---- 4. stable scatter of row indices into label buckets ---------------------
@@ -315,7 +335,7 @@ extern "C" int sq_centroid_accumulate(const double* X, const int* labels, long l
     label_scan_kernel<<<k, 256, 0, stream>>>(w.hist, g.W, w.base);
     SQ_LAUNCH_CHECK("label_scan_kernel");
     // base[] holds the totals on entry; the kernel reads totals[j] before it writes base[j]
-    label_base_kernel<<<1, 32, 0, stream>>>(w.base, k, w.base, w.item_off, counts, g.item_rows);
+    label_base_kernel<<<1, 256, 0, stream>>>(w.base, k, w.base, w.item_off, counts, g.item_rows);
     SQ_LAUNCH_CHECK("label_base_kernel");
     label_scatter_kernel<<<g.blocks, 32 * CW_WARPS_PER_BLOCK, sh, stream>>>(labels, n, k, g.rows_per_warp, g.W, w.hist, w.base, w.perm);
     SQ_LAUNCH_CHECK("label_scatter_kernel");

@@ -1,0 +1,127 @@
+"""Parity at the sizes BASELINE.json names.  Where the CPU oracle cannot finish the whole
+problem, row-independent pieces are checked on a random subsample and the rest through
+size-independent properties (linearity of the M-step, conservation of counts)."""
+import warnings
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _blobs(torch, n, d, k, spread, seed):
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+    cen = torch.randn((k, d), generator=g, device="cuda", dtype=torch.float64) * spread
+    X = torch.empty((n, d), dtype=torch.float64, device="cuda")
+    for a in range(0, n, 1 << 20):
+        b = min(n, a + (1 << 20))
+        X[a:b] = cen[torch.randint(0, k, (b - a,), generator=g, device="cuda")]
+        X[a:b] += torch.randn((b - a, d), generator=g, device="cuda", dtype=torch.float64)
+    return X
+
+
+def test_config1_qmeans_70000x784_k10_noiseless_bit_exact(cuda):
+    """BASELINE config 1 shape: three noiseless Lloyd iterations, labels bit-exact against the oracle"""
+    import torch
+    from oracle import qmeans as oq
+    from sqlearn.cluster._dmeans import _kmeans_single_lloyd
+    from sqlearn.cluster._engine import QMeansEngine
+    X = _blobs(torch, 70000, 784, 10, 3.0, 1)
+    X -= X.mean(dim=0)
+    Xh = X.cpu().numpy()
+    C0 = Xh[np.random.RandomState(0).permutation(70000)[:10]].copy()
+    eng = QMeansEngine(X.contiguous(), 10)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        labels, inertia, centers, n_iter = _kmeans_single_lloyd(eng, None, torch.as_tensor(C0).cuda(), False, True, True,
+                                                                None, True, max_iter=3, tol=0, delta=0)
+    want = oq.kmeans_single_lloyd(Xh, C0, False, True, True, True, max_iter=3, tol=0, delta=0,
+                                  rng=np.random.default_rng(0))
+    assert np.array_equal(labels.cpu().numpy(), want[0])
+    np.testing.assert_allclose(centers.cpu().numpy(), want[2], rtol=1e-10, atol=1e-12)
+    assert inertia == pytest.approx(want[1], rel=1e-10)
+
+
+def test_config2_qpca_70000x784_singular_values(cuda):
+    """BASELINE config 2 shape: Gram-route singular values / vectors against LAPACK's SVD"""
+    import torch
+    from sqlearn.decomposition import qPCA
+    X = _blobs(torch, 70000, 784, 10, 3.0, 2).cpu().numpy()
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        m = qPCA(n_components=50, svd_solver='full').fit(X)
+    Xc = X - X.mean(axis=0)
+    U, S, Vt = np.linalg.svd(Xc, full_matrices=False)
+    np.testing.assert_allclose(m.singular_values_, S[:50], rtol=1e-10)
+    idx = np.argmax(np.abs(U[:, :50]), axis=0)
+    signs = np.sign(U[idx, range(50)])
+    np.testing.assert_allclose(m.components_, Vt[:50] * signs[:, None], rtol=0, atol=1e-8)
+    assert m.frob_norm == pytest.approx(np.linalg.norm(Xc), rel=1e-11)
+
+
+def test_config3_standin_delta_sweep(cuda):
+    """BASELINE config 3 (k = 15, delta sweep 0.1..1.0) on a synthetic stand-in: the bundled CSV is
+    not in the reference tree.  Every pick lies inside its delta window; inertia equals sum of minima."""
+    import torch
+    import gpu_util as G
+    from oracle import qmeans as oq
+    X = _blobs(torch, 100000, 78, 15, 1.0, 3)
+    X = ((X - X.mean(dim=0)) / X.std(dim=0)).cpu().numpy()
+    C = X[np.random.RandomState(0).permutation(len(X))[:15]]
+    sub = np.random.RandomState(1).permutation(len(X))[:5000]
+    D = oq.cdist_sq(X[sub], C)
+    mins = D.min(axis=1)
+    for delta in np.arange(0.1, 1.01, 0.1):
+        lab, mind, inertia, _ = G.assign(X, C, mode=1, delta=float(delta), seed=int(delta * 10))
+        assert (D[np.arange(5000), lab[sub]] <= mins + delta + 1e-9).all()
+        np.testing.assert_allclose(mind[sub], mins, rtol=1e-10, atol=1e-11)
+        assert inertia == pytest.approx(mind.sum(), rel=1e-12)
+
+
+def test_config4_10Mx128_k256_properties(cuda):
+    """BASELINE config 4 at full size (10M x 128, k = 256) on one GPU: E-step labels bit-exact on a
+    20,000-row subsample (rows are independent), M-step linearity and count conservation, and the
+    delta-window picks inside their windows."""
+    import torch
+    from oracle import qmeans as oq
+    from sqlearn.cluster import _dmeans as D
+    from sqlearn.cluster._engine import QMeansEngine
+    from sqlearn.QuantumUtility import Utility as U
+    n, d, k = 10_000_000, 128, 256
+    X = _blobs(torch, n, d, k, 4.0, 1234)
+    eng = QMeansEngine(X, k)
+    mean = eng.col_sums() / n
+    eng.subtract_rowvec(mean)
+    eng.refresh_norms()
+    C = X[torch.randperm(1 << 20, generator=torch.Generator().manual_seed(0))[:k].cuda()].clone()
+    sub = torch.randperm(n, generator=torch.Generator().manual_seed(1))[:20000].cuda()
+    Xs, Ch = X[sub].cpu().numpy(), C.cpu().numpy()
+    Dm = oq.cdist_sq(Xs, Ch)
+    U.seed(1)
+    labels, mind, inertia = D._labels_inertia(eng, C, delta=0, true_distance_estimate=True)
+    assert np.array_equal(labels[sub].cpu().numpy(), Dm.argmin(axis=1))
+    np.testing.assert_allclose(mind[sub].cpu().numpy(), Dm.min(axis=1), rtol=1e-10, atol=1e-10)
+    assert float(inertia.item()) == pytest.approx(float(mind.sum().item()), rel=1e-12)
+    # M-step: counts add up to n, the k sums add up to the column sums of X (linearity)
+    eng.accumulate()
+    assert float(eng.counts.sum().item()) == n
+    cs = eng.col_sums()
+    scale = float(X.abs().sum(dim=0).max().item())
+    assert float((eng.sums.sum(dim=0) - cs).abs().max().item()) <= 1e-10 * scale
+    # centres of the subsample's clusters against a NumPy mean over all their rows (two clusters)
+    lab_all = labels.cpu().numpy()
+    for j in (int(lab_all[0]), int(lab_all[-1])):
+        rows = torch.as_tensor(np.where(lab_all == j)[0]).cuda()
+        want = X[rows].sum(dim=0)
+        np.testing.assert_allclose(eng.sums[j].cpu().numpy(), want.cpu().numpy(), rtol=1e-10, atol=1e-8)
+    # delta-window picks
+    labels, mind, inertia = D._labels_inertia(eng, C, delta=0.5, true_distance_estimate=False)
+    ls = labels[sub].cpu().numpy()
+    assert (Dm[np.arange(20000), ls] <= Dm.min(axis=1) + 0.5 + 1e-9).all()
+    # centroid tomography at delta/2
+    c2 = torch.empty_like(C)
+    eng.finalize(C, c2)
+    est = U.tomography(c2, 0.25)
+    unit = c2 / c2.norm(dim=1, keepdim=True)
+    assert float((est - unit).norm(dim=1).max().item()) <= 0.25
