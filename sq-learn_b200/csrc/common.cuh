@@ -7,6 +7,7 @@
 // reductions, and the error plumbing behind the C ABI in include/sqb200.h.
 #pragma once
 
+#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched at run time, no libcuda link)
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -48,6 +49,9 @@ int cuda_fail(cudaError_t e, const char* what);
 #define SQ_LAUNCH_CHECK(what) SQ_CUDA(cudaPeekAtLastError())
 
 int device_sm_count();
+// 2-D tensor map over a row-major fp64 matrix [rows, cols] with a box of {box_cols, box_rows}; 0 = ok
+int make_tensor_map_2d(CUtensorMap* map, const double* base, unsigned long long cols, unsigned long long rows,
+                       unsigned box_cols, unsigned box_rows);
 
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
@@ -160,6 +164,38 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                  : "+d"(d0), "+d"(d1)
                  : "d"(a), "d"(b));
 }
+
+// ---------------------------------------------------------------------------
+// TMA / mbarrier helpers (sm_90+ PTX; SASS: UTMALDG, SYNCS)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_LOOP:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE;\n\t"
+        "bra WAIT_LOOP;\n\t"
+        "DONE:\n\t}"
+        ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity)
+        : "memory");
+}
+// one 2-D box: coordinates (c0 = element along the row, c1 = row)
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, unsigned long long* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(map), "r"(c0), "r"(c1),
+          "r"((unsigned)__cvta_generic_to_shared(bar))
+        : "memory");
+}
+
 #endif  // __CUDACC__
 
 }  // namespace sq

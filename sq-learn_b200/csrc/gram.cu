@@ -15,8 +15,15 @@
 // order (deterministic) and mirrored into the lower triangle.
 #include "common.cuh"
 #include "sqb200.h"
+#include <cstdlib>
 
 namespace sq {
+
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
+}
 
 static const int GB = 128;       // block of features
 static const int GR = 16;        // rows per chunk
@@ -140,6 +147,93 @@ __global__ void __launch_bounds__(GTHREADS, 1) gram_kernel(GramArgs a, int vec16
         }
 }
 
+// ---- TMA variant (no centring; d even, X 16-byte aligned) ------------------------------------
+// The X tile arrives as boxes {4 features, GT_R rows}: slab layout [feature/4][row][4], so the
+// (8 features x 4 rows) DMMA fragment of either operand is two runs of 128 contiguous bytes and
+// needs no padding.  One elected thread issues the boxes; completion on an mbarrier per stage.
+static const int GT_R = 32;        // rows per chunk
+static const int GT_STAGES = 3;
+__global__ void __launch_bounds__(GTHREADS, 1) gram_tma_kernel(GramArgs a, const __grid_constant__ CUtensorMap tm) {
+    extern __shared__ __align__(1024) double smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int wm = warp >> 2, wn = warp & 3;
+    const int lq = lane >> 2, lr4 = lane & 3;
+    int pr = blockIdx.x, bi = 0;
+    while (pr >= a.nblk - bi) { pr -= a.nblk - bi; ++bi; }
+    const int bj = bi + pr;
+    const bool diag = (bi == bj);
+    const int fi = bi * GB, fj = bj * GB;
+    const long long r0 = (long long)blockIdx.y * a.rows_per_slice;
+    long long rend = r0 + a.rows_per_slice;
+    if (rend > a.n) rend = a.n;
+    const int chunks = (int)((rend - r0 + GT_R - 1) / GT_R);
+    constexpr int HALF = GB * GT_R;            // doubles of one operand's tile
+    constexpr int STAGE = 2 * HALF;
+    unsigned long long* full_bar = (unsigned long long*)(smem + GT_STAGES * STAGE);
+    if (tid == 0) {
+        for (int s = 0; s < GT_STAGES; ++s) mbar_init(&full_bar[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+    // rows past rend inside the last chunk of a slice belong to the next slice: they must not be counted
+    // twice, so the slice length is a multiple of GT_R (host) and only the matrix end is ragged (zero fill).
+    auto issue = [&](int c) {
+        if (tid == 0 && c < chunks) {
+            double* st = smem + (c % GT_STAGES) * STAGE;
+            unsigned long long* bar = &full_bar[c % GT_STAGES];
+            mbar_expect_tx(bar, (diag ? HALF : STAGE) * 8);
+            const int row = (int)(r0 + (long long)c * GT_R);
+#pragma unroll 4
+            for (int g = 0; g < GB / 4; ++g) {
+                tma_load_2d(st + g * GT_R * 4, &tm, fi + g * 4, row, bar);
+                if (!diag) tma_load_2d(st + HALF + g * GT_R * 4, &tm, fj + g * 4, row, bar);
+            }
+        }
+    };
+    for (int s = 0; s < GT_STAGES - 1; ++s) issue(s);
+
+    double acc[4][4][2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+    const unsigned smem_u32 = (unsigned)__cvta_generic_to_shared(smem);
+    // fragment base: feature group (w*8 + i*2 + lq/4), row lr4, sub-feature lq%4
+    const unsigned fa = (unsigned)((((wm * 8 + (lq >> 2)) * GT_R + lr4) * 4 + (lq & 3)) * 8);
+    const unsigned fb = (unsigned)((((wn * 8 + (lq >> 2)) * GT_R + lr4) * 4 + (lq & 3)) * 8);
+    unsigned phase = 0;
+    for (int c = 0; c < chunks; ++c) {
+        const int stg = c % GT_STAGES;
+        mbar_wait(&full_bar[stg], phase);
+        if (stg == GT_STAGES - 1) phase ^= 1;
+        __syncthreads();                       // everyone is done with the stage refilled below
+        issue(c + GT_STAGES - 1);
+        const unsigned sa = smem_u32 + (unsigned)(stg * STAGE * 8) + fa;
+        const unsigned sb = smem_u32 + (unsigned)(stg * STAGE * 8) + (diag ? 0u : (unsigned)(HALF * 8)) + fb;
+#pragma unroll
+        for (int kb = 0; kb < GT_R / 4; ++kb) {
+            double af[4], bf[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) af[i] = lds_f64(sa + (unsigned)(((i * 2 * GT_R) + kb * 4) * 32));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bf[j] = lds_f64(sb + (unsigned)(((j * 2 * GT_R) + kb * 4) * 32));
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+        }
+    }
+    double* out = a.partial + ((long long)blockIdx.y * a.pairs + blockIdx.x) * (GB * GB);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            int r = wm * 32 + i * 8 + lq, cc = wn * 32 + j * 8 + lr4 * 2;
+            *reinterpret_cast<double2*>(out + r * GB + cc) = make_double2(acc[i][j][0], acc[i][j][1]);
+        }
+}
+
 __global__ void gram_combine_kernel(const double* __restrict__ partial, int slices, int pairs, int nblk, int d,
                                     double* __restrict__ G) {
     long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -200,7 +294,7 @@ static GramGeom gram_geom(long long n, int d) {
     long long maxs = (n + 4 * GR - 1) / (4 * GR);
     if (target > maxs) target = (int)maxs;
     if (target < 1) target = 1;
-    g.rows_per_slice = ((n + target - 1) / target + GR - 1) / GR * GR;
+    g.rows_per_slice = ((n + target - 1) / target + 31) / 32 * 32;   // multiple of both chunk sizes (16, 32)
     g.slices = (int)((n + g.rows_per_slice - 1) / g.rows_per_slice);
     return g;
 }
@@ -234,8 +328,18 @@ extern "C" int sq_gram_centered(const double* X, long long n, int d, const doubl
     size_t smem = (size_t)GSTAGES * 2 * GR * GSTRIDE * sizeof(double);
     SQ_CUDA(cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int vec16 = ((d & 1) == 0 && ((uintptr_t)X & 15) == 0) ? 1 : 0;
-    gram_kernel<<<dim3(g.pairs, g.slices), GTHREADS, smem, stream>>>(a, vec16);
-    SQ_LAUNCH_CHECK("gram_kernel");
+    CUtensorMap tm;
+    bool use_tma = vec16 && !mean && !getenv("SQ_GRAM_NO_TMA") &&
+                   make_tensor_map_2d(&tm, X, (unsigned long long)d, (unsigned long long)n, 4, GT_R) == 0;
+    if (use_tma) {
+        size_t sm2 = (size_t)GT_STAGES * 2 * GB * GT_R * sizeof(double) + GT_STAGES * sizeof(unsigned long long);
+        SQ_CUDA(cudaFuncSetAttribute(gram_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2));
+        gram_tma_kernel<<<dim3(g.pairs, g.slices), GTHREADS, sm2, stream>>>(a, tm);
+        SQ_LAUNCH_CHECK("gram_tma_kernel");
+    } else {
+        gram_kernel<<<dim3(g.pairs, g.slices), GTHREADS, smem, stream>>>(a, vec16);
+        SQ_LAUNCH_CHECK("gram_kernel");
+    }
     long long dd = (long long)d * d;
     gram_combine_kernel<<<(unsigned)((dd + 255) / 256), 256, 0, stream>>>(a.partial, g.slices, g.pairs, g.nblk, d, out_gram);
     SQ_LAUNCH_CHECK("gram_combine_kernel");

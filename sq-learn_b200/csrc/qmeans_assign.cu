@@ -31,7 +31,6 @@
 #include "fejer.cuh"
 #include <cstdlib>
 #include <cstring>
-#include <cuda.h>  // CUtensorMap (types only; the encoder is fetched at run time, no libcuda link)
 
 namespace sq {
 
@@ -131,35 +130,6 @@ __device__ __forceinline__ double lds_f64(unsigned addr) {
     return v;
 }
 __device__ __forceinline__ double dmin(double a, double b) { return b < a ? b : a; }  // no NaN handling needed here
-
-// ---- TMA / mbarrier helpers (sm_90+ PTX; SASS: UTMALDG, SYNCS) -----------------
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"((unsigned)__cvta_generic_to_shared(bar)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_LOOP:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE;\n\t"
-        "bra WAIT_LOOP;\n\t"
-        "DONE:\n\t}"
-        ::"r"((unsigned)__cvta_generic_to_shared(bar)), "r"(parity)
-        : "memory");
-}
-// one 2-D box: coordinates (c0 = element along the row, c1 = row)
-__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int c0, int c1, unsigned long long* bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
-        ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(map), "r"(c0), "r"(c1),
-          "r"((unsigned)__cvta_generic_to_shared(bar))
-        : "memory");
-}
 
 template <class Cfg, bool VEC16, int MODE, bool TMA>
 __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_kernel(AssignArgs a, const __grid_constant__ CUtensorMap tmA,
@@ -755,30 +725,6 @@ static bool g_prof_on = false;
 static cudaEvent_t g_prof_ev[2] = {nullptr, nullptr};
 static double g_prof_ms = 0.0;
 static long long g_prof_launches = 0;
-
-// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency,
-// so the library still loads on a machine without a driver).
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-static int make_tensor_map_2d(CUtensorMap* map, const double* base, unsigned long long cols, unsigned long long rows,
-                              unsigned box_cols, unsigned box_rows) {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || !p) return 1;
-        fn = (EncodeTiledFn)p;
-    }
-    cuuint64_t gdim[2] = {cols, rows};
-    cuuint64_t gstride[1] = {cols * sizeof(double)};
-    cuuint32_t box[2] = {box_cols, box_rows > 256 ? 256u : box_rows};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, (void*)base, gdim, gstride, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    return r == CUDA_SUCCESS ? 0 : 1;
-}
 
 template <class Cfg>
 static int launch_assign(AssignArgs a, cudaStream_t stream) {
