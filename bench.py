@@ -304,7 +304,10 @@ def run_b200(args):
         line["extra"] = extra_measurements(eng, centers, D, Q, _cabi, torch)
     # ---- e2e through the public API: qMeans_.fit on pinned host arrays ----
     if not args.no_e2e:
-        line["e2e"] = e2e_fit(args, X, mean, centers, eng, qMeans_, Q, torch, dist, world, device)
+        try:
+            line["e2e"] = e2e_fit(args, X, mean, centers, eng, qMeans_, Q, torch, dist, world, device)
+        except Exception as exc:      # e.g. the host cannot pin a copy of the shard
+            line["e2e"] = {"value": None, "unit": UNIT, "error": "%s: %s" % (type(exc).__name__, exc)}
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_iteration_rate(args.cpu_rows, 2, 1, mode, args.rows)
     if rank == 0:
@@ -351,7 +354,8 @@ def extra_measurements(eng, centers, D, Q, _cabi, torch):
     g = torch.Generator(device=centers.device)
     g.manual_seed(1234)
     for B, d, delta, incremental in [(4096, 1000, 0.1, False), (4096, 1000, 0.1, True), (65536, 128, 0.25, True),
-                                     (64, 4096, 0.05, False), (70000, 61, 0.1, True)]:
+                                     (64, 4096, 0.05, False), (70000, 61, 0.1, True), (64, 100000, 0.1, False),
+                                     (1, 1000000, 0.01, False), (1, 1000000, 0.5, True)]:
         V = torch.rand((B, d), generator=g, device=centers.device, dtype=torch.float64) * 2 - 1
         V /= V.norm(dim=1, keepdim=True)
         res = {}

@@ -187,6 +187,10 @@ int sq_gram_centered(const double* X, long long n, int d, const double* mean, do
  * (pass zeros for centred X).                                                            */
 int sq_project_absmax(const double* X, long long n, int d, const double* Vt, int r, const double* mu_v,
                       unsigned long long* out_key, void* stream);
+/* (X - mean) @ components.T of _BasePCA.transform (sklearn/decomposition/_base.py:117-128) on the fp64
+ * tensor cores: out[n, r] = X Vt^T - offset, offset[j] = mean.v_j (zeros for centred X).            */
+int sq_project(const double* X, long long n, int d, const double* Vt, int r, const double* offset, double* out,
+               void* stream);
 /* column sums of X (np.mean(X, axis=0) * n: _qPCA.py:578, _dmeans.py:1264) */
 size_t sq_col_sums_workspace_bytes(long long n, int d);
 int sq_col_sums(const double* X, long long n, int d, double* out, void* ws, size_t ws_bytes, void* stream);

@@ -34,7 +34,7 @@
 
 namespace sq {
 
-enum AssignMode { MODE_EXACT = 0, MODE_WINDOW = 1, MODE_IPE = 2, MODE_COLABS = 3 };
+enum AssignMode { MODE_EXACT = 0, MODE_WINDOW = 1, MODE_IPE = 2, MODE_COLABS = 3, MODE_STORE = 4 };
 
 struct AssignArgs {
     const double* X;       // [n, d]
@@ -47,6 +47,7 @@ struct AssignArgs {
     double* rowmin_out;    // [n]   optional raw min (EXACT)
     int* flag_count;       // [1]   number of near-tie rows
     int* flag_rows;        // [n]   their indices
+    double* store;         // [n, k] MODE_STORE: x_i.c_j - cnorm[j]
     unsigned long long* colkey;  // [k] MODE_COLABS: max over rows of (bits(|y|) with the sign of y in bit 0)
     long long n;
     int d, k;
@@ -309,6 +310,24 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                         unsigned long long k1 = ((unsigned long long)__double_as_longlong(fabs(y1)) & ~1ull) | (y1 < 0.0 ? 1ull : 0ull);
                         colbest[j][0] = k0 > colbest[j][0] ? k0 : colbest[j][0];
                         colbest[j][1] = k1 > colbest[j][1] ? k1 : colbest[j][1];
+                    }
+                    acc[i][j][0] = acc[i][j][1] = 0.0;
+                }
+            }
+        } else if (kc == a.KC - 1 && MODE == MODE_STORE) {
+            // plain projection: Y[i, j] = x_i.c_j - offset[j] written out (qPCA.transform, _base.py:117-128)
+            const long long tile = (long long)blockIdx.x + (long long)tl * gridDim.x;
+            const long long r0 = tile * BM;
+            const int colbase = nt * BN + wn * Cfg::WN + lr4 * 2;
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                const long long gr = r0 + wm * Cfg::WM + i * 8 + lq;
+#pragma unroll
+                for (int j = 0; j < NI; ++j) {
+                    const int col = colbase + j * 8;
+                    if (gr < a.n) {
+                        if (col < a.k) a.store[gr * a.k + col] = acc[i][j][0] - cn_s[col];
+                        if (col + 1 < a.k) a.store[gr * a.k + col + 1] = acc[i][j][1] - cn_s[col + 1];
                     }
                     acc[i][j][0] = acc[i][j][1] = 0.0;
                 }
@@ -766,17 +785,20 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT, true);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW, true);
         else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(true, MODE_IPE, true);
-        else SQ_LAUNCH_ASSIGN(true, MODE_COLABS, true);
+        else if (a.mode == MODE_COLABS) SQ_LAUNCH_ASSIGN(true, MODE_COLABS, true);
+        else SQ_LAUNCH_ASSIGN(true, MODE_STORE, true);
     } else if (vec16) {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT, false);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW, false);
         else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(true, MODE_IPE, false);
-        else SQ_LAUNCH_ASSIGN(true, MODE_COLABS, false);
+        else if (a.mode == MODE_COLABS) SQ_LAUNCH_ASSIGN(true, MODE_COLABS, false);
+        else SQ_LAUNCH_ASSIGN(true, MODE_STORE, false);
     } else {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(false, MODE_EXACT, false);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(false, MODE_WINDOW, false);
         else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(false, MODE_IPE, false);
-        else SQ_LAUNCH_ASSIGN(false, MODE_COLABS, false);
+        else if (a.mode == MODE_COLABS) SQ_LAUNCH_ASSIGN(false, MODE_COLABS, false);
+        else SQ_LAUNCH_ASSIGN(false, MODE_STORE, false);
     }
 #undef SQ_LAUNCH_ASSIGN
     if (g_prof_on) {
@@ -980,4 +1002,20 @@ extern "C" int sq_project_absmax(const double* X, long long n, int d, const doub
         if (rcode) return rcode;
     }
     return SQ_OK;
+}
+
+// ---------------------------------------------------------------------------
+// Projection Y = X Vt^T - offset on the fp64 tensor cores (qPCA.transform)
+// ---------------------------------------------------------------------------
+extern "C" int sq_project(const double* X, long long n, int d, const double* Vt, int r, const double* offset,
+                          double* out, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(X && Vt && offset && out, "sq_project: null pointer");
+    SQ_REQUIRE(n >= 1 && n < 2147483647LL && d >= 1 && r >= 1, "sq_project: bad shape n=%lld d=%d r=%d", n, d, r);
+    AssignArgs a;
+    memset(&a, 0, sizeof(a));
+    a.X = X; a.C = Vt; a.cnorm = offset; a.store = out;
+    a.n = n; a.d = d; a.k = r; a.mode = MODE_STORE;
+    int bn = 0;
+    return dispatch_assign(a, stream, &bn);
 }

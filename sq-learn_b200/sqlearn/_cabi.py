@@ -49,6 +49,7 @@ SIGNATURES = {
     "sq_binomial_sample": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_ull, c_ull, c_void_p, c_void_p]),
     "sq_mu_norms_workspace_bytes": (c_size_t, [c_ll, c_int, c_int]),
     "sq_project_absmax": (c_int, [c_void_p, c_ll, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
+    "sq_project": (c_int, [c_void_p, c_ll, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "sq_gram_workspace_bytes": (c_size_t, [c_ll, c_int]),
     "sq_gram_centered": (c_int, [c_void_p, c_ll, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "sq_col_sums_workspace_bytes": (c_size_t, [c_ll, c_int]),

@@ -236,7 +236,10 @@ class qPCA(_BasePCA):
         self.singular_values_ = singular_values_[:n_components]
         # first n_components ROWS of U (reference :631), from this rank's first rows
         k_rows = min(int(n_components), Xd.shape[0])
-        U_rows = torch.matmul(Xd[:k_rows], Vt_d.T) / torch.clamp(S_d, min=1e-300)[None, :]
+        U_rows = dv.empty((k_rows, Vt_d.shape[0]))
+        _cabi.check(_cabi.lib.sq_project(dv.ptr(Xd), k_rows, n_features, dv.ptr(Vt_d), Vt_d.shape[0],
+                                         dv.ptr(torch.zeros_like(S_d)), dv.ptr(U_rows), dv.stream_ptr()), "sq_project")
+        U_rows = U_rows / torch.clamp(S_d, min=1e-300)[None, :]
         self.left_sv = U_rows.cpu().numpy()
         self.spectral_norm = self.singular_values_[0]
         self.frob_norm = frob
@@ -391,9 +394,9 @@ class qPCA(_BasePCA):
             if epsilon_delta != 0 or quantum_representation or norm or psi != 0:
                 warnings.warn("Warning! You are using the classical transform, so the quantum parameter are useless.")
             return super().transform(X)
-        X_final = super().transform(X, use_classical_components)
         if use_classical_components == False:  # noqa: E712
-            return X_final
+            return super().transform(X, use_classical_components)
+        X_final = self._transform_device(X, use_classical_components)       # stays on the GPU
         if quantum_representation:
             assert (psi > 0 if norm != 'est_representation' else psi >= 0)
             assert (epsilon_delta > 0)
@@ -409,6 +412,8 @@ class qPCA(_BasePCA):
         if true_tomography == False:  # noqa: E712
             epsilon_delta = np.sqrt(self.n_components_) * (epsilon_delta)
         A_sign = tomography(U, epsilon_delta, true_tomography=true_tomography)
+        if isinstance(U, torch.Tensor):
+            return A_sign.cpu().numpy(), epsilon_delta, float(torch.linalg.norm(U - A_sign).item())
         f_norm = np.linalg.norm(U - A_sign)
         return A_sign, epsilon_delta, f_norm
 
@@ -416,7 +421,9 @@ class qPCA(_BasePCA):
         """The four representations of _qPCA.py:859-880."""
         if type == 'est_representation':
             return self.compute_error(X, epsilon_delta, true_tomography)
-        elif type == 'q_state':
+        if isinstance(X, torch.Tensor):
+            X = X.cpu().numpy()
+        if type == 'q_state':
             Y_sign = tomography(X, psi, true_tomography=true_tomography)
             f_norm = np.linalg.norm(Y_sign)
             norm_Y = [np.linalg.norm(Y_sign[i, :], ord=2) / f_norm for i in range(len(Y_sign))]
