@@ -18,12 +18,23 @@
 namespace sq {
 
 // Stirling series remainder: log(k!) - [ (k+1/2) log(k+1) - (k+1) + log(sqrt(2 pi)) ]
+#ifdef __CUDACC__
+__constant__ const double kStirlingTailDev[10] = {0.08106146679532726, 0.04134069595540929, 0.02767792568499834,
+                                                  0.02079067210376509, 0.01664469118982119, 0.01387612882307075,
+                                                  0.01189670994589177, 0.01041126526197209, 0.009255462182712733,
+                                                  0.008330563433362871};
+#endif
 __host__ __device__ inline double stirling_tail(double k) {
-    const double tab[10] = {0.08106146679532726, 0.04134069595540929, 0.02767792568499834,
-                            0.02079067210376509, 0.01664469118982119, 0.01387612882307075,
-                            0.01189670994589177, 0.01041126526197209, 0.009255462182712733,
-                            0.008330563433362871};
-    if (k <= 9.0) return tab[(int)k];
+    if (k <= 9.0) {
+#ifdef __CUDA_ARCH__
+        return kStirlingTailDev[(int)k];
+#else
+        const double tab[10] = {0.08106146679532726, 0.04134069595540929, 0.02767792568499834, 0.02079067210376509,
+                                0.01664469118982119, 0.01387612882307075, 0.01189670994589177, 0.01041126526197209,
+                                0.009255462182712733, 0.008330563433362871};
+        return tab[(int)k];
+#endif
+    }
     double kp1 = k + 1.0;
     double kp1sq = kp1 * kp1;
     return (1.0 / 12.0 - (1.0 / 360.0 - 1.0 / 1260.0 / kp1sq) / kp1sq) / kp1;
