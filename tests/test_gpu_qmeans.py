@@ -149,31 +149,57 @@ def test_window_mode_law_and_support(cuda, golden_stoch):
             assert stats.binomtest(int(hits), len(two), 0.5).pvalue > P_MIN
 
 
-def test_ipe_mode_distance_law(cuda, golden_stoch):
-    """k = 1: the reported min distance IS the IPE-estimated distance |x|^2+|c|^2-2*ipe(x,c)."""
+def _ipe_distance_pmf(x, y, eps):
+    """exact law of |x|^2+|y|^2-2*ipe(x,y,eps): median of 13 amplitude-estimation outcomes (closed-form pmf)"""
+    from oracle import quantum_utility as qu
+    from scipy import stats as st
+    S = x @ x + y @ y
+    inner = x @ y
+    a = (S - 2 * inner) / (2 * S)
+    M = qu.ae_M(eps * max(1, abs(inner)) / S)
+    pmf = qu.ae_pmf(a, M)
+    at = np.round(np.sin(np.pi * np.arange(M) / M) ** 2, 12)
+    vals = np.unique(at)
+    single = np.array([pmf[at == v].sum() for v in vals])
+    G = np.cumsum(single)
+    med_cdf = st.binom.sf(6, 13, np.clip(G, 0, 1))        # P(at least 7 of 13 draws <= v)
+    med_pmf = np.diff(np.concatenate([[0.0], med_cdf]))
+    return 2 * S * vals, med_pmf
+
+
+@pytest.mark.parametrize("mode", [2, 5])
+def test_ipe_mode_distance_law(cuda, golden_stoch, mode):
+    """k = 1: the reported min distance IS the IPE-estimated distance |x|^2+|c|^2-2*ipe(x,c).  Checked against
+    the exact law (closed-form amplitude-estimation pmf -> median of 13) and against the reference's draws."""
     import gpu_util as G
-    n = 4000
+    n = 20000
     x = golden_stoch["ipe_x"]
-    for ykey, rkey, spread in (("ipe_y", "ipe_draws_e0.25", False), ("ipe_y2", "ipe2_draws_e0.25", True)):
+    for ykey, rkey in (("ipe_y", "ipe_draws_e0.25"), ("ipe_y2", "ipe2_draws_e0.25")):
         y, ref = golden_stoch[ykey], golden_stoch[rkey]
-        _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), y[None], mode=2, delta=0.5, seed=3)
+        _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), y[None], mode=mode, delta=0.5, seed=3)
+        support, pmf = _ipe_distance_pmf(x, y, 0.25)
+        idx = np.array([np.argmin(np.abs(support - v)) for v in mind])
+        assert np.allclose(support[idx], mind, rtol=1e-9, atol=1e-9)        # every value is a grid value
+        obs = np.bincount(idx, minlength=len(support)).astype(float)
+        big = pmf * n >= 8
+        o = np.append(obs[big], obs[~big].sum())
+        e = np.append(pmf[big], pmf[~big].sum()) * n
+        keep = e > 0
+        assert stats.chisquare(o[keep], e[keep] * o[keep].sum() / e[keep].sum()).pvalue > P_MIN
+        # the reference's own draws follow the same law
         ref_d = x @ x + y @ y - 2 * ref
-        vals = np.unique(np.round(ref_d, 9))
-        if spread:
-            assert len(vals) >= 2 and len(np.unique(np.round(mind, 9))) >= 2
-        # same support, same frequencies
-        tab = np.stack([[np.isclose(mind, v, rtol=1e-9).sum() for v in vals],
-                        [np.isclose(ref_d, v, rtol=1e-9).sum() for v in vals]])
-        assert tab[0].sum() == n
-        if len(vals) > 1:
-            assert stats.chi2_contingency(tab[:, tab.sum(axis=0) > 0])[1] > P_MIN
+        ridx = np.array([np.argmin(np.abs(support - v)) for v in ref_d])
+        robs = np.bincount(ridx, minlength=len(support)).astype(float)
+        ro = np.append(robs[big], robs[~big].sum())
+        assert stats.chisquare(ro[keep], e[keep] * ro[keep].sum() / e[keep].sum()).pvalue > P_MIN
 
 
-def test_ipe_mode_label_law(cuda, golden_stoch):
+@pytest.mark.parametrize("mode", [2, 5])
+def test_ipe_mode_label_law(cuda, golden_stoch, mode):
     import gpu_util as G
     X, C, ref_lab = golden_stoch["ipe_X"], golden_stoch["ipe_C"], golden_stoch["ipe_labels"]
     reps = 200
-    labels, _, _, _ = G.assign(np.tile(X, (reps, 1)), C, mode=2, delta=0.5, seed=4)
+    labels, _, _, _ = G.assign(np.tile(X, (reps, 1)), C, mode=mode, delta=0.5, seed=4)
     mine = labels.reshape(reps, len(X))
     tab = np.stack([np.bincount(mine.ravel(), minlength=3) / reps * len(ref_lab),
                     np.bincount(ref_lab.ravel(), minlength=3)])
@@ -251,3 +277,30 @@ def test_device_kmeans_plusplus_equals_host_version(cuda):
         got = _kmeans_plusplus_device(eng, k, r2).cpu().numpy()
         np.testing.assert_array_equal(got, want)
         assert r1.random_sample() == r2.random_sample()      # both generators are in the same state
+
+
+def test_pruned_ipe_has_the_law_of_full_ipe(cuda):
+    """mode 5 (pruned) against mode 2 (every pair sampled) on clustered data, several tile shapes: same label
+    frequencies per row group and the same distribution of the reported minimum distance"""
+    import gpu_util as G
+    rs = np.random.RandomState(5)
+    for n, d, k, spread in [(4000, 16, 12, 2.0), (3000, 64, 200, 1.0), (2000, 8, 40, 0.7)]:
+        cen = rs.randn(k, d) * spread
+        base = cen[rs.randint(0, k, 40)] + 0.3 * rs.randn(40, d)      # 40 distinct points, each repeated
+        X = np.repeat(base, n // 40, axis=0)
+        l2, m2, _, _ = G.assign(X, cen, mode=2, delta=0.5, seed=11)
+        l5, m5, _, _ = G.assign(X, cen, mode=5, delta=0.5, seed=12)
+        reps = n // 40
+        worst = 1.0
+        for g in range(40):
+            a, b = l2[g * reps:(g + 1) * reps], l5[g * reps:(g + 1) * reps]
+            labs = np.union1d(a, b)
+            if len(labs) > 1:
+                tab = np.stack([[np.sum(a == v) for v in labs], [np.sum(b == v) for v in labs]])
+                tab = tab[:, tab.sum(axis=0) >= 5]
+                if tab.shape[1] > 1:
+                    worst = min(worst, stats.chi2_contingency(tab)[1])
+            ma, mb = m2[g * reps:(g + 1) * reps], m5[g * reps:(g + 1) * reps]
+            if len(np.unique(np.round(ma, 9))) > 1:
+                worst = min(worst, stats.ks_2samp(ma, mb).pvalue)
+        assert worst > 1e-5          # 80 tests per shape: Bonferroni-style floor
