@@ -29,6 +29,7 @@
 #include "common.cuh"
 #include "sqb200.h"
 #include "fejer.cuh"
+#include "ipe.cuh"
 #include "binomial.cuh"
 #include <cstdlib>
 #include <cmath>
@@ -499,12 +500,10 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
 #pragma unroll
                         for (int e = 0; e < 2; ++e) {
                             int col = colbase + j * 8 + e;
-                            double v = INFINITY;
-                            if (gr < a.n && col < a.k) {
-                                Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x1bE0u, (unsigned)col);
-                                v = ipe_distance(acc[i][j][e], xn, cn_s[col], 0.5 * a.delta, rng) - xn;
-                            }
-                            acc[i][j][e] = v;
+                            const bool ok = gr < a.n && col < a.k;
+                            const double v = ipe_estimate_warp(acc[i][j][e], xn, ok ? cn_s[col] : 0.0, 0.5 * a.delta, ok,
+                                                               a.seed, a.offset + (unsigned long long)gr, (unsigned)col);
+                            acc[i][j][e] = ok ? v - xn : INFINITY;
                         }
                 }
             }

@@ -304,3 +304,42 @@ def test_pruned_ipe_has_the_law_of_full_ipe(cuda):
             if len(np.unique(np.round(ma, 9))) > 1:
                 worst = min(worst, stats.ks_2samp(ma, mb).pvalue)
         assert worst > 1e-5          # 80 tests per shape: Bonferroni-style floor
+
+
+IPE_REGIMES = [
+    # (x, c, delta): regimes of the amplitude-estimation grid (M points, true position x_grid = M*theta/pi)
+    ((3.0, 0.0), (3.05, 0.1), 0.5),          # a ~ 0: the window wraps around grid point 0
+    ((3.0, 0.0), (3.0, 0.0), 0.5),           # a = 0: deterministic
+    ((30.0, 0.0), (0.0, 25.0), 0.5),         # orthogonal, large norms: M ~ 2e4, x_grid = M/4
+    ((2.0, 0.0), (-2.1, 0.05), 0.5),         # a ~ 1: the window straddles M/2
+    ((1.0, 0.2), (0.9, 0.5), 3.0),           # M <= 9: whole grid enumerated
+    ((1.0, 0.2), (0.9, 0.5), 1.5),           # M ~ 12: one or two tail cells per side
+    ((1.0, 0.2), (0.7, -0.5), 1.0),          # M ~ 20
+    ((5.0, 1.0), (1.0, 0.3), 0.5),           # generic, M ~ 100
+    ((0.3, 0.1), (0.2, -0.4), 0.2),          # |dot| < 1
+    ((12.0, -3.0), (11.0, -2.0), 0.1),       # close pair, fine grid
+]
+
+
+@pytest.mark.parametrize("case", range(len(IPE_REGIMES)))
+def test_ipe_distance_law_regimes(cuda, case):
+    """k = 1, n identical rows: the reported distance is one IPE estimate per row; its law must be the exact
+    median-of-13 law of the reference's amplitude-estimation pmf in every regime of the grid"""
+    import gpu_util as G
+    xv, cv, delta = IPE_REGIMES[case]
+    x, c = np.array(xv), np.array(cv)
+    n = 30000
+    _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), c[None], mode=2, delta=delta, seed=21 + case)
+    support, pmf = _ipe_distance_pmf(x, c, delta / 2)
+    idx = np.array([np.argmin(np.abs(support - v)) for v in mind])
+    assert np.allclose(support[idx], mind, rtol=1e-9, atol=1e-9)
+    obs = np.bincount(idx, minlength=len(support)).astype(float)
+    big = pmf * n >= 8
+    o = np.append(obs[big], obs[~big].sum())
+    e = np.append(pmf[big], pmf[~big].sum()) * n
+    keep = e > 1e-9
+    if keep.sum() == 1:
+        assert o[keep][0] == n
+    else:
+        assert o[~keep].sum() == 0
+        assert stats.chisquare(o[keep], e[keep] * o[keep].sum() / e[keep].sum()).pvalue > P_MIN
