@@ -265,7 +265,7 @@ def run_b200(args):
     tot, cnt = (_cabi.ctypes.c_double)(), (_cabi.ctypes.c_longlong)()
     _cabi.lib.sq_profile_assign(2, None, None)
     for _ in range(max(3, min(args.steps, 10))):
-        D._labels_inertia(eng, centers, delta=delta, pool=None, true_distance_estimate=tde, unit_norm_centers=inter)
+        D._labels_inertia(eng, centers, delta=delta, pool=None, true_distance_estimate=tde)
     torch.cuda.synchronize()
     _cabi.lib.sq_profile_assign(0, _cabi.ctypes.byref(tot), _cabi.ctypes.byref(cnt))
     k_ms = tot.value / max(cnt.value, 1)
@@ -343,14 +343,8 @@ def extra_measurements(eng, centers, D, Q, _cabi, torch):
     out = {}
     for name, (delta, tde) in {"exact": (0.0, True), "window": (DELTA, False), "ipe": (DELTA, True)}.items():
         out["estep_%s_ms" % name] = _timed(
-            torch, lambda: D._labels_inertia(eng, centers, delta=delta, pool=None, true_distance_estimate=tde,
-                                             unit_norm_centers=True),
+            torch, lambda: D._labels_inertia(eng, centers, delta=delta, pool=None, true_distance_estimate=tde),
             2 if name == "ipe" else 3)
-    # mode 5 (pairs that cannot be the row minimum are not sampled); the estimator picks it only when the
-    # centres are plain means (intermediate_error=False), here it is timed on the same unit-norm centres
-    out["estep_ipe_pruned_ms"] = _timed(
-        torch, lambda: D._labels_inertia(eng, centers, delta=DELTA, pool=None, true_distance_estimate=True,
-                                         unit_norm_centers=False), 2)
     D._labels_inertia(eng, centers, delta=0.0, pool=None, true_distance_estimate=True)
     out["mstep_accumulate_ms"] = _timed(torch, eng.accumulate, 3)
     c2 = torch.empty_like(centers)

@@ -86,9 +86,8 @@ int sq_tomography_batched_spec(const double* V, long long B, int d, double delta
  * amplitude_estimation / median_evaluation (Utility.py:697-737, :442-531,
  * :534-572) and select_labels (_dmeans.py:2252-2257) fused in.
  * mode 0: exact argmin (delta == 0); 1: uniform pick in the delta window
- * (true_distance_estimate=False); 2: IPE-estimated distances (True); 5: the same law as 2 with
- * exact pruning - pairs whose estimate provably cannot be the row minimum are not sampled (pays off
- * when the centroids are well separated compared with delta; k <= 256, else it runs as mode 2).
+ * (true_distance_estimate=False); 2: IPE-estimated distances (True) - for every pair the median of the 13
+ * amplitude-estimation outcomes is drawn from its exact law (csrc/ipe.cuh).
  * xnorm[n] = ||x_i||^2 (sq_row_sqnorms).  Outputs: labels[n] int32,
  * mindist[n] (may be NULL), inertia[1] = sum_i min_j D_ij, n_fixed[1] (may be
  * NULL) = rows re-evaluated with the reference's exact arithmetic.          */

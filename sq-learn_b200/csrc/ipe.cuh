@@ -48,7 +48,7 @@ __device__ __noinline__ double ipe_tail_draw(double M, double t, double j0, uint
     // offsets: right m = 5 .. mhi (distance m - t), left m = -4 .. mlo (distance -m + t), mhi - mlo + 1 = M
     double half = floor((M - 1.0) * 0.5);
     double mlo = -half;
-    if (t > 0.5 && fmod(M, 2.0) != 0.0) mlo += 1.0;
+    if (t > 0.5 && M - 2.0 * floor(M * 0.5) != 0.0) mlo += 1.0;   // M odd
     const double mhi = mlo + M - 1.0;
     const double cntR = mhi - 4.0, cntL = -mlo - 3.0;      // cells on each side (>= 0)
     const double aR = 4.5 - t, aL = 3.5 + t;               // lower edge of the first cell
@@ -86,19 +86,30 @@ __device__ __noinline__ double ipe_tail_draw(double M, double t, double j0, uint
 
 static __constant__ double kIpeInv[14] = {0.0, 1.0, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7,
                                           1.0 / 8, 1.0 / 9, 1.0 / 10, 1.0 / 11, 1.0 / 12, 1.0 / 13};
+// kIpeBinom[k-1][i] = C(k+i-1, i)
+static __constant__ double kIpeBinom[13][13] = {
+    {1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0,},
+    {1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0, 8.0, 9.0, 10.0, 11.0, 12.0, 13.0,},
+    {1.0, 3.0, 6.0, 10.0, 15.0, 21.0, 28.0, 36.0, 45.0, 55.0, 66.0, 78.0, 91.0,},
+    {1.0, 4.0, 10.0, 20.0, 35.0, 56.0, 84.0, 120.0, 165.0, 220.0, 286.0, 364.0, 455.0,},
+    {1.0, 5.0, 15.0, 35.0, 70.0, 126.0, 210.0, 330.0, 495.0, 715.0, 1001.0, 1365.0, 1820.0,},
+    {1.0, 6.0, 21.0, 56.0, 126.0, 252.0, 462.0, 792.0, 1287.0, 2002.0, 3003.0, 4368.0, 6188.0,},
+    {1.0, 7.0, 28.0, 84.0, 210.0, 462.0, 924.0, 1716.0, 3003.0, 5005.0, 8008.0, 12376.0, 18564.0,},
+    {1.0, 8.0, 36.0, 120.0, 330.0, 792.0, 1716.0, 3432.0, 6435.0, 11440.0, 19448.0, 31824.0, 50388.0,},
+    {1.0, 9.0, 45.0, 165.0, 495.0, 1287.0, 3003.0, 6435.0, 12870.0, 24310.0, 43758.0, 75582.0, 125970.0,},
+    {1.0, 10.0, 55.0, 220.0, 715.0, 2002.0, 5005.0, 11440.0, 24310.0, 48620.0, 92378.0, 167960.0, 293930.0,},
+    {1.0, 11.0, 66.0, 286.0, 1001.0, 3003.0, 8008.0, 19448.0, 43758.0, 92378.0, 184756.0, 352716.0, 646646.0,},
+    {1.0, 12.0, 78.0, 364.0, 1365.0, 4368.0, 12376.0, 31824.0, 75582.0, 167960.0, 352716.0, 705432.0, 1352078.0,},
+    {1.0, 13.0, 91.0, 455.0, 1820.0, 6188.0, 18564.0, 50388.0, 125970.0, 293930.0, 646646.0, 1352078.0, 2704156.0}};
 
 // P(Binomial(n, F) >= k) = F^k sum_{i=0}^{n-k} C(k+i-1, i) (1-F)^i, 1 <= k <= n <= 13; nmk = n - k,
 // bound >= nmk is the trip count (uniform over the callers that run together)
 __device__ __forceinline__ double ipe_order_cdf(double F, int k, int nmk, int bound) {
     const double q = 1.0 - F;
-    double term = 1.0, sum = 1.0;
-    const double km1 = (double)(k - 1);
+    const double* cf = kIpeBinom[k - 1];
+    double sum = 0.0;
 #pragma unroll 1
-    for (int i = 1; i <= bound; ++i) {
-        // C(k+i-1, i) = C(k+i-2, i-1) (k+i-1)/i
-        term *= q * ((km1 + (double)i) * kIpeInv[i]);
-        sum += (i <= nmk) ? term : 0.0;
-    }
+    for (int i = bound; i >= 0; --i) sum = fma(sum, q, (i <= nmk) ? cf[i] : 0.0);
     double Fk = 1.0, p = F;
     int kk = k;
 #pragma unroll
@@ -109,7 +120,6 @@ __device__ __forceinline__ double ipe_order_cdf(double F, int k, int nmk, int bo
     }
     return Fk * sum;
 }
-
 
 // Replay path: the tail draws are regenerated from their keys, the window draws are sampled one by
 // one and everything is sorted.  Also serves grids too small for a window (M <= 9).
@@ -172,13 +182,43 @@ __device__ __noinline__ double ipe_estimate_warp(double dot, double xn, double c
         } else {
             status = FAST;
             const double st = sinpi(t), s2 = st * st, invM = 1.0 / M;
-            double acc = 0.0;
+            // p_i = (M sin(pi z_i / M))^2 at the offsets z_i = i - 3 - t
+            double pw[8];
+            if (M >= 32.0) {
+                // |pi z / M| < pi/8: M sin(pi z/M) = pi z P(u), u = (pi z/M)^2, Taylor to u^7 (next term < 2e-18)
+                const double piM = PI * invM;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const double ms = M * sinpi(((double)(i - 3) - t) * invM);
-                w[i] = s2 / (ms * ms);
-                acc += w[i];
+                for (int i = 0; i < 8; ++i) {
+                    const double z = (double)(i - 3) - t, y = z * piM, u = y * y;
+                    double P = -1.0 / 1307674368000.0;
+                    P = fma(P, u, 1.0 / 6227020800.0);
+                    P = fma(P, u, -1.0 / 39916800.0);
+                    P = fma(P, u, 1.0 / 362880.0);
+                    P = fma(P, u, -1.0 / 5040.0);
+                    P = fma(P, u, 1.0 / 120.0);
+                    P = fma(P, u, -1.0 / 6.0);
+                    P = fma(P, u, 1.0);
+                    const double ms = PI * z * P;
+                    pw[i] = ms * ms;
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const double ms = M * sinpi(((double)(i - 3) - t) * invM);
+                    pw[i] = ms * ms;
+                }
             }
+            // w_i = s2 / p_i with one division: prefix and suffix products
+            {
+                const double a01 = pw[0] * pw[1], a23 = pw[2] * pw[3], a45 = pw[4] * pw[5], a67 = pw[6] * pw[7];
+                const double lo4 = a01 * a23, hi4 = a45 * a67;
+                const double r = s2 / (lo4 * hi4);
+                const double rl = r * hi4, rh = r * lo4;          // s2 / lo4, s2 / hi4
+                const double r01 = rl * a23, r23 = rl * a01, r45 = rh * a67, r67 = rh * a45;   // s2 / a01, ...
+                w[0] = r01 * pw[1]; w[1] = r01 * pw[0]; w[2] = r23 * pw[3]; w[3] = r23 * pw[2];
+                w[4] = r45 * pw[5]; w[5] = r45 * pw[4]; w[6] = r67 * pw[7]; w[7] = r67 * pw[6];
+            }
+            double acc = ((w[0] + w[1]) + (w[2] + w[3])) + ((w[4] + w[5]) + (w[6] + w[7]));
             W = acc;
             // r-order of the window: increasing with the offset unless it straddles 0 or M/2
             sorted = (j0 >= 3.0) && (2.0 * (j0 + 4.0) <= M);

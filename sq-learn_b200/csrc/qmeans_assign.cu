@@ -37,8 +37,7 @@
 
 namespace sq {
 
-enum AssignMode { MODE_EXACT = 0, MODE_WINDOW = 1, MODE_IPE = 2, MODE_COLABS = 3, MODE_STORE = 4,
-                  MODE_IPEP = 5 /* IPE with exact pruning, chosen by the host for k <= one centroid tile */ };
+enum AssignMode { MODE_EXACT = 0, MODE_WINDOW = 1, MODE_IPE = 2, MODE_COLABS = 3, MODE_STORE = 4 };
 
 struct AssignArgs {
     const double* X;       // [n, d]
@@ -51,12 +50,6 @@ struct AssignArgs {
     double* rowmin_out;    // [n]   optional raw min (EXACT)
     int* flag_count;       // [1]   number of near-tie rows
     int* flag_rows;        // [n]   their indices
-    // IPE with exact pruning (see ipe_* below)
-    double ipe_cdf[14];    // CDF of Binomial(13, ipe_ppot)
-    double ipe_q;          // P(at least 7 of the 13 draws are potential tail draws)
-    double ipe_ppot;       // upper bound of the mass outside the 8-point window, valid for M >= ipe_Mmin
-    double ipe_Mmin;       // smallest grid size M of any pair with |x|^2+|c|^2 >= 2 or |x.c| >= 1
-    int ipe_prune;         // 1: bound-and-prune epilogue (k <= one centroid tile); 0: every pair is sampled
     double* store;         // [n, k] MODE_STORE: x_i.c_j - cnorm[j]
     unsigned long long* colkey;  // [k] MODE_COLABS: max over rows of (bits(|y|) with the sign of y in bit 0)
     long long n;
@@ -79,186 +72,6 @@ struct TileCfg {
     static constexpr int STAGE_DOUBLES = (BM + BN) * BK;
     static_assert(WM % 8 == 0 && WN % 8 == 0, "warp tile must be a multiple of 8x8");
 };
-
-// ---- IPE noise model -------------------------------------------------------
-// One inner-product estimate turned into a squared distance (Utility.py:729-736
-// with _dmeans.py:765-769): returns 2*S*a_tilde, S = |x|^2+|c|^2.
-__device__ __noinline__ double ipe_distance(double dot, double xn, double cn, double eps, Philox rng) {
-    const double PI = 3.14159265358979323846;
-    double S = xn + cn;
-    if (!(S > 0.0)) return 0.0;
-    double a = (S - 2.0 * dot) / (2.0 * S);
-    if (a < 1e-15) a = 0.0;  // math.isclose(a, 0, abs_tol=1e-15); negatives are rounding noise
-    if (a > 1.0) a = 1.0;
-    double eps_a = eps * fmax(1.0, fabs(dot)) / S;
-    double M = ceil((PI / (2.0 * eps_a)) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
-    double x = M * (asin(sqrt(a)) / PI);
-    // median of Q = 13 draws (median_evaluation with gamma = 0.1).  a_tilde = sin^2(pi j / M) is
-    // increasing in r = min(j, M - j), so the median is taken over r and one sine is evaluated.
-    FejerTable T;
-    fejer_setup(T, M, x);
-    double med;
-    if (T.exact) {
-        med = fmin(T.j0, M - T.j0);
-    } else {
-        double r[13];
-        int ntail = 0, nr = 0;
-        // window draws first (no divergence), the few tail draws afterwards
-#pragma unroll 1
-        for (int q = 0; q < 13; q += 2) {
-            double u[2];
-            rng.uniform2(u[0], u[1]);
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (q + h >= 13) break;
-                double j;
-                bool in = T.brute ? (j = fejer_brute(T, u[h]), true) : fejer_window(T, u[h], j);
-                if (in) {
-                    double v = fmin(j, M - j);
-                    int p = nr++;
-                    while (p > 0 && r[p - 1] > v) { r[p] = r[p - 1]; --p; }
-                    r[p] = v;
-                } else ++ntail;
-            }
-        }
-#pragma unroll 1
-        for (int q = 0; q < ntail; ++q) {
-            double j = fejer_tail(T, rng);
-            double v = fmin(j, M - j);
-            int p = nr++;
-            while (p > 0 && r[p - 1] > v) { r[p] = r[p - 1]; --p; }
-            r[p] = v;
-        }
-        med = r[6];
-    }
-    double sn = sinpi(med / M);
-    return 2.0 * S * sn * sn;
-}
-
-// ---- IPE with exact pruning ------------------------------------------------------
-// Sampling 13 amplitude-estimation outcomes for each of the n*k pairs is what makes the reference's
-// E-step expensive, yet only the smallest estimate of a row matters.  The estimates can be bounded
-// without sampling: the median of the 13 draws lies among the 8 grid points around M*theta_a/pi unless
-// at least 7 draws fall outside that window, and inside the window |a~ - a| <= w (2 sqrt(a(1-a)) + w),
-// w = 5 pi / M.  To keep the law exact the 13 uniforms of a pair are generated in two steps: first the
-// number T' of "potential tail" draws (uniforms below p_pot, an upper bound of the mass outside the
-// window; T' ~ Binomial(13, p_pot)), then the uniforms themselves given T'.  A pair with T' < 7 is
-// "safe": its estimate obeys the bound whatever the uniforms are.  Per row the set of unsafe pairs
-// (each pair independently with probability q = P(T' >= 7), ~1e-4) is drawn from one row stream.
-// Only unsafe pairs and pairs whose lower bound does not exceed the smallest safe upper bound of the
-// row are actually sampled - typically one or two per row.
-__device__ __forceinline__ int ipe_invcdf(const double* cdf, double u) {
-    int t = 0;
-#pragma unroll
-    for (int k = 0; k < 13; ++k) t += (u >= cdf[k]) ? 1 : 0;
-    return t;
-}
-
-// columns of the unsafe pairs of a row; returns their number (the list is valid when it is <= 4)
-__device__ __noinline__ int ipe_row_marks(const AssignArgs& a, long long grow, int* cols, int cap) {
-    Philox rng(a.seed, a.offset + (unsigned long long)grow, 0x1bE2u, 0u);
-    int m = (int)binomial_split((double)a.k, a.ipe_q, 1.0 - a.ipe_q, rng);
-    for (int i = 0; i < m && i < cap; ++i) {
-        // uniform subset without replacement: redraw on duplicates
-        while (true) {
-            int c = (int)(rng.uniform() * a.k);
-            if (c >= a.k) c = a.k - 1;
-            bool dup = false;
-            for (int t = 0; t < i; ++t) dup |= (cols[t] == c);
-            if (!dup) { cols[i] = c; break; }
-        }
-    }
-    return m;
-}
-
-// conservative float bounds of 2*S*a~ for a safe pair; `sample` is set when the bound does not apply
-// (tiny grid) or cannot be trusted in single precision.  The window j0-3 .. j0+4 around x = M theta_a / pi
-// spans the angles theta_a -+ 4 pi / M, so a~ = sin^2(pi j / M) lies in sin^2 of that interval.
-__device__ __forceinline__ void ipe_bounds(double dot, double xn, double cn, float eps, float Mmin, float& lo,
-                                           float& hi, bool& sample) {
-    const double S = xn + cn;
-    const float Sf = (float)S, dotf = fabsf((float)dot);
-    sample = !(Sf > 1e-30f && Sf < 1e30f);
-    const float inv2S = __frcp_rn(2.0f * Sf);
-    float af = (float)(S - 2.0 * dot) * inv2S;
-    af = fminf(fmaxf(af, 0.0f), 1.0f);
-    const float eps_a = eps * fmaxf(1.0f, dotf) * 2.0f * inv2S;
-    const float Mf = (1.5707963f / eps_a) * (1.0f + sqrtf(1.0f + 4.0f * eps_a)) * 0.99999f;   // <= true M
-    sample |= !(Mf >= Mmin);
-    const float th = asinf(sqrtf(af));
-    const float w = 12.5790f / Mf + 2e-5f;              // 4 pi / M plus rounding slack (asinf, sqrtf)
-    const float sl = sinf(fmaxf(th - w, 0.0f));
-    const float sh = sinf(fminf(th + w, 1.5707964f));
-    lo = 2.0f * Sf * fmaxf(sl * sl - 4e-6f, 0.0f) * 0.9999f;
-    hi = 2.0f * Sf * fminf(sh * sh + 4e-6f, 1.0f) * 1.0001f;
-}
-
-// the estimate itself, with the uniforms generated as described above (marked = unsafe pair)
-__device__ __noinline__ double ipe_distance_marked(const AssignArgs& a, double dot, double xn, double cn, bool marked,
-                                                   long long grow, int col) {
-    const double PI = 3.14159265358979323846, eps = 0.5 * a.delta;
-    double S = xn + cn;
-    if (!(S > 0.0)) return 0.0;
-    double av = (S - 2.0 * dot) / (2.0 * S);
-    if (av < 1e-15) av = 0.0;
-    if (av > 1.0) av = 1.0;
-    double eps_a = eps * fmax(1.0, fabs(dot)) / S;
-    double M = ceil((PI / (2.0 * eps_a)) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
-    Philox rng(a.seed, a.offset + (unsigned long long)grow, 0x1bE1u, (unsigned)col);
-    if (M < a.ipe_Mmin) return ipe_distance(dot, xn, cn, eps, rng);   // tiny grid: 13 plain uniforms
-    double x = M * (asin(sqrt(av)) / PI);
-    FejerTable T;
-    fejer_setup(T, M, x);
-    double med;
-    if (T.exact) {
-        med = fmin(T.j0, M - T.j0);
-    } else {
-        // T' given the mark: Binomial(13, p_pot) truncated to >= 7 (marked) or < 7 (safe)
-        double u0 = rng.uniform();
-        double c6 = a.ipe_cdf[6];
-        int tp = ipe_invcdf(a.ipe_cdf, marked ? c6 + u0 * (1.0 - c6) : u0 * c6);
-        if (marked && tp < 7) tp = 7;
-        if (!marked && tp > 6) tp = 6;
-        const double W = T.cum[2 * FEJER_W - 1];          // mass of the window (>= 1 - p_pot)
-        double r[13];
-        int ntail = 0, nr = 0;
-#pragma unroll 1
-        for (int q = 0; q < 13; q += 2) {
-            double w2[2];
-            rng.uniform2(w2[0], w2[1]);
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                if (q + h >= 13) break;
-                // potential tail draws live in [0, p_pot), the others in [p_pot, 1); the tail is [0, 1 - W)
-                double U = (q + h < tp) ? w2[h] * a.ipe_ppot : a.ipe_ppot + w2[h] * (1.0 - a.ipe_ppot);
-                double j;
-                if (U >= 1.0 - W && fejer_window(T, U - (1.0 - W), j)) {
-                    double v = fmin(j, M - j);
-                    int p = nr++;
-                    while (p > 0 && r[p - 1] > v) { r[p] = r[p - 1]; --p; }
-                    r[p] = v;
-                } else if (U >= 1.0 - W) {
-                    // rounding put U past the last window threshold: it is the last window point
-                    double v = fmin(fejer_wrap(T, fejer_offset(2 * FEJER_W - 1)), M - fejer_wrap(T, fejer_offset(2 * FEJER_W - 1)));
-                    int p = nr++;
-                    while (p > 0 && r[p - 1] > v) { r[p] = r[p - 1]; --p; }
-                    r[p] = v;
-                } else ++ntail;
-            }
-        }
-#pragma unroll 1
-        for (int q = 0; q < ntail; ++q) {
-            double j = fejer_tail(T, rng);
-            double v = fmin(j, M - j);
-            int p = nr++;
-            while (p > 0 && r[p - 1] > v) { r[p] = r[p - 1]; --p; }
-            r[p] = v;
-        }
-        med = r[6];
-    }
-    double sn = sinpi(med / M);
-    return 2.0 * S * sn * sn;
-}
 
 __device__ __forceinline__ double lds_f64(unsigned addr) {
     double v;
@@ -284,9 +97,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     int* first = cnt + BM;                                   // [BM] lowest candidate column
     int* run_a1 = first + BM;                                // [BM]
     int* run_cnt = run_a1 + BM;                              // [BM]
-    int* marks = run_cnt + BM;                               // [BM][4] IPE: columns of the row's unsafe pairs
-    int* nmark = marks + 4 * BM;                             // [BM]    IPE: their number
-    double* cn_s = (double*)(nmark + BM + (BM & 1));         // [NT*BN] centroid norms (+inf past k)
+    double* cn_s = (double*)(run_cnt + BM);                  // [NT*BN] centroid norms (+inf past k)
     unsigned long long* full_bar = (unsigned long long*)(cn_s + a.NT * BN);  // [STAGES] TMA completion barriers
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -507,95 +318,13 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                         }
                 }
             }
-            if (MODE == MODE_IPEP) {
-                // exact pruning (see ipe_* above): only pairs that can still be the row minimum are sampled,
-                // all others become +inf
-                const float epsf = (float)(0.5 * a.delta), Mminf = (float)a.ipe_Mmin;
-                if (tid < BM) {
-                    const long long gr = r0 + tid;
-                    int cols[4] = {-1, -1, -1, -1};
-                    nmark[tid] = (gr < a.n) ? ipe_row_marks(a, gr, cols, 4) : 0;
-                    marks[tid * 4] = cols[0]; marks[tid * 4 + 1] = cols[1];
-                    marks[tid * 4 + 2] = cols[2]; marks[tid * 4 + 3] = cols[3];
-                }
-                __syncthreads();  // xn_s, marks
-                unsigned must = 0;   // bit (i*8 + j*2 + e): the pair has to be sampled whatever the bounds say
-#pragma unroll
-                for (int i = 0; i < MI; ++i) {
-                    const int row = wm * Cfg::WM + i * 8 + lq;
-                    const double xn = xn_s[row];
-                    const int nm = nmark[row];
-                    float rowhi = INFINITY;
-#pragma unroll
-                    for (int j = 0; j < NI; ++j)
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int col = colbase + j * 8 + e;
-                            if (col < a.k) {
-                                float lo, hi;
-                                bool smp;
-                                ipe_bounds(acc[i][j][e], xn, cn_s[col], epsf, Mminf, lo, hi, smp);
-                                bool mk = false;
-                                if (nm > 0) mk = (marks[row * 4] == col) | (marks[row * 4 + 1] == col) |
-                                                 (marks[row * 4 + 2] == col) | (marks[row * 4 + 3] == col);
-                                if (smp || mk) must |= 1u << (i * 8 + j * 2 + e);
-                                else rowhi = fminf(rowhi, hi);
-                            }
-                        }
-                    rowhi = fminf(rowhi, __shfl_xor_sync(0xffffffffu, rowhi, 1));
-                    rowhi = fminf(rowhi, __shfl_xor_sync(0xffffffffu, rowhi, 2));
-                    if (lr4 == 0) wmin[row * WN_CNT + wn] = (double)rowhi;
-                }
-                __syncthreads();
-                {
-                    constexpr int ENTRIES = BM * WN_CNT;
-                    for (int e0 = 0; e0 < ENTRIES; e0 += Cfg::THREADS) {
-                        int e = e0 + tid;
-                        double m = (e < ENTRIES) ? wmin[e] : INFINITY;
-#pragma unroll
-                        for (int o = 1; o < WN_CNT; o <<= 1) m = dmin(m, __shfl_xor_sync(0xffffffffu, m, o));
-                        if (e < ENTRIES && (e % WN_CNT) == 0) rowmin_s[e / WN_CNT] = m;
-                    }
-                }
-                __syncthreads();
-#pragma unroll
-                for (int i = 0; i < MI; ++i) {
-                    const int row = wm * Cfg::WM + i * 8 + lq;
-                    const long long gr = r0 + row;
-                    const int nm = nmark[row];
-                    const double xn = xn_s[row];
-                    const float H = (float)rowmin_s[row];
-#pragma unroll
-                    for (int j = 0; j < NI; ++j)
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            const int col = colbase + j * 8 + e;
-                            double v = INFINITY;
-                            if (gr < a.n && col < a.k && nm <= 4) {   // rows with more unsafe pairs are redone as a whole
-                                bool cand = (must >> (i * 8 + j * 2 + e)) & 1u;
-                                if (!cand) {
-                                    float lo, hi;
-                                    bool smp;
-                                    ipe_bounds(acc[i][j][e], xn, cn_s[col], epsf, Mminf, lo, hi, smp);
-                                    cand = lo <= H;
-                                }
-                                if (cand) {
-                                    bool mk = (nm > 0) && ((marks[row * 4] == col) | (marks[row * 4 + 1] == col) |
-                                                           (marks[row * 4 + 2] == col) | (marks[row * 4 + 3] == col));
-                                    v = ipe_distance_marked(a, acc[i][j][e], xn, cn_s[col], mk, gr, col) - xn;
-                                }
-                            }
-                            acc[i][j][e] = v;
-                        }
-                }
-            }
             // ---- phase A: v in place, per-warp row minima ----
 #pragma unroll
             for (int j = 0; j < NI; ++j) {
                 const double2 cn2 = *reinterpret_cast<const double2*>(cn_s + colbase + j * 8);
 #pragma unroll
                 for (int i = 0; i < MI; ++i) {
-                    if (MODE != MODE_IPE && MODE != MODE_IPEP) {   // (IPE already holds noisy distance - |x|^2)
+                    if (MODE != MODE_IPE) {   // (IPE already holds noisy distance - |x|^2)
                         acc[i][j][0] = fma(-2.0, acc[i][j][0], cn2.x);
                         acc[i][j][1] = fma(-2.0, acc[i][j][1], cn2.y);
                     }
@@ -710,10 +439,6 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                         if (MODE == MODE_EXACT && rc > 1 && a.tie_tol >= 0.0) {
                             int slot = atomicAdd(a.flag_count, 1);
                             a.flag_rows[slot] = (int)gr;  // n < 2^31 per call (checked on the host)
-                        }
-                        if (MODE == MODE_IPEP && nmark[row] > 4) {
-                            int slot = atomicAdd(a.flag_count, 1);
-                            a.flag_rows[slot] = (int)gr;  // redone by qmeans_ipe_fixup_kernel
                         }
                     }
                 }
@@ -881,41 +606,6 @@ __global__ void qmeans_window_fixup_kernel(AssignArgs a) {
     }
 }
 
-// ---- IPE rows redone as a whole (many unsafe pairs, or more than four candidates) -----------------
-__global__ void qmeans_ipe_fixup_kernel(AssignArgs a) {
-    const int nflag = *a.flag_count;
-    const int lane = threadIdx.x & 31;
-    const int wglobal = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int nwarps = (gridDim.x * blockDim.x) >> 5;
-    for (int f = wglobal; f < nflag; f += nwarps) {
-        const long long gr = a.flag_rows[f];
-        const double* x = a.X + gr * (long long)a.d;
-        const double xn = a.xnorm[gr];
-        int cols[32];
-        int m = 0;
-        if (lane == 0) m = ipe_row_marks(a, gr, cols, 32);
-        m = __shfl_sync(0xffffffffu, m, 0);
-        double best = INFINITY;
-        int bc = 0x7fffffff;
-        for (int j = lane; j < a.k; j += 32) {
-            double dotv = 0.0;
-            const double* c = a.C + (long long)j * a.d;
-            for (int t = 0; t < a.d; ++t) dotv = fma(x[t], c[t], dotv);
-            bool mk = false;
-            for (int t = 0; t < m && t < 32; ++t) mk |= (__shfl_sync(__activemask(), cols[t], 0) == j);
-            double dt = ipe_distance_marked(a, dotv, xn, a.cnorm[j], mk, gr, j);
-            if (dt < best || (dt == best && j < bc)) { best = dt; bc = j; }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            double ob = __shfl_xor_sync(0xffffffffu, best, o);
-            int oc = __shfl_xor_sync(0xffffffffu, bc, o);
-            if (ob < best || (ob == best && oc < bc)) { best = ob; bc = oc; }
-        }
-        if (lane == 0) { a.labels[gr] = bc; a.mindist[gr] = fmax(best, 0.0); }
-    }
-}
-
 // ---- ||row||^2 of a row-major matrix (row_norms(X, squared=True), extmath.py:49-78)
 __global__ void row_sqnorm_kernel(const double* __restrict__ X, long long n, int d, double* __restrict__ out) {
     const int lane = threadIdx.x & 31;
@@ -992,7 +682,7 @@ static size_t assign_ws_layout(long long n, int k, AssignWs* w, char* base) {
 template <class Cfg>
 static size_t assign_smem_bytes() {
     return (size_t)Cfg::STAGES * Cfg::STAGE_DOUBLES * 8 + (size_t)Cfg::BM * Cfg::WARPS_N * 8 +
-           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4 * 4 + 4 * 4 + 16 + 4) + 72;  // + NT*BN centroid norms, added at launch
+           (size_t)Cfg::BM * (8 + 8 + 8 + 8 + 4 * 4 + 4 * 4) + 72;  // + NT*BN centroid norms, added at launch
 }
 
 // optional timing of the main kernel alone (bench.py's roofline leg): events are
@@ -1041,14 +731,12 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
     if (use_tma) {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(true, MODE_EXACT, true);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(true, MODE_WINDOW, true);
-        else if (a.mode == MODE_IPE && a.ipe_prune) SQ_LAUNCH_ASSIGN(true, MODE_IPEP, true);
         else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(true, MODE_IPE, true);
         else if (a.mode == MODE_COLABS) SQ_LAUNCH_ASSIGN(true, MODE_COLABS, true);
         else SQ_LAUNCH_ASSIGN(true, MODE_STORE, true);
     } else {
         if (a.mode == MODE_EXACT) SQ_LAUNCH_ASSIGN(false, MODE_EXACT, false);
         else if (a.mode == MODE_WINDOW) SQ_LAUNCH_ASSIGN(false, MODE_WINDOW, false);
-        else if (a.mode == MODE_IPE && a.ipe_prune) SQ_LAUNCH_ASSIGN(false, MODE_IPEP, false);
         else if (a.mode == MODE_IPE) SQ_LAUNCH_ASSIGN(false, MODE_IPE, false);
         else if (a.mode == MODE_COLABS) SQ_LAUNCH_ASSIGN(false, MODE_COLABS, false);
         else SQ_LAUNCH_ASSIGN(false, MODE_STORE, false);
@@ -1124,11 +812,8 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     cudaStream_t stream = (cudaStream_t)stream_;
     SQ_REQUIRE(X && xnorm && C && labels && inertia, "sq_qmeans_assign: null pointer");
     SQ_REQUIRE(n >= 1 && n < 2147483647LL && d >= 1 && k >= 1, "sq_qmeans_assign: bad shape n=%lld d=%d k=%d", n, d, k);
-    SQ_REQUIRE((mode >= 0 && mode <= 2) || mode == MODE_IPEP,
-               "sq_qmeans_assign: mode must be 0 (exact), 1 (delta window), 2 (ipe) or 5 (ipe, pruned)");
+    SQ_REQUIRE(mode >= 0 && mode <= 2, "sq_qmeans_assign: mode must be 0 (exact), 1 (delta window) or 2 (ipe)");
     SQ_REQUIRE(mode == MODE_EXACT || delta > 0.0, "sq_qmeans_assign: noisy modes need delta > 0");
-    const int mode_in = mode;
-    (void)mode_in;
     size_t need = assign_ws_layout(n, k, nullptr, nullptr);
     if (!ws || ws_bytes < need) { set_error("sq_qmeans_assign: workspace needs %zu bytes, got %zu", need, ws_bytes); return SQ_ERR_WORKSPACE; }
     AssignWs w;
@@ -1145,26 +830,6 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     a.n = n; a.d = d; a.k = k; a.mode = mode; a.delta = delta;
     a.tie_tol = 16.0 * (d + 8) * 1.1102230246251565e-16;
     a.seed = seed; a.offset = offset;
-    a.ipe_prune = 0;
-    if (mode == MODE_IPEP) mode = MODE_IPE, a.mode = MODE_IPE, a.ipe_prune = -1;   // requested; granted below if possible
-    if (a.ipe_prune == -1 && k <= 256) {
-        // smallest M of a pair with eps_a <= eps/2, the bound on the mass outside the window, and the law of T'
-        const double PI = 3.14159265358979323846, e2 = 0.25 * delta;
-        a.ipe_Mmin = ceil((PI / (2.0 * e2)) * (1.0 + sqrt(1.0 + 4.0 * e2)));
-        a.ipe_ppot = 0.07292 + 1.0 / a.ipe_Mmin + 2.0 / (a.ipe_Mmin * a.ipe_Mmin);
-        if (a.ipe_Mmin >= 10.0 && a.ipe_ppot < 0.5) {
-            double p = a.ipe_ppot, acc = 0.0, binom = 1.0;
-            for (int t = 0; t < 14; ++t) {            // pmf(t) = C(13,t) p^t (1-p)^(13-t)
-                if (t > 0) binom = binom * (13 - t + 1) / t;
-                acc += binom * pow(p, t) * pow(1.0 - p, 13 - t);
-                a.ipe_cdf[t] = acc;
-            }
-            a.ipe_cdf[13] = 1.0;
-            a.ipe_q = 1.0 - a.ipe_cdf[6];
-            a.ipe_prune = 1;
-        }
-    }
-    if (a.ipe_prune < 0) a.ipe_prune = 0;   // not possible for this k / delta: every pair is sampled
     int bn = 0;
     if (mode == MODE_WINDOW && k > 256) {
         // the window needs the row minimum over all k before candidates can be drawn
@@ -1184,10 +849,6 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
         int fb = device_sm_count() * 4;
         qmeans_window_fixup_kernel<<<fb, 256, 0, stream>>>(a);
         SQ_LAUNCH_CHECK("qmeans_window_fixup_kernel");
-    } else if (mode == MODE_IPE && a.ipe_prune) {
-        int fb = device_sm_count() * 4;
-        qmeans_ipe_fixup_kernel<<<fb, 256, 0, stream>>>(a);
-        SQ_LAUNCH_CHECK("qmeans_ipe_fixup_kernel");
     }
     rc = sq_sum_f64(a.mindist, n, inertia, w.partial, SUM_BLOCKS * sizeof(double), stream);
     if (rc) return rc;

@@ -30,7 +30,7 @@ import torch
 
 from .. import _device as dv
 from ..QuantumUtility import Utility as qu
-from ._engine import MODE_EXACT, MODE_IPE, MODE_IPE_PRUNED, MODE_WINDOW, QMeansEngine
+from ._engine import MODE_EXACT, MODE_IPE, MODE_WINDOW, QMeansEngine
 
 # the reference seeds Python's global generator when the module is imported (_dmeans.py:22)
 random.seed(a=1234)
@@ -162,23 +162,19 @@ def _kmeans_plusplus_device(engine, n_clusters, random_state, n_local_trials=Non
     return centers
 
 
-def _mode_of(delta, true_distance_estimate, unit_norm_centers=False):
+def _mode_of(delta, true_distance_estimate):
     if not delta or delta <= 0:
         return MODE_EXACT
-    if not true_distance_estimate:
-        return MODE_WINDOW
-    # With centroid tomography the centres are unit vectors and every pair stays a
-    # candidate, so pruning only costs; with plain means it skips most pairs.  Same law either way.
-    return MODE_IPE if unit_norm_centers else MODE_IPE_PRUNED
+    return MODE_IPE if true_distance_estimate else MODE_WINDOW
 
 
-def labels_estimation(engine, centers, delta, pool, true_distance_estimate, unit_norm_centers=False):
+def labels_estimation(engine, centers, delta, pool, true_distance_estimate):
     """E-step on the device (reference: _dmeans.py:732-777).
 
     Returns (labels int32 device tensor, per-row min distance device tensor,
     inertia device scalar).  ``pool`` is accepted and unused: the IPE draws of
     every (sample, centroid) pair run inside one kernel."""
-    mode = _mode_of(delta, true_distance_estimate, unit_norm_centers)
+    mode = _mode_of(delta, true_distance_estimate)
     row0, total = engine.row0, engine.n_total
     seed, off = qu._take_streams(total)
     engine.assign(centers, mode, delta if delta else 0.0, seed, off + row0)
@@ -186,9 +182,9 @@ def labels_estimation(engine, centers, delta, pool, true_distance_estimate, unit
 
 
 def _labels_inertia(engine, centers, distances=None, delta=0, pool=None, true_distance_estimate=True,
-                    n_threads=None, unit_norm_centers=False):
+                    n_threads=None):
     """E step of the q-means EM algorithm (reference: _dmeans.py:674-724)."""
-    return labels_estimation(engine, centers, delta, pool, true_distance_estimate, unit_norm_centers)
+    return labels_estimation(engine, centers, delta, pool, true_distance_estimate)
 
 
 def _centers_update(engine, labels, error, intermediate_error, true_tomography, stop_when_reached_accuracy,
@@ -233,8 +229,7 @@ def _lloyd_iteration(engine, centers, centers_old, centers_new, host, delta, int
     returns (inertia, shift) read back through the pinned 2-double buffer ``host``."""
     centers_old.copy_(centers)
     labels, _, _ = _labels_inertia(engine, centers, delta=delta, pool=pool,
-                                   true_distance_estimate=true_distance_estimate,
-                                   unit_norm_centers=bool(intermediate_err and true_tomography))
+                                   true_distance_estimate=true_distance_estimate)
     out = _centers_update(engine, labels, delta / 2, intermediate_error=intermediate_err,
                           true_tomography=true_tomography,
                           stop_when_reached_accuracy=stop_when_reached_accuracy,

@@ -15,7 +15,6 @@ from .. import _cabi
 from .. import _device as dv
 
 MODE_EXACT, MODE_WINDOW, MODE_IPE = 0, 1, 2
-MODE_IPE_PRUNED = 5   # same law as MODE_IPE; skips pairs that provably cannot be the row minimum
 
 
 class QMeansEngine:
