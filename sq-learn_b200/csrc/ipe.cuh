@@ -152,7 +152,7 @@ __device__ __noinline__ double ipe_median_replay(double M, double x, int T, uint
 
 // |x|^2 + |c|^2 - 2 ipe(x, c) for the pair held by each lane.  All 32 lanes of the warp must call
 // it together; lanes without a pair pass valid = false.  eps is ipe's epsilon (delta / 2).
-__device__ __noinline__ double ipe_estimate_warp(double dot, double xn, double cn, double eps, bool valid,
+__device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, double cn, double eps, bool valid,
                                                  uint64_t seed, uint64_t rowkey, uint32_t col) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;

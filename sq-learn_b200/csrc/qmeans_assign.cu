@@ -50,6 +50,8 @@ struct AssignArgs {
     double* rowmin_out;    // [n]   optional raw min (EXACT)
     int* flag_count;       // [1]   number of near-tie rows
     int* flag_rows;        // [n]   their indices
+    double* ipe_scratch;   // [grid][BM*BN] MODE_IPE: each CTA's tile of dot products, then of estimates
+    size_t ipe_scratch_bytes;   // (host) capacity of ipe_scratch: bounds the grid
     double* store;         // [n, k] MODE_STORE: x_i.c_j - cnorm[j]
     unsigned long long* colkey;  // [k] MODE_COLABS: max over rows of (bits(|y|) with the sign of y in bit 0)
     long long n;
@@ -299,23 +301,45 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 if (MODE != MODE_WINDOW || nt == 0) { cnt[tid] = 0; first[tid] = 0x7fffffff; }
             }
             if (MODE == MODE_IPE) {
-                __syncthreads();  // xn_s
-                // every pair is sampled: the accumulator becomes (noisy squared distance - |x|^2)
+                // Every pair is sampled: the accumulator becomes (noisy squared distance - |x|^2).  The tile of
+                // dot products is parked in this CTA's slice of the workspace (L2-resident), so that the
+                // sampler runs with the whole register file instead of beside 2*MI*NI live accumulators, and
+                // the pairs are dealt to the lanes as a flat list (no idle lanes for k < BN).
+                double* sc = a.ipe_scratch + (size_t)blockIdx.x * (BM * BN);
+                const int cl0 = wn * Cfg::WN + lr4 * 2;
+#pragma unroll
+                for (int i = 0; i < MI; ++i)
+#pragma unroll
+                    for (int j = 0; j < NI; ++j)
+                        *reinterpret_cast<double2*>(sc + (wm * Cfg::WM + i * 8 + lq) * BN + cl0 + j * 8) =
+                            make_double2(acc[i][j][0], acc[i][j][1]);
+                __syncthreads();  // xn_s, sc
+                const int kk = min(BN, a.k - n0);                  // live columns of this centroid tile
+                const int rows = (int)min((long long)BM, a.n - r0);
+                const int pairs = rows * kk;
+                const int rounds = (pairs + Cfg::THREADS - 1) / Cfg::THREADS;
+#pragma unroll 1
+                for (int it = 0; it < rounds; ++it) {
+                    const int idx = it * Cfg::THREADS + tid;
+                    const bool ok = idx < pairs;
+                    const int row = ok ? idx / kk : 0, cl = ok ? idx - row * kk : 0;
+                    const double xn = xn_s[row];
+                    const double v = ipe_estimate_warp(sc[row * BN + cl], xn, ok ? cn_s[n0 + cl] : 0.0, 0.5 * a.delta, ok,
+                                                       a.seed, a.offset + (unsigned long long)(r0 + row),
+                                                       (unsigned)(n0 + cl));
+                    if (ok) sc[row * BN + cl] = v - xn;
+                }
+                __syncthreads();
 #pragma unroll
                 for (int i = 0; i < MI; ++i) {
                     const int row = wm * Cfg::WM + i * 8 + lq;
-                    const long long gr = r0 + row;
-                    const double xn = xn_s[row];
 #pragma unroll
-                    for (int j = 0; j < NI; ++j)
-#pragma unroll
-                        for (int e = 0; e < 2; ++e) {
-                            int col = colbase + j * 8 + e;
-                            const bool ok = gr < a.n && col < a.k;
-                            const double v = ipe_estimate_warp(acc[i][j][e], xn, ok ? cn_s[col] : 0.0, 0.5 * a.delta, ok,
-                                                               a.seed, a.offset + (unsigned long long)gr, (unsigned)col);
-                            acc[i][j][e] = ok ? v - xn : INFINITY;
-                        }
+                    for (int j = 0; j < NI; ++j) {
+                        const double2 v2 = *reinterpret_cast<const double2*>(sc + row * BN + cl0 + j * 8);
+                        const int col = colbase + j * 8;
+                        acc[i][j][0] = (row < rows && col < a.k) ? v2.x : INFINITY;
+                        acc[i][j][1] = (row < rows && col + 1 < a.k) ? v2.y : INFINITY;
+                    }
                 }
             }
             // ---- phase A: v in place, per-warp row minima ----
@@ -665,6 +689,9 @@ struct AssignWs {
     double* mindist;
 };
 static const int SUM_BLOCKS = 1024;
+// ipe mode parks one tile of dot products (<= 64 KB) per resident CTA behind the fixed part of the workspace;
+// sq_qmeans_assign_workspace_bytes asks for enough for 4 CTAs on each of 160 SMs, less still works (smaller grid)
+static const size_t IPE_SCRATCH_BYTES = (size_t)640 * 65536;
 
 static size_t assign_ws_layout(long long n, int k, AssignWs* w, char* base) {
     size_t off = 0;
@@ -726,6 +753,15 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
         if (per_sm < 1) per_sm = 1;                                                                                 \
         int grid = device_sm_count() * per_sm;                                                                      \
         if (grid > a.num_tiles) grid = a.num_tiles;                                                                 \
+        if (M == MODE_IPE) {                                                                                        \
+            size_t fit = a.ipe_scratch_bytes / ((size_t)Cfg::BM * Cfg::BN * sizeof(double));                        \
+            if (fit < 1 || !a.ipe_scratch) {                                                                        \
+                set_error("sq_qmeans_assign: ipe mode needs %zu more workspace bytes per resident CTA",             \
+                          (size_t)Cfg::BM * Cfg::BN * sizeof(double));                                              \
+                return SQ_ERR_WORKSPACE;                                                                            \
+            }                                                                                                       \
+            if ((size_t)grid > fit) grid = (int)fit;                                                                \
+        }                                                                                                           \
         qmeans_assign_kernel<Cfg, V, M, T><<<grid, Cfg::THREADS, smem, stream>>>(a, tmA, tmB);                      \
     } while (0)
     if (use_tma) {
@@ -802,7 +838,7 @@ extern "C" int sq_sum_f64(const double* v, long long n, double* out, void* ws, s
 
 extern "C" size_t sq_qmeans_assign_workspace_bytes(long long n, int d, int k) {
     (void)d;
-    return assign_ws_layout(n, k, nullptr, nullptr);
+    return assign_ws_layout(n, k, nullptr, nullptr) + IPE_SCRATCH_BYTES;
 }
 
 extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, const double* C, int k,
@@ -830,6 +866,9 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     a.n = n; a.d = d; a.k = k; a.mode = mode; a.delta = delta;
     a.tie_tol = 16.0 * (d + 8) * 1.1102230246251565e-16;
     a.seed = seed; a.offset = offset;
+    a.store = nullptr; a.colkey = nullptr;
+    a.ipe_scratch = (double*)((char*)ws + need);            // whatever lies behind the fixed part
+    a.ipe_scratch_bytes = ws_bytes - need;
     int bn = 0;
     if (mode == MODE_WINDOW && k > 256) {
         // the window needs the row minimum over all k before candidates can be drawn
