@@ -86,38 +86,19 @@ __device__ __noinline__ double ipe_tail_draw(double M, double t, double j0, uint
 
 static __constant__ double kIpeInv[14] = {0.0, 1.0, 1.0 / 2, 1.0 / 3, 1.0 / 4, 1.0 / 5, 1.0 / 6, 1.0 / 7,
                                           1.0 / 8, 1.0 / 9, 1.0 / 10, 1.0 / 11, 1.0 / 12, 1.0 / 13};
-// kIpeBinom[k-1][i] = C(k+i-1, i)
-static __constant__ double kIpeBinom[13][13] = {
-    {1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0,},
-    {1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0, 8.0, 9.0, 10.0, 11.0, 12.0, 13.0,},
-    {1.0, 3.0, 6.0, 10.0, 15.0, 21.0, 28.0, 36.0, 45.0, 55.0, 66.0, 78.0, 91.0,},
-    {1.0, 4.0, 10.0, 20.0, 35.0, 56.0, 84.0, 120.0, 165.0, 220.0, 286.0, 364.0, 455.0,},
-    {1.0, 5.0, 15.0, 35.0, 70.0, 126.0, 210.0, 330.0, 495.0, 715.0, 1001.0, 1365.0, 1820.0,},
-    {1.0, 6.0, 21.0, 56.0, 126.0, 252.0, 462.0, 792.0, 1287.0, 2002.0, 3003.0, 4368.0, 6188.0,},
-    {1.0, 7.0, 28.0, 84.0, 210.0, 462.0, 924.0, 1716.0, 3003.0, 5005.0, 8008.0, 12376.0, 18564.0,},
-    {1.0, 8.0, 36.0, 120.0, 330.0, 792.0, 1716.0, 3432.0, 6435.0, 11440.0, 19448.0, 31824.0, 50388.0,},
-    {1.0, 9.0, 45.0, 165.0, 495.0, 1287.0, 3003.0, 6435.0, 12870.0, 24310.0, 43758.0, 75582.0, 125970.0,},
-    {1.0, 10.0, 55.0, 220.0, 715.0, 2002.0, 5005.0, 11440.0, 24310.0, 48620.0, 92378.0, 167960.0, 293930.0,},
-    {1.0, 11.0, 66.0, 286.0, 1001.0, 3003.0, 8008.0, 19448.0, 43758.0, 92378.0, 184756.0, 352716.0, 646646.0,},
-    {1.0, 12.0, 78.0, 364.0, 1365.0, 4368.0, 12376.0, 31824.0, 75582.0, 167960.0, 352716.0, 705432.0, 1352078.0,},
-    {1.0, 13.0, 91.0, 455.0, 1820.0, 6188.0, 18564.0, 50388.0, 125970.0, 293930.0, 646646.0, 1352078.0, 2704156.0}};
-
-// P(Binomial(n, F) >= k) = F^k sum_{i=0}^{n-k} C(k+i-1, i) (1-F)^i, 1 <= k <= n <= 13; nmk = n - k,
-// bound >= nmk is the trip count (uniform over the callers that run together)
-__device__ __forceinline__ double ipe_order_cdf(double F, int k, int nmk, int bound) {
-    const double q = 1.0 - F;
-    const double* cf = kIpeBinom[k - 1];
-    double sum = 0.0;
-#pragma unroll 1
-    for (int i = bound; i >= 0; --i) sum = fma(sum, q, (i <= nmk) ? cf[i] : 0.0);
-    double Fk = 1.0, p = F;
-    int kk = k;
-#pragma unroll
-    for (int b = 0; b < 4; ++b) {
-        if (kk & 1) Fk *= p;
-        p *= p;
-        kk >>= 1;
-    }
+// P(Binomial(n, F) >= k) = F^k sum_{i=0}^{n-k} C(k+i-1, i) (1-F)^i for 1 <= k <= 7, 0 <= n - k <= 6
+// (k = 7 - b and n - k = 6 - c with b, c the tail draws below / above the window).  Straight-line code:
+// term_i = term_{i-1} q (k-1+i)/i.
+__device__ __forceinline__ double ipe_order_cdf(double F, int k, int nmk) {
+    const double q = 1.0 - F, km1 = (double)(k - 1);
+    double term = q * km1 + q, sum = 1.0 + ((1 <= nmk) ? term : 0.0);      // i = 1: (k-1+1)/1 = k
+    term *= q * fma(km1, 1.0 / 2, 1.0); sum += (2 <= nmk) ? term : 0.0;
+    term *= q * fma(km1, 1.0 / 3, 1.0); sum += (3 <= nmk) ? term : 0.0;
+    term *= q * fma(km1, 1.0 / 4, 1.0); sum += (4 <= nmk) ? term : 0.0;
+    term *= q * fma(km1, 1.0 / 5, 1.0); sum += (5 <= nmk) ? term : 0.0;
+    term *= q * fma(km1, 1.0 / 6, 1.0); sum += (6 <= nmk) ? term : 0.0;
+    const double F2 = F * F, F4 = F2 * F2;
+    const double Fk = ((k & 1) ? F : 1.0) * ((k & 2) ? F2 : 1.0) * ((k & 4) ? F4 : 1.0);
     return Fk * sum;
 }
 
@@ -299,17 +280,16 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
     {
         const bool fast = (status == FAST);
         const int kk = fast ? k : 1, nmk = fast ? n - k : 0;
-        const int bound = __reduce_max_sync(FULL, nmk);
         const double iW = 1.0 / W;
         const bool srt = __all_sync(FULL, sorted || !fast);
         if (srt) {
             // cumulative window CDF in offset order; smallest i with V <= G(F_i), by bisection (F_7 = 1)
             const double F0 = w[0] * iW, F1 = F0 + w[1] * iW, F2 = F1 + w[2] * iW, F3 = F2 + w[3] * iW,
                          F4 = F3 + w[4] * iW, F5 = F4 + w[5] * iW, F6 = F5 + w[6] * iW;
-            const bool h1 = V <= ipe_order_cdf(F3, kk, nmk, bound);                       // answer in 0..3
-            const bool h2 = V <= ipe_order_cdf(h1 ? F1 : F5, kk, nmk, bound);             // lower pair of the half
+            const bool h1 = V <= ipe_order_cdf(F3, kk, nmk);                       // answer in 0..3
+            const bool h2 = V <= ipe_order_cdf(h1 ? F1 : F5, kk, nmk);             // lower pair of the half
             const double Fq = h1 ? (h2 ? F0 : F2) : (h2 ? F4 : F6);
-            const bool h3 = V <= ipe_order_cdf(Fq, kk, nmk, bound);
+            const bool h3 = V <= ipe_order_cdf(Fq, kk, nmk);
             const int i = (h1 ? 0 : 4) + (h2 ? 0 : 2) + (h3 ? 0 : 1);
             if (fast) med = rlo + (double)i;
         } else {
@@ -323,7 +303,7 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
                     const double j2 = ipe_wrap(j0 + (double)(i2 - 3), M), r2 = fmin(j2, M - j2);
                     Fi += (r2 <= ri) ? w[i2] : 0.0;
                 }
-                const double G = (Fi >= W) ? 1.0 : ipe_order_cdf(Fi * iW, kk, nmk, bound);
+                const double G = (Fi >= W) ? 1.0 : ipe_order_cdf(Fi * iW, kk, nmk);
                 if (V <= G) best = fmin(best, ri);
             }
             if (fast) med = (best <= rhi) ? best : rhi;   // rounding in F_i at the last point

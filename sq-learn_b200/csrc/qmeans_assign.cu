@@ -318,16 +318,23 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 const int rows = (int)min((long long)BM, a.n - r0);
                 const int pairs = rows * kk;
                 const int rounds = (pairs + Cfg::THREADS - 1) / Cfg::THREADS;
+                // (the dot product of the next round is fetched while this round's estimate is computed)
+                int row = 0, cl = 0;
+                bool ok = tid < pairs;
+                if (ok) { row = tid / kk; cl = tid - row * kk; }
+                double dot = sc[row * BN + cl];
 #pragma unroll 1
                 for (int it = 0; it < rounds; ++it) {
-                    const int idx = it * Cfg::THREADS + tid;
-                    const bool ok = idx < pairs;
-                    const int row = ok ? idx / kk : 0, cl = ok ? idx - row * kk : 0;
+                    const int idx2 = (it + 1) * Cfg::THREADS + tid;
+                    const bool ok2 = idx2 < pairs;
+                    const int row2 = ok2 ? idx2 / kk : 0, cl2 = ok2 ? idx2 - row2 * kk : 0;
+                    const double dot2 = sc[row2 * BN + cl2];
                     const double xn = xn_s[row];
-                    const double v = ipe_estimate_warp(sc[row * BN + cl], xn, ok ? cn_s[n0 + cl] : 0.0, 0.5 * a.delta, ok,
+                    const double v = ipe_estimate_warp(dot, xn, ok ? cn_s[n0 + cl] : 0.0, 0.5 * a.delta, ok,
                                                        a.seed, a.offset + (unsigned long long)(r0 + row),
                                                        (unsigned)(n0 + cl));
                     if (ok) sc[row * BN + cl] = v - xn;
+                    row = row2; cl = cl2; ok = ok2; dot = dot2;
                 }
                 __syncthreads();
 #pragma unroll
