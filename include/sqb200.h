@@ -71,6 +71,22 @@ int sq_tomography_batched_ws(const double* V, long long B, int d, double delta, 
                              unsigned long long vec_offset, double* est, double* n_used, double* err, void* ws,
                              size_t ws_bytes, void* stream);
 
+/* One long vector (or a few) over several GPUs: the leaf blocks of the long-vector path are sharded, rank r
+ * splitting blocks [blk_lo, blk_hi) (reference: the single-process loop of real_tomography, Utility.py:259-402;
+ * SURVEY 8(e) "single huge vector").  Every rank holds the whole V and the same (seed, vec_offset).  Per attempt
+ * the host runs phase 1 (stage-1 counts of the own blocks), sums the block masses bm_a | bm_b over the ranks
+ * (entries of foreign blocks zeroed first), phase 2 (stage-2 counts, signs, error partials), sums errp the same
+ * way, phase 3 (error, stop rule); phase 0 once before the first attempt.  After the last attempt est is complete
+ * on the own blocks only.  Block draws are keyed by (vector, block, node), so the result equals
+ * sq_tomography_batched_ws bit for bit whatever the number of ranks.  sq_tomography_workspace_layout fills
+ * out[0] = number of blocks, out[1] = leaves per block, out[2..6] = byte offsets in ws of bm_a, bm_b, bcnt,
+ * errp ([B, blocks] doubles each) and done ([B] int32), out[7] = total bytes.                             */
+int sq_tomography_workspace_layout(long long B, int d, long long out[8]);
+int sq_tomography_sharded_phase(const double* V, long long B, int d, double delta, int norm_inf, int stop,
+                                double n_measure, int attempt, unsigned long long seed,
+                                unsigned long long vec_offset, double* est, double* n_used, double* err, void* ws,
+                                size_t ws_bytes, int blk_lo, int blk_hi, int phase, void* stream);
+
 /* Incremental mode with the stop rule, lower latency: `lanes` CTAs per vector try different attempts of the
  * schedule at the same time and record the first (in schedule order) that meets the accuracy; that attempt
  * is then replayed to produce the outputs.  Attempts are fresh draws keyed by their index, so est / n_used /

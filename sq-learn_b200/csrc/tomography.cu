@@ -300,6 +300,7 @@ struct TomoBigArgs {
     int* done;             // [B]
     long long B;
     int d, nblk, NB, logNB;
+    int blk_lo;            // first block of this launch (leaf blocks can be sharded over GPUs)
     double N;
     int at, norm_inf, stop;
     double delta;
@@ -376,7 +377,7 @@ __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
     extern __shared__ double sm[];
     const long long b = blockIdx.y;
     if (a.done[b]) return;
-    const int blk = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+    const int blk = blockIdx.x + a.blk_lo, tid = threadIdx.x, T = blockDim.x;
     double* v = sm;               // [TB]
     double* P = v + TB;           // [TB]
     double* mass = P + TB;        // [2 TB]
@@ -547,6 +548,53 @@ extern "C" size_t sq_tomography_workspace_bytes(long long B, int d) {
     return total;
 }
 
+// phases of one attempt on the long-vector path; [blk_lo, blk_hi) is the range of leaf blocks this call splits
+static int tomo_big_prepare(TomoBigArgs& a, const double* V, long long B, int d, double delta, int norm_inf, int stop,
+                            unsigned long long seed, unsigned long long vec_offset, double* est, double* n_used,
+                            double* err, void* ws, size_t ws_bytes, const char* who) {
+    int nblk, NB, logNB;
+    size_t off[6], total;
+    tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
+    if (NB > 4096) { set_error("%s: d=%d exceeds the supported %d", who, d, 4096 * TB); return SQ_ERR_UNSUPPORTED; }
+    if (!ws || ws_bytes < total) { set_error("%s: workspace needs %zu bytes, got %zu", who, total, ws_bytes); return SQ_ERR_WORKSPACE; }
+    char* w = (char*)ws;
+    a.V = V; a.est = est; a.n_used = n_used; a.err = err;
+    a.sumsq = (double*)(w + off[0]); a.bm_a = (double*)(w + off[1]); a.bm_b = (double*)(w + off[2]);
+    a.bcnt = (double*)(w + off[3]); a.errp = (double*)(w + off[4]); a.done = (int*)(w + off[5]);
+    a.B = B; a.d = d; a.nblk = nblk; a.NB = NB; a.logNB = logNB; a.norm_inf = norm_inf; a.stop = stop; a.delta = delta;
+    a.seed = seed; a.vec_offset = vec_offset; a.blk_lo = 0; a.at = 0; a.N = 1.0;
+    return SQ_OK;
+}
+
+static int tomo_big_phase(TomoBigArgs a, int phase, int blk_lo, int blk_hi, cudaStream_t stream) {
+    const size_t sm_top = (size_t)(4 * a.NB + 32) * sizeof(double);
+    const size_t sm_blk = (size_t)(6 * TB + 32) * sizeof(double);
+    const int ttop = a.NB < 64 ? 64 : (a.NB > 512 ? 512 : a.NB);   // register budget: ~96 per thread
+    const dim3 gall(a.nblk, (unsigned)a.B), gown(blk_hi - blk_lo, (unsigned)a.B);
+    a.blk_lo = blk_lo;
+    if (phase == 0) {
+        int rc = sq_row_sqnorms(a.V, a.B, a.d, (double*)a.sumsq, stream);
+        if (rc) return rc;
+        tomo_big_init_kernel<<<(unsigned)((a.B + 255) / 256), 256, 0, stream>>>(a);
+        SQ_CUDA(cudaFuncSetAttribute(tomo_big_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_top));
+        SQ_CUDA(cudaFuncSetAttribute(tomo_big_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_blk));
+    } else if (phase == 1) {
+        // stage 1: block masses (cheap, all blocks), top tree, leaves of the own blocks
+        tomo_big_mass_kernel<<<gall, 256, 0, stream>>>(a);
+        tomo_big_top_kernel<<<(unsigned)a.B, ttop, sm_top, stream>>>(a, 1);
+        if (blk_hi > blk_lo) tomo_big_block_kernel<<<gown, 256, sm_blk, stream>>>(a, 1);
+    } else if (phase == 2) {
+        // stage 2 (needs the '+' / '-' masses of every block)
+        tomo_big_top_kernel<<<(unsigned)a.B, ttop, sm_top, stream>>>(a, 2);
+        if (blk_hi > blk_lo) tomo_big_block_kernel<<<gown, 256, sm_blk, stream>>>(a, 2);
+    } else {
+        // error over all blocks, stop rule
+        tomo_big_finish_kernel<<<(unsigned)a.B, 256, 0, stream>>>(a);
+    }
+    SQ_LAUNCH_CHECK("tomo_big kernels");
+    return SQ_OK;
+}
+
 extern "C" int sq_tomography_batched_ws(const double* V, long long B, int d, double delta, int norm_inf, int stop,
                                         const double* sched_host, int sched_len, unsigned long long seed,
                                         unsigned long long vec_offset, double* est, double* n_used, double* err,
@@ -561,40 +609,56 @@ extern "C" int sq_tomography_batched_ws(const double* V, long long B, int d, dou
     SQ_REQUIRE(sched_len >= 1 && sched_len <= 128, "sq_tomography_batched_ws: sched_len=%d outside [1,128]", sched_len);
     SQ_REQUIRE(delta > 0.0, "sq_tomography_batched_ws: delta must be > 0");
     if (B == 0) return SQ_OK;
-    int nblk, NB, logNB;
-    size_t off[6], total;
-    tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
-    if (NB > 4096) { set_error("sq_tomography_batched_ws: d=%d exceeds the supported %d", d, 4096 * TB); return SQ_ERR_UNSUPPORTED; }
-    if (!ws || ws_bytes < total) { set_error("sq_tomography_batched_ws: workspace needs %zu bytes, got %zu", total, ws_bytes); return SQ_ERR_WORKSPACE; }
-    char* w = (char*)ws;
     TomoBigArgs a;
-    a.V = V; a.est = est; a.n_used = n_used; a.err = err;
-    a.sumsq = (double*)(w + off[0]); a.bm_a = (double*)(w + off[1]); a.bm_b = (double*)(w + off[2]);
-    a.bcnt = (double*)(w + off[3]); a.errp = (double*)(w + off[4]); a.done = (int*)(w + off[5]);
-    a.B = B; a.d = d; a.nblk = nblk; a.NB = NB; a.logNB = logNB; a.norm_inf = norm_inf; a.stop = stop; a.delta = delta;
-    a.seed = seed; a.vec_offset = vec_offset;
-    int rc = sq_row_sqnorms(V, B, d, (double*)(w + off[0]), stream_);
+    int rc = tomo_big_prepare(a, V, B, d, delta, norm_inf, stop, seed, vec_offset, est, n_used, err, ws, ws_bytes,
+                              "sq_tomography_batched_ws");
     if (rc) return rc;
-    tomo_big_init_kernel<<<(unsigned)((B + 255) / 256), 256, 0, stream>>>(a);
-    SQ_LAUNCH_CHECK("tomo_big_init_kernel");
-    size_t sm_top = (size_t)(4 * NB + 32) * sizeof(double);
-    size_t sm_blk = (size_t)(6 * TB + 32) * sizeof(double);
-    SQ_CUDA(cudaFuncSetAttribute(tomo_big_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_top));
-    SQ_CUDA(cudaFuncSetAttribute(tomo_big_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_blk));
-    dim3 gblk(nblk, (unsigned)B);
-    int ttop = NB < 64 ? 64 : (NB > 512 ? 512 : NB);   // register budget: ~96 per thread
+    rc = tomo_big_phase(a, 0, 0, a.nblk, stream);
+    if (rc) return rc;
     for (int at = 0; at < sched_len; ++at) {
         SQ_REQUIRE(sched_host[at] >= 1.0 && sched_host[at] < 9.0e15, "sq_tomography_batched_ws: schedule entry out of range");
         a.at = at; a.N = sched_host[at];
-        tomo_big_mass_kernel<<<gblk, 256, 0, stream>>>(a);
-        tomo_big_top_kernel<<<(unsigned)B, ttop, sm_top, stream>>>(a, 1);
-        tomo_big_block_kernel<<<gblk, 256, sm_blk, stream>>>(a, 1);
-        tomo_big_top_kernel<<<(unsigned)B, ttop, sm_top, stream>>>(a, 2);
-        tomo_big_block_kernel<<<gblk, 256, sm_blk, stream>>>(a, 2);
-        tomo_big_finish_kernel<<<(unsigned)B, 256, 0, stream>>>(a);
-        SQ_LAUNCH_CHECK("tomo_big kernels");
+        for (int phase = 1; phase <= 3; ++phase) {
+            rc = tomo_big_phase(a, phase, 0, a.nblk, stream);
+            if (rc) return rc;
+        }
     }
     return SQ_OK;
+}
+
+extern "C" int sq_tomography_workspace_layout(long long B, int d, long long out[8]) {
+    SQ_REQUIRE(out && B >= 1 && d > sq_tomography_max_fused_dim(), "sq_tomography_workspace_layout: needs B >= 1 and d > %d",
+               sq_tomography_max_fused_dim());
+    int nblk, NB, logNB;
+    size_t off[6], total;
+    tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
+    out[0] = nblk;
+    out[1] = TB;
+    for (int i = 0; i < 5; ++i) out[2 + i] = (long long)off[1 + i];   // bm_a, bm_b, bcnt, errp, done
+    out[7] = (long long)total;
+    return SQ_OK;
+}
+
+extern "C" int sq_tomography_sharded_phase(const double* V, long long B, int d, double delta, int norm_inf, int stop,
+                                           double n_measure, int attempt, unsigned long long seed,
+                                           unsigned long long vec_offset, double* est, double* n_used, double* err,
+                                           void* ws, size_t ws_bytes, int blk_lo, int blk_hi, int phase,
+                                           void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(V && est && n_used && err, "sq_tomography_sharded_phase: null pointer");
+    SQ_REQUIRE(d > sq_tomography_max_fused_dim(), "sq_tomography_sharded_phase: d=%d fits one CTA; shard by vector instead", d);
+    SQ_REQUIRE(B >= 1 && B <= 65535, "sq_tomography_sharded_phase: B=%lld outside [1, 65535]", B);
+    SQ_REQUIRE(phase >= 0 && phase <= 3, "sq_tomography_sharded_phase: phase must be 0..3");
+    SQ_REQUIRE(delta > 0.0 && attempt >= 0 && attempt < 128, "sq_tomography_sharded_phase: bad delta / attempt");
+    SQ_REQUIRE(phase == 0 || (n_measure >= 1.0 && n_measure < 9.0e15), "sq_tomography_sharded_phase: n_measure out of range");
+    TomoBigArgs a;
+    int rc = tomo_big_prepare(a, V, B, d, delta, norm_inf, stop, seed, vec_offset, est, n_used, err, ws, ws_bytes,
+                              "sq_tomography_sharded_phase");
+    if (rc) return rc;
+    SQ_REQUIRE(blk_lo >= 0 && blk_lo <= blk_hi && blk_hi <= a.nblk, "sq_tomography_sharded_phase: block range [%d, %d) outside [0, %d]",
+               blk_lo, blk_hi, a.nblk);
+    a.at = attempt; a.N = phase == 0 ? 1.0 : n_measure;
+    return tomo_big_phase(a, phase, blk_lo, blk_hi, stream);
 }
 
 // ---- incremental mode with speculative attempt lanes -----------------------------------------

@@ -20,6 +20,8 @@ import os
 import warnings
 from collections import Counter
 
+import ctypes
+
 import numpy as np
 import torch
 
@@ -274,6 +276,83 @@ def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, v
         sched.ctypes.data, len(sched), seed_, vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err),
         dv.ptr(tr), dv.ptr(att), dv.stream_ptr()), "sq_tomography_batched")
     return est, n_used, err, tr, att, sched
+
+
+def tomography_sharded(A, delta, N=None, norm='L2', stop_when_reached_accuracy=True, incremental_measure=True,
+                       faster_measure_increment=0):
+    """``tomography(A, delta)`` computed by all the ranks of the process group together (collective: every rank
+    passes the same ``A``, [d] or [B, d], and gets the same estimate back as a device tensor).
+
+    Short vectors (d <= sq_tomography_max_fused_dim()) are dealt to the ranks by vector.  A long vector is cut
+    into blocks of leaves and rank r splits the measurement counts of its share of the blocks (reference: the
+    loop of real_tomography, Utility.py:259-402); per attempt the ranks exchange two small sums
+    (block masses, block error partials).  Draws are keyed by (vector, block, node), so the estimate is
+    bit-identical to the single-GPU one for any number of ranks."""
+    import torch.distributed as dist
+    if norm not in ('L2', 'inf'):
+        raise ValueError("norm must be 'L2' or 'inf'")
+    V = A if isinstance(A, torch.Tensor) else dv.to_device(np.asarray(A, dtype=np.float64))
+    one = V.dim() == 1
+    V = V.reshape(1, -1) if one else V
+    V = V.contiguous()
+    B, d = V.shape
+    rank, world = dv.dist_info()
+    _sync_state()
+    stop = bool(stop_when_reached_accuracy)
+    if world == 1 or B == 0:
+        est = _tomography_device(V, delta, N, norm, stop, incremental_measure, faster_measure_increment)[0]
+        return est[0] if one else est
+    seed_, off = _take_streams(B)
+    est = torch.zeros_like(V)
+    if d <= _cabi.lib.sq_tomography_max_fused_dim():
+        lo, hi = (B * rank) // world, (B * (rank + 1)) // world
+        if hi > lo:
+            est[lo:hi] = _tomography_device(V[lo:hi], delta, N, norm, stop, incremental_measure,
+                                            faster_measure_increment, vec_offset=off + lo, seed_=seed_)[0]
+        dist.all_reduce(est)                       # every row is written by one rank, zero elsewhere
+        return est[0] if one else est
+    if B > 65535:
+        raise ValueError("tomography_sharded: at most 65535 long vectors per call")
+    if N is None:
+        N = tomography_num_measurements(d, delta, norm)
+    sched = tomography_schedule(int(N), faster_measure_increment).astype(np.float64) if incremental_measure \
+        else np.asarray([float(int(N))])
+    if incremental_measure and not stop:
+        sched = sched[-1:]
+    lay = (ctypes.c_longlong * 8)()
+    _cabi.check(_cabi.lib.sq_tomography_workspace_layout(B, d, lay), "sq_tomography_workspace_layout")
+    nblk, tb, nb = int(lay[0]), int(lay[1]), int(lay[7])
+    ws = dv.workspace(nb)
+
+    def view(i, dtype=torch.float64, cols=nblk):
+        o = int(lay[2 + i])
+        return ws[o:o + B * cols * (8 if dtype == torch.float64 else 4)].view(dtype).view(B, cols)
+    bm = ws[int(lay[2]):int(lay[4])].view(torch.float64)      # bm_a | bm_b, adjacent in the layout
+    bm_a, bm_b, errp = view(0), view(1), view(3)
+    done = ws[int(lay[6]):int(lay[6]) + 4 * B].view(torch.int32)
+    blo, bhi = (nblk * rank) // world, (nblk * (rank + 1)) // world
+    n_used, err = dv.empty((B,)), dv.empty((B,))
+
+    def phase(ph, at, n_meas):
+        _cabi.check(_cabi.lib.sq_tomography_sharded_phase(
+            dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, 1 if (stop and incremental_measure) else 0,
+            float(n_meas), at, seed_, off, dv.ptr(est), dv.ptr(n_used), dv.ptr(err), dv.ptr(ws), nb, blo, bhi, ph,
+            dv.stream_ptr()), "sq_tomography_sharded_phase")
+    phase(0, 0, 1.0)
+    for at, n_meas in enumerate(sched):
+        phase(1, at, n_meas)
+        bm_a[:, :blo] = 0; bm_a[:, bhi:] = 0; bm_b[:, :blo] = 0; bm_b[:, bhi:] = 0
+        dist.all_reduce(bm)
+        phase(2, at, n_meas)
+        errp[:, :blo] = 0; errp[:, bhi:] = 0
+        dist.all_reduce(errp, op=dist.ReduceOp.MAX if norm == 'inf' else dist.ReduceOp.SUM)
+        phase(3, at, n_meas)
+        if stop and incremental_measure and at + 1 < len(sched) and bool(done.all()):
+            break
+    est[:, :blo * tb] = 0
+    est[:, bhi * tb:] = 0
+    dist.all_reduce(est)
+    return est[0] if one else est
 
 
 def real_tomography(V, N=None, delta=None, stop_when_reached_accuracy=True, norm='L2', incremental_measure=True,

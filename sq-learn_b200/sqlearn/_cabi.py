@@ -27,6 +27,10 @@ SIGNATURES = {
     "sq_tomography_workspace_bytes": (c_size_t, [c_ll, c_int]),
     "sq_tomography_batched_ws": (c_int, [c_void_p, c_ll, c_int, c_double, c_int, c_int, c_void_p, c_int, c_ull, c_ull,
                                          c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "sq_tomography_workspace_layout": (c_int, [c_ll, c_int, c_void_p]),
+    "sq_tomography_sharded_phase": (c_int, [c_void_p, c_ll, c_int, c_double, c_int, c_int, c_double, c_int, c_ull, c_ull,
+                                            c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int,
+                                            c_void_p]),
     "sq_tomography_batched_spec": (c_int, [c_void_p, c_ll, c_int, c_double, c_int, c_void_p, c_int, c_int, c_ull, c_ull,
                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "sq_qmeans_assign_workspace_bytes": (c_size_t, [c_ll, c_int, c_int]),

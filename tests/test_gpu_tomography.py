@@ -231,6 +231,76 @@ def test_long_vectors(cuda, d):
     assert (r3 < 0.05).all()
 
 
+@pytest.mark.parametrize("norm_inf", [0, 1])
+def test_sharded_phases_equal_the_single_call(cuda, norm_inf):
+    """sq_tomography_sharded_phase with the leaf blocks dealt to 3 emulated ranks (own workspace and output each,
+    block masses and error partials merged the way the host's all-reduce does) gives sq_tomography_batched_ws's
+    result bit for bit, stop rule included"""
+    import ctypes
+    import torch
+    from oracle import quantum_utility as qu
+    from sqlearn import _cabi, _device as dv
+    rs = np.random.RandomState(12)
+    B, d, delta, R = 2, 50000, 0.3 if not norm_inf else 0.02, 3
+    V = rs.uniform(-1, 1, (B, d))
+    sched = qu.schedule(qu.tomography_N(d, delta, "inf" if norm_inf else "L2")).astype(float)[-12:]
+    want = _big(V, delta, sched, stop=1, norm_inf=norm_inf, seed=21, vec_offset=4)
+    Vd = torch.as_tensor(V).cuda()
+    lay = (ctypes.c_longlong * 8)()
+    _cabi.check(_cabi.lib.sq_tomography_workspace_layout(B, d, lay), "layout")
+    nblk, tb, nb = int(lay[0]), int(lay[1]), int(lay[7])
+    assert nblk == -(-d // tb) and nb == _cabi.lib.sq_tomography_workspace_bytes(B, d)
+    ranks = []
+    for r in range(R):
+        ws = torch.zeros(nb, dtype=torch.uint8, device="cuda")
+        f = lambda i, ws=ws: ws[int(lay[2 + i]):int(lay[2 + i]) + B * nblk * 8].view(torch.float64).view(B, nblk)
+        ranks.append(dict(ws=ws, est=torch.zeros_like(Vd), n_used=torch.zeros(B, dtype=torch.float64, device="cuda"),
+                          err=torch.zeros(B, dtype=torch.float64, device="cuda"), bm_a=f(0), bm_b=f(1), errp=f(3),
+                          done=ws[int(lay[6]):int(lay[6]) + 4 * B].view(torch.int32),
+                          lo=nblk * r // R, hi=nblk * (r + 1) // R))
+
+    def phase(rk, ph, at, n_meas):
+        _cabi.check(_cabi.lib.sq_tomography_sharded_phase(
+            Vd.data_ptr(), B, d, delta, norm_inf, 1, float(n_meas), at, 21, 4, rk["est"].data_ptr(),
+            rk["n_used"].data_ptr(), rk["err"].data_ptr(), rk["ws"].data_ptr(), nb, rk["lo"], rk["hi"], ph,
+            dv.stream_ptr()), "sharded_phase")
+
+    def merge(key, op):
+        for rk in ranks:
+            rk[key][:, :rk["lo"]] = 0
+            rk[key][:, rk["hi"]:] = 0
+        tot = ranks[0][key].clone()
+        for rk in ranks[1:]:
+            tot = op(tot, rk[key])
+        for rk in ranks:
+            rk[key].copy_(tot)
+    for rk in ranks:
+        phase(rk, 0, 0, 1.0)
+    for at, n_meas in enumerate(sched):
+        for rk in ranks:
+            phase(rk, 1, at, n_meas)
+        merge("bm_a", torch.add); merge("bm_b", torch.add)
+        for rk in ranks:
+            phase(rk, 2, at, n_meas)
+        merge("errp", torch.maximum if norm_inf else torch.add)
+        for rk in ranks:
+            phase(rk, 3, at, n_meas)
+        if bool(ranks[0]["done"].all()):
+            break
+    est = torch.zeros_like(Vd)
+    for rk in ranks:
+        est[:, rk["lo"] * tb:rk["hi"] * tb] = rk["est"][:, rk["lo"] * tb:rk["hi"] * tb]
+    torch.cuda.synchronize()
+    assert np.array_equal(est.cpu().numpy(), want[0])
+    for rk in ranks:
+        assert np.array_equal(rk["n_used"].cpu().numpy(), want[1]) and np.array_equal(rk["err"].cpu().numpy(), want[2])
+    assert (want[1] < sched[-1]).any() or (want[2] > delta).any()     # the stop rule was exercised (or never met)
+    # argument checks
+    assert _cabi.lib.sq_tomography_sharded_phase(Vd.data_ptr(), B, d, delta, 0, 1, 10.0, 0, 1, 0, est.data_ptr(),
+                                                 ranks[0]["n_used"].data_ptr(), ranks[0]["err"].data_ptr(),
+                                                 ranks[0]["ws"].data_ptr(), nb, 0, nblk + 1, 1, dv.stream_ptr()) != 0
+
+
 def test_long_vector_law_matches_oracle(cuda):
     """d = 5000 at a small N: error and one component's estimate follow the oracle's law"""
     from oracle import quantum_utility as qu

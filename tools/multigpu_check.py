@@ -57,10 +57,29 @@ def main():
         ok &= np.allclose(pca.singular_values_, w["singular_values_"], rtol=1e-10)
         ok &= np.allclose(pca.components_, w["components_"], atol=1e-8)
         ok &= abs(pca.muA - w["muA"]) <= 1e-10 * w["muA"]
+        # one long vector over all ranks (leaf blocks sharded) and a batch of short ones (dealt by vector):
+        # bit-identical to the single-GPU routine with the same streams
+        for shape, delta, inc in [((1, 300000), 0.05, False), ((2, 70000), 0.3, True), ((37, 500), 0.2, True)]:
+            g = torch.Generator(device="cuda"); g.manual_seed(99)
+            V = torch.rand(shape, generator=g, device="cuda", dtype=torch.float64) * 2 - 1
+            V /= V.norm(dim=1, keepdim=True)
+            for norm in ("L2", "inf"):
+                U.seed(11)
+                got = U.tomography_sharded(V, delta, norm=norm, incremental_measure=inc)
+                U.seed(11)
+                ref = U._tomography_device(V, delta, None, norm, True, inc, 0)[0]
+                same = bool(torch.equal(got, ref))
+                if not same:
+                    print("rank %d: tomography_sharded differs for %s %s: max |diff| %g" % (
+                        rank, shape, norm, float((got - ref).abs().max())), flush=True)
+                ok &= same
+                lim = delta if norm == "L2" else delta
+                e = (got - V).norm(dim=1) if norm == "L2" else (got - V).abs().amax(dim=1)
+                ok &= bool((e <= lim).all()) if inc else True
     flag = torch.tensor([1.0 if ok else 0.0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print("multigpu_check world=%d: %s (q-means labels/centres/inertia, replicated noisy centres, qPCA sigma/V/mu)"
+        print("multigpu_check world=%d: %s (q-means labels/centres/inertia, replicated noisy centres, qPCA sigma/V/mu, sharded tomography bit-identical)"
               % (world, "OK" if flag.item() == 1 else "MISMATCH"))
     dist.destroy_process_group()
     sys.exit(0 if flag.item() == 1 else 1)
