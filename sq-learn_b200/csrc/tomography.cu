@@ -84,7 +84,8 @@ __device__ __forceinline__ void build_tree(double* mass, int L, int logL, int ti
     __syncthreads();
 }
 
-// top-down conditional binomial splitting; cnt[1] must be set by the caller
+// top-down conditional binomial splitting; cnt[1] must be set by the caller.  cnt may alias mass: a node's
+// two child masses are read by that node alone, right before it stores the two child counts over them.
 __device__ __forceinline__ void split_tree(const double* mass, double* cnt, int logL, int tid, int T,
                                            unsigned long long seed, unsigned long long vec, unsigned stream) {
     for (int lev = 0; lev < logL; ++lev) {
@@ -93,9 +94,10 @@ __device__ __forceinline__ void split_tree(const double* mass, double* cnt, int 
         for (int i = first + tid; i < 2 * first; i += T) {
             double n = cnt[i];
             double left = 0.0;
+            const double ml = mass[2 * i], mr = mass[2 * i + 1];
             if (n > 0.0) {
                 Philox rng(seed, vec, stream, (unsigned)i);
-                left = binomial_split(n, mass[2 * i], mass[2 * i + 1], rng);
+                left = binomial_split(n, ml, mr, rng);
             }
             cnt[2 * i] = left;
             cnt[2 * i + 1] = n - left;
@@ -104,21 +106,50 @@ __device__ __forceinline__ void split_tree(const double* mass, double* cnt, int 
     __syncthreads();
 }
 
-// inclusive prefix sums of src[0..L) into dst[0..L) (L a power of two >= 2); every thread scans a
-// contiguous chunk, the chunk totals are scanned by warp 0.  Fixed order: deterministic.
-__device__ __forceinline__ void block_scan(const double* src, double* dst, int L, double* red, int tid, int T) {
-    const int per = (L + T - 1) / T;
-    const int i0 = tid * per, i1 = min(L, i0 + per);
-    double s = 0.0;
-    for (int i = i0; i < i1; ++i) { s += src[i]; dst[i] = s; }
-    __syncthreads();                      // red may still be read by an earlier reduction
-    // chunk totals -> exclusive offsets (T <= 512: at most 16 warps)
-    double w = warp_scan_incl(s);
-    if ((tid & 31) == 31) red[tid >> 5] = w;
+// The fused kernel's results must not depend on how many threads work on a vector (the host picks
+// that from the batch size).  Draws are keyed by node / sample index already; the two helpers below
+// fix the order of the floating-point additions as a function of L alone.
+
+// sum_{i < L} f(i): pairs (i, i + L/2) are added in registers, then the L/2 partials are halved in
+// scratch[0..L/2) until one is left.  f may have side effects on other arrays (it runs once per i).
+template <class F>
+__device__ __forceinline__ double canon_sum(F f, double* scratch, int L, int tid, int T) {
+    const int h = L >> 1;
+    for (int i = tid; i < h; i += T) { double lo = f(i), hi = f(i + h); scratch[i] = lo + hi; }
+    for (int s = h >> 1; s >= 1; s >>= 1) {
+        __syncthreads();
+        for (int i = tid; i < s; i += T) scratch[i] += scratch[i + s];
+    }
     __syncthreads();
-    double off = w - s;
-    for (int k = 0; k < (tid >> 5); ++k) off += red[k];
-    for (int i = i0; i < i1; ++i) dst[i] += off;
+    const double r = scratch[0];
+    __syncthreads();  // scratch is reused by the caller
+    return r;
+}
+
+// in-place inclusive prefix sums of x[0..L): groups of 32 consecutive entries by the warp shuffle network,
+// group totals accumulated in order by warp 0 (tot: scratch of L/32 + 1 doubles)
+__device__ __forceinline__ void canon_scan(double* x, int L, double* tot, int tid, int T) {
+    const int lane = tid & 31, warp = tid >> 5, nw = T >> 5;
+    const int G = (L + 31) >> 5;
+    for (int g = warp; g < G; g += nw) {
+        const int i = (g << 5) + lane;
+        double s = warp_scan_incl(i < L ? x[i] : 0.0);
+        if (i < L) x[i] = s;
+        if (lane == 31) tot[g] = s;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        double base = 0.0;
+        for (int c = 0; c < G; c += 32) {
+            const double t = (c + lane < G) ? tot[c + lane] : 0.0;
+            const double s = warp_scan_incl(t);
+            __syncwarp();
+            if (c + lane < G) tot[c + lane] = base + (s - t);      // exclusive offset of the group
+            base += __shfl_sync(0xffffffffu, s, 31);
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < L; i += T) x[i] += tot[i >> 5];
     __syncthreads();
 }
 
@@ -146,38 +177,37 @@ __device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL
     }
 }
 
+// shared memory of one vector, in doubles: P [L] | A [2L] (sum tree, then counts in place; CDF, int counts
+// and reduction scratch on the direct path) | tot [L/32 + 1 <= 160]
+__host__ __device__ inline size_t tomo_smem_doubles(int L) { return (size_t)3 * L + 160; }
+
 __global__ void tomo_fused_kernel(TomoArgs a) {
     extern __shared__ double sm[];
-    const int L = a.L, d = a.d, tid = threadIdx.x, T = blockDim.x;
-    double* v = sm;            // [L]
-    double* P = v + L;         // [L]
-    double* mass = P + L;      // [2L]
-    double* cnt = mass + 2 * L;  // [2L]
-    double* red = cnt + 2 * L;   // [32]
+    const int L = a.L, d = a.d, tid = threadIdx.x, T = blockDim.x, H = L >> 1;
+    double* P = sm;             // [L]
+    double* A = P + L;          // [2L]
+    double* tot = A + 2 * L;    // [160]
+    double* mass = A;
+    double* cnt = A;
 
     const long long b = blockIdx.x;
     const unsigned long long vec = a.vec_offset + (unsigned long long)b;
     const double* Vg = a.V + b * (long long)d;
 
-    double ss = 0.0;
-    for (int i = tid; i < L; i += T) {
-        double x = (i < d) ? Vg[i] : 0.0;
-        v[i] = x;
-        ss += x * x;
-    }
-    ss = block_sum(ss, red, tid, T);
-    double nrm = sqrt(ss);
+    // The input stays in global memory (L2) and is re-read by the passes of an attempt.
+    // ||V||^2 by the sum tree: an order of additions that depends on L only.
+    for (int i = tid; i < L; i += T) { double x = (i < d) ? Vg[i] : 0.0; mass[L + i] = x * x; }
+    build_tree(mass, L, a.logL, tid, T);
+    const double nrm = sqrt(mass[1]);
     // np.isclose(nrm, 1, rtol=1e-2): |nrm - 1| <= 1e-8 + 1e-2
-    bool keep = fabs(nrm - 1.0) <= (1e-8 + 1e-2);
+    const bool keep = fabs(nrm - 1.0) <= (1e-8 + 1e-2);
     if (!(nrm > 0.0)) {
         // zero (or NaN) vector: the reference divides by zero; we return zeros
         for (int i = tid; i < d; i += T) a.est[b * (long long)d + i] = 0.0;
-        if (tid == 0) { a.n_used[b] = 0.0; a.err[b] = 0.0; if (a.attempts) a.attempts[b] = 0; }
+        if (tid == 0 && a.spec != 1) { a.n_used[b] = 0.0; a.err[b] = 0.0; if (a.attempts) a.attempts[b] = 0; }
         return;
     }
-    if (!keep) {
-        for (int i = tid; i < L; i += T) v[i] = v[i] / nrm;
-    }
+    auto vin = [&](int i) { return (i < d) ? (keep ? Vg[i] : Vg[i] / nrm) : 0.0; };
     __syncthreads();
 
     double n_last = 0.0, err_last = 0.0;
@@ -191,6 +221,7 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
     if (a.spec == 2) { at0 = min(a.stop_idx[b], a.sched_len - 1); at_end = at0 + 1; }
     for (int at = at0; at < at_end; at += step) {
         if (a.spec == 1) {
+            __syncthreads();
             if (tid == 0) s_cut = *((volatile int*)&a.stop_idx[b]);
             __syncthreads();
             if (at > s_cut) break;          // an earlier attempt already succeeded
@@ -198,68 +229,70 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
         const double N = a.sched[at];
         // Few measurements: draw them one by one (N/T categorical draws per thread, log2(d) probes each)
         // instead of walking the tree, whose log2(d) dependent binomial draws cost more than that.
-        const bool direct = N <= 64.0 * T;
-        int* cnt_i = reinterpret_cast<int*>(cnt);
+        // The rule depends on (N, L) only.
+        const bool direct = N <= 64.0 * (L < 32 ? 32 : (L > 512 ? 512 : L));
+        int* cnt_i = reinterpret_cast<int*>(A + L);      // [L] ints = A[L .. L + L/2)
+        double e;
         if (direct) {
-            for (int i = tid; i < L; i += T) { P[i] = v[i] * v[i]; cnt_i[i] = 0; }
+            for (int i = tid; i < L; i += T) { double x = vin(i); A[i] = x * x; cnt_i[i] = 0; }
             __syncthreads();
-            block_scan(P, mass, L, red, tid, T);                 // stage-1 CDF in mass[0..L)
-            sample_direct(mass, L, a.logL, mass[L - 1], cnt_i, (long long)N, tid, T, a.seed, vec, (unsigned)(2 * at));
+            canon_scan(A, L, tot, tid, T);                         // stage-1 CDF in A[0..L)
+            sample_direct(A, L, a.logL, A[L - 1], cnt_i, (long long)N, tid, T, a.seed, vec, (unsigned)(2 * at));
             __syncthreads();
-            double sminus = 0.0;
-            for (int i = tid; i < L; i += T) {
-                double p = sqrt((double)cnt_i[i] / N);
+            const double sminus = canon_sum([&](int i) {
+                double p = sqrt((double)cnt_i[i] / N), x = vin(i);
                 P[i] = p;
-                double ap = 0.5 * (v[i] + p), am = 0.5 * (v[i] - p);
-                mass[L + i] = ap * ap;
-                sminus += am * am;
-            }
-            sminus = block_sum(sminus, red, tid, T);
-            __syncthreads();
+                double ap = 0.5 * (x + p), am = 0.5 * (x - p);
+                A[i] = ap * ap;                                    // (the stage-1 CDF is not needed any more)
+                return am * am;
+            }, A + L + H, L, tid, T);
             for (int i = tid; i < L; i += T) cnt_i[i] = 0;
-            block_scan(mass + L, mass, L, red, tid, T);          // stage-2 '+' CDF; the '-' outcomes are one lump
-            sample_direct(mass, L, a.logL, mass[L - 1] + sminus, cnt_i, (long long)N, tid, T, a.seed, vec,
+            __syncthreads();
+            canon_scan(A, L, tot, tid, T);                         // stage-2 '+' CDF; the '-' outcomes are one lump
+            sample_direct(A, L, a.logL, A[L - 1] + sminus, cnt_i, (long long)N, tid, T, a.seed, vec,
                           (unsigned)(2 * at + 1));
             __syncthreads();
-            for (int i = tid; i < L; i += T) cnt[L + i] = (double)cnt_i[i];   // the sign rule below reads cnt[L + i]
-            __syncthreads();
         } else {
-        // ---- stage 1 ----
-        for (int i = tid; i < L; i += T) mass[L + i] = v[i] * v[i];
-        build_tree(mass, L, a.logL, tid, T);
-        if (tid == 0) cnt[1] = N;
-        split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at));
-        // ---- stage 2 ----
-        double sminus = 0.0;
-        for (int i = tid; i < L; i += T) {
-            double p = sqrt(cnt[L + i] / N);
-            P[i] = p;
-            double ap = 0.5 * (v[i] + p), am = 0.5 * (v[i] - p);
-            mass[L + i] = ap * ap;
-            sminus += am * am;
-        }
-        sminus = block_sum(sminus, red, tid, T);
-        build_tree(mass, L, a.logL, tid, T);
-        if (tid == 0) {
-            Philox rng(a.seed, vec, (unsigned)(2 * at + 1), 0u);
-            cnt[1] = binomial_split(N, mass[1], sminus, rng);
-        }
-        split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at + 1));
+            // ---- stage 1 ----
+            for (int i = tid; i < L; i += T) { double x = vin(i); mass[L + i] = x * x; }
+            build_tree(mass, L, a.logL, tid, T);
+            if (tid == 0) cnt[1] = N;
+            split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at));
+            // ---- stage 2 ----
+            const double sminus = canon_sum([&](int i) {
+                double p = sqrt(cnt[L + i] / N), x = vin(i);
+                P[i] = p;
+                double ap = 0.5 * (x + p), am = 0.5 * (x - p);
+                mass[L + i] = ap * ap;                             // (leaf slot i: read and written by this call only)
+                return am * am;
+            }, A, L, tid, T);
+            build_tree(mass, L, a.logL, tid, T);
+            if (tid == 0) {
+                Philox rng(a.seed, vec, (unsigned)(2 * at + 1), 0u);
+                cnt[1] = binomial_split(N, mass[1], sminus, rng);
+            }
+            split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at + 1));
         }
         // ---- sign rule + error ----
-        double e = 0.0;
-        for (int i = tid; i < L; i += T) {
+        auto sign_and_diff = [&](int i) {
             double p = P[i];
-            double est = (cnt[L + i] > 0.4 * p * p * N) ? p : -p;
+            double c2 = direct ? (double)cnt_i[i] : cnt[L + i];
+            double est = (c2 > 0.4 * p * p * N) ? p : -p;
             P[i] = est;
-            double df = v[i] - est;
-            if (i < d) e = a.norm_inf ? fmax(e, fabs(df)) : e + df * df;
+            return (i < d) ? vin(i) - est : 0.0;
+        };
+        if (a.norm_inf) {
+            double m = 0.0;
+            for (int i = tid; i < L; i += T) m = fmax(m, fabs(sign_and_diff(i)));
+            e = block_max(m, tot, tid, T);
+        } else {
+            e = sqrt(canon_sum([&](int i) { double df = sign_and_diff(i); return df * df; }, A, L, tid, T));
         }
-        e = a.norm_inf ? block_max(e, red, tid, T) : sqrt(block_sum(e, red, tid, T));
         n_last = N;
         err_last = e;
         n_att = at + 1;
         if (a.trace) {
+            __syncthreads();
             double* tr = a.trace + (b * a.sched_len + at) * (long long)d;
             for (int i = tid; i < d; i += T) tr[i] = P[i];
         }
@@ -276,6 +309,20 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
     if (tid == 0) { a.n_used[b] = n_last; a.err[b] = err_last; if (a.attempts) a.attempts[b] = n_att; }
 }
 
+// Threads per vector: with few vectors in flight the latency of a vector counts (one thread per leaf, at most 512);
+// with many, throughput does (few threads per vector keep every lane busy through the upper
+// levels of the tree and let 9+ vectors share an SM).  The results do not depend on the choice.
+static int tomo_launch(const TomoArgs& a, long long B, int lanes, cudaStream_t stream) {
+    const int L = a.L;
+    const bool many = B * (long long)lanes >= 4096;
+    int threads = many ? L / 8 : L;
+    threads = threads < 32 ? 32 : (threads > 512 ? 512 : threads);
+    const size_t smem = tomo_smem_doubles(L) * sizeof(double);
+    SQ_CUDA(cudaFuncSetAttribute(tomo_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tomo_fused_kernel<<<dim3((unsigned)B, lanes), threads, smem, stream>>>(a);
+    SQ_LAUNCH_CHECK("tomo_fused_kernel");
+    return SQ_OK;
+}
 
 // ---------------------------------------------------------------------------
 // Long vectors (d > 4096): the same algorithm split over the grid.
@@ -502,9 +549,6 @@ extern "C" int sq_tomography_batched(const double* V, long long B, int d, double
     while (L < d) { L <<= 1; ++logL; }
     a.L = L; a.logL = logL; a.sched_len = sched_len; a.norm_inf = norm_inf; a.stop = stop; a.delta = delta;
     a.seed = seed; a.vec_offset = vec_offset;
-    int threads = L < 32 ? 32 : (L > 512 ? 512 : L);
-    size_t smem = (size_t)(6 * L + 32) * sizeof(double);
-    SQ_CUDA(cudaFuncSetAttribute(tomo_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // gridDim.x limit is 2^31-1; batches beyond that are split
     long long done = 0;
     while (done < B) {
@@ -514,8 +558,9 @@ extern "C" int sq_tomography_batched(const double* V, long long B, int d, double
         if (trace) c.trace = trace + done * sched_len * d;
         if (attempts) c.attempts = attempts + done;
         c.vec_offset = vec_offset + (unsigned long long)done;
-        tomo_fused_kernel<<<(unsigned)nb, threads, smem, stream>>>(c);
-        SQ_LAUNCH_CHECK("tomo_fused_kernel");
+        c.B = nb;
+        int rc = tomo_launch(c, nb, 1, stream);
+        if (rc) return rc;
         done += nb;
     }
     return SQ_OK;
@@ -694,14 +739,10 @@ extern "C" int sq_tomography_batched_spec(const double* V, long long B, int d, d
     while (L < d) { L <<= 1; ++logL; }
     a.L = L; a.logL = logL; a.sched_len = sched_len; a.norm_inf = norm_inf; a.stop = 1; a.delta = delta;
     a.seed = seed; a.vec_offset = vec_offset;
-    int threads = L < 32 ? 32 : (L > 512 ? 512 : L);
-    size_t smem = (size_t)(6 * L + 32) * sizeof(double);
-    SQ_CUDA(cudaFuncSetAttribute(tomo_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     tomo_fill_int_kernel<<<(unsigned)((B + 255) / 256), 256, 0, stream>>>(stop_idx, B, sched_len);
     a.spec = 1;
-    tomo_fused_kernel<<<dim3((unsigned)B, lanes), threads, smem, stream>>>(a);
+    int rc = tomo_launch(a, B, lanes, stream);
+    if (rc) return rc;
     a.spec = 2;
-    tomo_fused_kernel<<<(unsigned)B, threads, smem, stream>>>(a);
-    SQ_LAUNCH_CHECK("tomo_fused_kernel (speculative)");
-    return SQ_OK;
+    return tomo_launch(a, B, 1, stream);
 }

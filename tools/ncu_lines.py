@@ -17,7 +17,7 @@ for r in csv.reader(io.StringIO(src)):
     if len(r) == 2 and r[0] == "File Path": cur = r[1].split("/")[-1]; continue
     if len(r) == 2: continue
     if r and r[0] == "Line No": h2 = r; continue
-    if r and r[0].isdigit(): lines.append((cur, int(r[0]), r))
+    if r and r[0].isdigit() and r[h2.index("# Samples")].isdigit() and r[h2.index("Instructions Executed")].isdigit(): lines.append((cur, int(r[0]), r))
 isamp, iex = h2.index("# Samples"), h2.index("Instructions Executed")
 tot = sum(int(r[iex]) for f, l, r in lines); ts = sum(int(r[isamp]) for f, l, r in lines)
 print("warp instructions", tot, "samples", ts)
