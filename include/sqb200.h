@@ -173,6 +173,17 @@ int sq_fejer_sample_bruteforce(const double* M, const double* x, long long B, un
  * make_gaussian_est (Utility.py:88-104), introduce_error(_array) (:68-73).  */
 int sq_truncnorm_add(const double* x, long long L, double halfwidth, unsigned long long seed,
                      unsigned long long offset, double* out, void* stream);
+/* The same with one half-width per element (half-widths <= 0 leave the element unchanged): the error model of
+ * QLSSVC.predict / get_P / get_h, introduce_error(p_i, err / (2 beta_i)) (sklearn/svm/_qSVM.py:199-214, 263-298). */
+int sq_truncnorm_add_each(const double* x, long long L, const double* halfwidth, unsigned long long seed,
+                          unsigned long long offset, double* out, void* stream);
+/* K[n, m] = k(X[n, d], Y[m, d]) for QLSSVC.get_kernel (_qSVM.py:375-389 over scikit-learn's pairwise kernels):
+ * kind 0 linear X Y^T, 1 poly (gamma X Y^T + coef0)^degree, 2 rbf exp(-gamma ||x - y||^2) (squared distances
+ * clipped at 0, exact zeros on the diagonal when Y == X), 3 sigmoid tanh(gamma X Y^T + coef0).  The dot products
+ * run on the fp64 tensor cores (sq_project).  ws from sq_kernel_matrix_workspace_bytes.                      */
+size_t sq_kernel_matrix_workspace_bytes(long long n, int m);
+int sq_kernel_matrix(const double* X, long long n, const double* Y, int m, int d, int kind, double gamma,
+                     double coef0, double degree, double* K, void* ws, size_t ws_bytes, void* stream);
 /* Binomial(n_i, pl_i/(pl_i+pr_i)) per element: the sampler the tomography
  * kernel splits its multinomial counts with (test hook; no reference
  * counterpart beyond RandomState.choice, Utility.py:54).                    */

@@ -130,3 +130,29 @@ def load_qpca(util=None):
               check_is_fitted=lambda *a, **k: None, _infer_dimension=None)
     exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
     return ns["qPCA"]
+
+
+def load_qsvm(util=None):
+    """Class ``QLSSVC`` of the reference (svm/_qSVM.py), AST-extracted and exec'd with the installed
+    scikit-learn's pairwise kernels / accuracy_score and a minimal BaseEstimator (only _validate_data)."""
+    from sklearn.metrics import accuracy_score
+    from sklearn.metrics.pairwise import linear_kernel, polynomial_kernel, rbf_kernel, sigmoid_kernel
+    util = util or load_utility()
+    path = os.path.join(REF, "sklearn", "svm", "_qSVM.py")
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        tree = ast.parse(open(path).read())
+    keep = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == "QLSSVC"]
+
+    class BaseEstimator:
+        def _validate_data(self, X, y=None, **kw):
+            X = np.asarray(X, dtype=np.float64)
+            self.n_features_in_ = X.shape[1]
+            return (X, np.asarray(y)) if y is not None else X
+
+    ns = dict(np=np, BaseEstimator=BaseEstimator, check_array=lambda X, **k: np.asarray(X),
+              check_is_fitted=lambda *a, **k: None, linear_kernel=linear_kernel, rbf_kernel=rbf_kernel,
+              sigmoid_kernel=sigmoid_kernel, polynomial_kernel=polynomial_kernel, accuracy_score=accuracy_score,
+              introduce_error=util.introduce_error, introduce_error_array=util.introduce_error_array)
+    exec(compile(ast.Module(body=keep, type_ignores=[]), path, "exec"), ns)
+    return ns["QLSSVC"]

@@ -2,8 +2,9 @@
 
 Mirrors the reference's public names for that path only:
 ``sqlearn.QuantumUtility`` (sklearn/QuantumUtility/Utility.py),
-``sqlearn.cluster.qMeans_`` (sklearn/cluster/_dmeans.py) and
-``sqlearn.decomposition.qPCA`` (sklearn/decomposition/_qPCA.py).  Compute runs
+``sqlearn.cluster.qMeans_`` (sklearn/cluster/_dmeans.py),
+``sqlearn.decomposition.qPCA`` (sklearn/decomposition/_qPCA.py) and
+``sqlearn.svm.QLSSVC`` (sklearn/svm/_qSVM.py).  Compute runs
 in hand-written sm_100a CUDA kernels behind the C ABI of ``include/sqb200.h``;
 importing this package fails if that library has not been built.
 """

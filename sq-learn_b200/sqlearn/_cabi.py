@@ -49,6 +49,10 @@ SIGNATURES = {
     "sq_sqdiff_sum": (c_int, [c_void_p, c_void_p, c_ll, c_void_p, c_void_p]),
     "sq_fejer_sample": (c_int, [c_void_p, c_void_p, c_ll, c_ull, c_ull, c_void_p, c_void_p]),
     "sq_fejer_sample_bruteforce": (c_int, [c_void_p, c_void_p, c_ll, c_ull, c_ull, c_void_p, c_void_p]),
+    "sq_truncnorm_add_each": (c_int, [c_void_p, c_ll, c_void_p, c_ull, c_ull, c_void_p, c_void_p]),
+    "sq_kernel_matrix_workspace_bytes": (c_size_t, [c_ll, c_int]),
+    "sq_kernel_matrix": (c_int, [c_void_p, c_ll, c_void_p, c_int, c_int, c_int, c_double, c_double, c_double,
+                                 c_void_p, c_void_p, c_size_t, c_void_p]),
     "sq_truncnorm_add": (c_int, [c_void_p, c_ll, c_double, c_ull, c_ull, c_void_p, c_void_p]),
     "sq_binomial_sample": (c_int, [c_void_p, c_void_p, c_void_p, c_ll, c_ull, c_ull, c_void_p, c_void_p]),
     "sq_mu_norms_workspace_bytes": (c_size_t, [c_ll, c_int, c_int]),
