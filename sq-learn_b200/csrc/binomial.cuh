@@ -35,9 +35,9 @@ __host__ __device__ inline double stirling_tail(double k) {
         return tab[(int)k];
 #endif
     }
-    double kp1 = k + 1.0;
-    double kp1sq = kp1 * kp1;
-    return (1.0 / 12.0 - (1.0 / 360.0 - 1.0 / 1260.0 / kp1sq) / kp1sq) / kp1;
+    // (1/12 - (1/360 - 1/1260/(k+1)^2)/(k+1)^2)/(k+1) with one division
+    const double r = 1.0 / (k + 1.0), r2 = r * r;
+    return r * (1.0 / 12.0 - r2 * (1.0 / 360.0 - r2 * (1.0 / 1260.0)));
 }
 
 // Binomial(n, p) with p = pl / (pl + pr).  pl, pr >= 0 are the two bucket
@@ -82,6 +82,9 @@ __host__ __device__ inline double binomial_split(double n, double pl, double pr,
         double alpha = (2.83 + 5.1 / b) * spq;
         double r = p / q;
         double m = floor((n + 1.0) * p);
+        // the part of the acceptance bound that does not depend on the candidate k
+        const double nm = n - m + 1.0;
+        const double hm = (m + 0.5) * log((m + 1.0) / (r * nm)) + stirling_tail(m) + stirling_tail(n - m);
         while (true) {
             double u, v;
             rng.uniform2(u, v);
@@ -91,10 +94,8 @@ __host__ __device__ inline double binomial_split(double n, double pl, double pr,
             if (us >= 0.07 && v <= vr) break;
             if (k < 0.0 || k > n) continue;
             v = log(v * alpha / (a / (us * us) + b));
-            double nm = n - m + 1.0;
             double nk = n - k + 1.0;
-            double ub = (m + 0.5) * log((m + 1.0) / (r * nm)) + (n + 1.0) * log1p((k - m) / nk) +
-                        (k + 0.5) * log(r * nk / (k + 1.0)) + stirling_tail(m) + stirling_tail(n - m) -
+            double ub = hm + (n + 1.0) * log1p((k - m) / nk) + (k + 0.5) * log(r * nk / (k + 1.0)) -
                         stirling_tail(k) - stirling_tail(n - k);
             if (v <= ub) break;
         }
