@@ -155,10 +155,24 @@ __device__ __forceinline__ void canon_scan(double* x, int L, double* tot, int ti
 
 // N independent categorical draws from the CDF cdf[0..L) with total mass tot (draws >= cdf[L-1] fall in
 // the lumped remainder and are dropped); counts accumulate in cnt_i[0..L).  Sample s uses the Philox
-// stream (vec, stream, s/2), so the counts do not depend on the thread count.
-__device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL, double tot, int* cnt_i, long long N,
-                                              int tid, int T, unsigned long long seed, unsigned long long vec,
-                                              unsigned stream) {
+// stream (vec, stream, s/2), so the counts do not depend on the thread count.  With enough draws to pay
+// for it, a guide table (guide[j] = first bin that can hold a target in bucket j of L equal buckets) turns
+// the log2(L) dependent probes of the bisection into one or two; either way the bin found is the smallest
+// i with target < cdf[i].
+template <bool guided>
+__device__ __forceinline__ void sample_direct_impl(const double* cdf, int L, double tot, int* cnt_i, int* guide,
+                                                   long long N, int tid, int T, unsigned long long seed,
+                                                   unsigned long long vec, unsigned stream) {
+    const double scale = (double)L / tot;
+    if (guided) {
+        for (int i = tid; i < L; i += T) {
+            const double lo = i ? cdf[i - 1] : 0.0, hi = cdf[i];
+            int j0 = (int)ceil(lo * scale), j1 = (i == L - 1) ? L : (int)ceil(hi * scale);
+            j1 = min(j1, L);
+            for (int j = j0; j < j1; ++j) guide[j] = i;
+        }
+        __syncthreads();
+    }
     const long long pairs = (N + 1) >> 1;
     for (long long p = tid; p < pairs; p += T) {
         Philox rng(seed, vec, stream, (unsigned)p);
@@ -169,12 +183,26 @@ __device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL
             if (2 * p + h >= N) break;
             const double target = u[h] * tot;
             if (target >= cdf[L - 1]) continue;
-            int lo = 0;                        // smallest i with target < cdf[i]
-            for (int step = L >> 1; step > 0; step >>= 1)
-                if (cdf[lo + step - 1] <= target) lo += step;
+            int lo;
+            if (guided) {
+                lo = guide[min((int)(target * scale), L - 1)];
+                while (lo > 0 && cdf[lo - 1] > target) --lo;       // (rounding of the bucket edges)
+                while (cdf[lo] <= target) ++lo;
+            } else {
+                lo = 0;                        // smallest i with target < cdf[i]
+                for (int step = L >> 1; step > 0; step >>= 1)
+                    if (cdf[lo + step - 1] <= target) lo += step;
+            }
             atomicAdd(&cnt_i[lo], 1);
         }
     }
+}
+__device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL, double tot, int* cnt_i, int* guide,
+                                              long long N, int tid, int T, unsigned long long seed,
+                                              unsigned long long vec, unsigned stream) {
+    // short vectors: the bisection is 6-8 probes, cheaper than building a table
+    if (L >= 512 && N >= L) sample_direct_impl<true>(cdf, L, tot, cnt_i, guide, N, tid, T, seed, vec, stream);
+    else sample_direct_impl<false>(cdf, L, tot, cnt_i, guide, N, tid, T, seed, vec, stream);
 }
 
 // shared memory of one vector, in doubles: P [L] | A [2L] (sum tree, then counts in place; CDF, int counts
@@ -232,12 +260,13 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
         // The rule depends on (N, L) only.
         const bool direct = N <= 64.0 * (L < 32 ? 32 : (L > 512 ? 512 : L));
         int* cnt_i = reinterpret_cast<int*>(A + L);      // [L] ints = A[L .. L + L/2)
+        int* guide = reinterpret_cast<int*>(A + L + H);  // [L] ints = A[L + L/2 .. 2L), shared with the reduction scratch
         double e;
         if (direct) {
             for (int i = tid; i < L; i += T) { double x = vin(i); A[i] = x * x; cnt_i[i] = 0; }
             __syncthreads();
             canon_scan(A, L, tot, tid, T);                         // stage-1 CDF in A[0..L)
-            sample_direct(A, L, a.logL, A[L - 1], cnt_i, (long long)N, tid, T, a.seed, vec, (unsigned)(2 * at));
+            sample_direct(A, L, a.logL, A[L - 1], cnt_i, guide, (long long)N, tid, T, a.seed, vec, (unsigned)(2 * at));
             __syncthreads();
             const double sminus = canon_sum([&](int i) {
                 double p = sqrt((double)cnt_i[i] / N), x = vin(i);
@@ -249,7 +278,7 @@ __global__ void tomo_fused_kernel(TomoArgs a) {
             for (int i = tid; i < L; i += T) cnt_i[i] = 0;
             __syncthreads();
             canon_scan(A, L, tot, tid, T);                         // stage-2 '+' CDF; the '-' outcomes are one lump
-            sample_direct(A, L, a.logL, A[L - 1] + sminus, cnt_i, (long long)N, tid, T, a.seed, vec,
+            sample_direct(A, L, a.logL, A[L - 1] + sminus, cnt_i, guide, (long long)N, tid, T, a.seed, vec,
                           (unsigned)(2 * at + 1));
             __syncthreads();
         } else {
