@@ -112,6 +112,11 @@ int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, c
                      double delta, unsigned long long seed, unsigned long long offset, int* labels,
                      double* mindist, double* inertia, int* n_fixed, void* ws, size_t ws_bytes, void* stream);
 
+/* Test hook (no reference counterpart): with on != 0 every pair of later mode-2 calls is sampled by the
+ * draw-by-draw replay path of csrc/ipe.cuh (the path taken when the median of the 13 outcomes may lie outside
+ * the enumerated window), so that its law can be tested; results stay exact, only slower.                  */
+int sq_ipe_debug_force_replay(int on);
+
 /* Same E-step as sq_qmeans_assign for callers that cannot give the library a workspace
  * (no counterpart in the reference).  Meant for hosts that are not allowed to allocate on
  * the device: a plugin inside a process whose GPU memory belongs to another framework's

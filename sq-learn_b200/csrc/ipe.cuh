@@ -134,7 +134,8 @@ __device__ __noinline__ double ipe_median_replay(double M, double x, int T, uint
 // |x|^2 + |c|^2 - 2 ipe(x, c) for the pair held by each lane.  All 32 lanes of the warp must call
 // it together; lanes without a pair pass valid = false.  eps is ipe's epsilon (delta / 2).
 __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, double cn, double eps, bool valid,
-                                                 uint64_t seed, uint64_t rowkey, uint32_t col) {
+                                                 uint64_t seed, uint64_t rowkey, uint32_t col,
+                                                 bool force_replay = false) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const double PI = 3.14159265358979323846;
@@ -276,7 +277,7 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
 
     // ---- the (7 - b)-th smallest of the n = 13 - T window draws ----
     const int k = 7 - b, n = IPE_Q - T;
-    if (status == FAST && (mixed || k < 1 || k > n)) status = REPLAY;
+    if (status == FAST && (mixed || k < 1 || k > n || force_replay)) status = REPLAY;
     {
         const bool fast = (status == FAST);
         const int kk = fast ? k : 1, nmk = fast ? n - k : 0;

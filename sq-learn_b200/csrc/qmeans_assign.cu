@@ -52,6 +52,7 @@ struct AssignArgs {
     int* flag_rows;        // [n]   their indices
     double* ipe_scratch;   // [grid][BM*BN] MODE_IPE: each CTA's tile of dot products, then of estimates
     size_t ipe_scratch_bytes;   // (host) capacity of ipe_scratch: bounds the grid
+    int ipe_force_replay;       // test hook: every pair takes the draw-by-draw replay path of ipe.cuh
     double* store;         // [n, k] MODE_STORE: x_i.c_j - cnorm[j]
     unsigned long long* colkey;  // [k] MODE_COLABS: max over rows of (bits(|y|) with the sign of y in bit 0)
     long long n;
@@ -332,7 +333,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     const double xn = xn_s[row];
                     const double v = ipe_estimate_warp(dot, xn, ok ? cn_s[n0 + cl] : 0.0, 0.5 * a.delta, ok,
                                                        a.seed, a.offset + (unsigned long long)(r0 + row),
-                                                       (unsigned)(n0 + cl));
+                                                       (unsigned)(n0 + cl), a.ipe_force_replay != 0);
                     if (ok) sc[row * BN + cl] = v - xn;
                     row = row2; cl = cl2; ok = ok2; dot = dot2;
                 }
@@ -721,6 +722,7 @@ static size_t assign_smem_bytes() {
 
 // optional timing of the main kernel alone (bench.py's roofline leg): events are
 // recorded on the launching stream around the kernel when profiling is on
+static int g_ipe_force_replay = 0;
 static bool g_prof_on = false;
 static cudaEvent_t g_prof_ev[2] = {nullptr, nullptr};
 static double g_prof_ms = 0.0;
@@ -876,6 +878,7 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     a.store = nullptr; a.colkey = nullptr;
     a.ipe_scratch = (double*)((char*)ws + need);            // whatever lies behind the fixed part
     a.ipe_scratch_bytes = ws_bytes - need;
+    a.ipe_force_replay = g_ipe_force_replay;
     int bn = 0;
     if (mode == MODE_WINDOW && k > 256) {
         // the window needs the row minimum over all k before candidates can be drawn
@@ -899,6 +902,11 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     rc = sq_sum_f64(a.mindist, n, inertia, w.partial, SUM_BLOCKS * sizeof(double), stream);
     if (rc) return rc;
     if (n_fixed) SQ_CUDA(cudaMemcpyAsync(n_fixed, w.flag_count, sizeof(int), cudaMemcpyDeviceToDevice, stream));
+    return SQ_OK;
+}
+
+extern "C" int sq_ipe_debug_force_replay(int on) {
+    g_ipe_force_replay = on ? 1 : 0;
     return SQ_OK;
 }
 

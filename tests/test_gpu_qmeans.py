@@ -292,15 +292,23 @@ IPE_REGIMES = [
 ]
 
 
+@pytest.mark.parametrize("replay", [0, 1])
 @pytest.mark.parametrize("case", range(len(IPE_REGIMES)))
-def test_ipe_distance_law_regimes(cuda, case):
+def test_ipe_distance_law_regimes(cuda, case, replay):
     """k = 1, n identical rows: the reported distance is one IPE estimate per row; its law must be the exact
-    median-of-13 law of the reference's amplitude-estimation pmf in every regime of the grid"""
+    median-of-13 law of the reference's amplitude-estimation pmf in every regime of the grid.  replay = 1 sends
+    every pair through the draw-by-draw path that normally serves only the rare pairs whose median may leave the
+    enumerated window."""
     import gpu_util as G
+    from sqlearn import _cabi
     xv, cv, delta = IPE_REGIMES[case]
     x, c = np.array(xv), np.array(cv)
     n = 30000
-    _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), c[None], mode=2, delta=delta, seed=21 + case)
+    _cabi.lib.sq_ipe_debug_force_replay(replay)
+    try:
+        _, mind, _, _ = G.assign(np.repeat(x[None], n, axis=0), c[None], mode=2, delta=delta, seed=21 + case + 100 * replay)
+    finally:
+        _cabi.lib.sq_ipe_debug_force_replay(0)
     support, pmf = _ipe_distance_pmf(x, c, delta / 2)
     idx = np.array([np.argmin(np.abs(support - v)) for v in mind])
     assert np.allclose(support[idx], mind, rtol=1e-9, atol=1e-9)

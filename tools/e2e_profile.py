@@ -6,7 +6,8 @@ from sqlearn.cluster import qMeans_
 from sqlearn.cluster import _dmeans as D
 from sqlearn.QuantumUtility import Utility as Q
 dev = torch.device("cuda", 0)
-X = bench.make_shard(10_000_000, 0, 1, dev)
+ROWS = int(sys.argv[1]) if len(sys.argv) > 1 else 10_000_000
+X = bench.make_shard(ROWS, 0, 1, dev)
 Xh = torch.empty(X.shape, dtype=torch.float64, pin_memory=True); Xh.copy_(X)
 init = X[:256].cpu().numpy(); del X
 torch.cuda.synchronize()
