@@ -322,3 +322,20 @@ def test_ipe_distance_law_regimes(cuda, case, replay):
     else:
         assert o[~keep].sum() == 0
         assert stats.chisquare(o[keep], e[keep] * o[keep].sum() / e[keep].sum()).pvalue > P_MIN
+
+
+@pytest.mark.parametrize("n,d,k", [(1000, 33, 300), (777, 128, 256), (100, 7, 10), (5000, 64, 600), (64, 16, 1)])
+def test_ipe_mode_tends_to_exact_labels_for_small_delta(cuda, n, d, k):
+    """every tile shape, several centroid tiles (k > 256), odd d (no TMA): with delta -> 0 the estimates converge to
+    the true distances, so on separated blobs the labels are the exact ones and the reported distances are close"""
+    import gpu_util as G
+    rs = np.random.RandomState(n + k)
+    cen = rs.randn(k, d) * 6
+    lab = rs.randint(0, k, n)
+    X = cen[lab] + 0.3 * rs.randn(n, d)
+    le, me, _, _ = G.assign(X, cen, mode=0, delta=0.0, seed=1)
+    li, mi, _, _ = G.assign(X, cen, mode=2, delta=1e-3, seed=2)
+    assert np.array_equal(le, lab)
+    assert np.array_equal(li, le)
+    S = (X * X).sum(axis=1) + (cen[lab] ** 2).sum(axis=1)
+    assert np.all(np.abs(mi - me) <= 0.01 * S + 1e-9)
