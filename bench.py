@@ -345,6 +345,10 @@ def extra_measurements(eng, centers, D, Q, _cabi, torch):
         out["estep_%s_ms" % name] = _timed(
             torch, lambda: D._labels_inertia(eng, centers, delta=delta, pool=None, true_distance_estimate=tde),
             2 if name == "ipe" else 3)
+    # IPE mode samples, for every (row, centroid) pair, the median of 13 amplitude-estimation outcomes
+    pairs = float(eng.n) * float(eng.k)
+    out["ipe_pairs_per_s"] = pairs / (out["estep_ipe_ms"] * 1e-3)
+    out["ipe_reference_draws_per_s"] = 13.0 * pairs / (out["estep_ipe_ms"] * 1e-3)
     D._labels_inertia(eng, centers, delta=0.0, pool=None, true_distance_estimate=True)
     out["mstep_accumulate_ms"] = _timed(torch, eng.accumulate, 3)
     c2 = torch.empty_like(centers)
