@@ -107,6 +107,8 @@ int sq_tomography_batched_spec(const double* V, long long B, int d, double delta
  * xnorm[n] = ||x_i||^2 (sq_row_sqnorms).  Outputs: labels[n] int32,
  * mindist[n] (may be NULL), inertia[1] = sum_i min_j D_ij, n_fixed[1] (may be
  * NULL) = rows re-evaluated with the reference's exact arithmetic.          */
+/* workspace_bytes = the fixed part + 40 MiB for the ipe tiles (64 KB per resident CTA); sq_qmeans_assign accepts
+ * less in modes 0 and 1 (fixed part only) and runs mode 2 on a smaller grid when fewer tiles fit. */
 size_t sq_qmeans_assign_workspace_bytes(long long n, int d, int k);
 int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, const double* C, int k, int mode,
                      double delta, unsigned long long seed, unsigned long long offset, int* labels,
@@ -129,7 +131,10 @@ int sq_ipe_debug_force_replay(int on);
  * stream capture.  All calls share the one array and it keeps the previous call's contents:
  * two calls whose kernels can run at the same time on one GPU (different streams, no
  * dependency) race on it; serialise them.  Inputs, outputs and results are those of
- * sq_qmeans_assign.                                                                      */
+ * sq_qmeans_assign.  In mode 2 every resident CTA parks a tile of dot products (<= 64 KB) in
+ * the scratch, so what the fixed part leaves of the 2 MiB bounds the grid (about ten CTAs at
+ * the largest n): same results, a fraction of the speed - give sq_qmeans_assign a workspace
+ * if you can.                                                                              */
 int sq_qmeans_assign_noalloc(const double* X, const double* xnorm, long long n, int d, const double* C, int k,
                              int mode, double delta, unsigned long long seed, unsigned long long offset, int* labels,
                              double* mindist, double* inertia, int* n_fixed, void* stream);

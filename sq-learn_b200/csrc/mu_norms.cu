@@ -30,10 +30,12 @@ struct MuArgs {
     int row_blocks;
 };
 
-__device__ __forceinline__ double powabs(double l2, bool nz, double e) {
+__device__ __forceinline__ double powabs(double av, double l2, bool nz, double e) {
     // |a|^e with the reference's conventions: exponent 0 counts non-zeros
     if (!nz) return 0.0;
     if (e == 0.0) return 1.0;
+    if (e == 2.0) return av * av;      // (every grid has 2p = 2 or 2(1-p) = 2 at its ends, and the extra Frobenius row)
+    if (e == 1.0) return av;
     return exp2(e * l2);
 }
 
@@ -59,7 +61,7 @@ __global__ void mu_row_kernel(MuArgs a) {
             frob = fma(v, v, frob);
 #pragma unroll
             for (int g = 0; g < MU_MAXP; ++g)
-                if (g < a.np) rs[g] += powabs(l2, nz, a.er[g]);
+                if (g < a.np) rs[g] += powabs(av, l2, nz, a.er[g]);
         }
 #pragma unroll
         for (int g = 0; g < MU_MAXP; ++g)
@@ -90,7 +92,7 @@ __global__ void __launch_bounds__(256) mu_col_kernel(MuArgs a) {
             double l2 = nz ? log2(av) : 0.0;
 #pragma unroll
             for (int g = 0; g < MU_MAXP; ++g)
-                if (g < a.np) cs[g] += powabs(l2, nz, a.ec[g]);
+                if (g < a.np) cs[g] += powabs(av, l2, nz, a.ec[g]);
         }
 #pragma unroll
         for (int g = 0; g < MU_MAXP; ++g)
