@@ -153,6 +153,25 @@ def test_dims_and_sharding_invariance(cuda, d):
         assert not np.array_equal(other[0], est)
 
 
+@pytest.mark.parametrize("d,delta,stop", [(128, 0.25, 1), (1000, 0.3, 1), (1000, 0.05, 0), (61, 0.1, 1), (2000, 0.2, 0)])
+def test_result_does_not_depend_on_threads_per_vector(cuda, d, delta, stop):
+    """the host gives a vector L threads in a small batch and L/8 in a large one; estimates, attempt counts
+    and errors must agree bit for bit (every reduction is ordered by L alone, draws are keyed by node / sample)"""
+    import gpu_util as G
+    from oracle import quantum_utility as qu
+    rs = np.random.RandomState(d + stop)
+    B = 4200                                     # >= 4096 vectors: the many-vector geometry
+    base = rs.uniform(-1, 1, (7, d))
+    V = base[rs.randint(0, 7, B)] * rs.uniform(0.5, 2.0, (B, 1))
+    N = qu.tomography_N(d, delta)
+    sched = qu.schedule(N).astype(float) if stop else np.array([float(N)])
+    big = G.tomography(V, delta, sched, stop=stop, seed=33, vec_offset=1000)
+    for i in (0, 17, 4199):
+        one = G.tomography(V[i:i + 1], delta, sched, stop=stop, seed=33, vec_offset=1000 + i)
+        assert np.array_equal(one[0][0], big[0][i])
+        assert one[1][0] == big[1][i] and one[2][0] == big[2][i]
+
+
 def test_trace_and_public_api(cuda, golden_stoch):
     import gpu_util as G
     from oracle import quantum_utility as qu
