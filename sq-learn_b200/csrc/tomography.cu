@@ -116,9 +116,17 @@ template <class F>
 __device__ __forceinline__ double canon_sum(F f, double* scratch, int L, int tid, int T) {
     const int h = L >> 1;
     for (int i = tid; i < h; i += T) { double lo = f(i), hi = f(i + h); scratch[i] = lo + hi; }
-    for (int s = h >> 1; s >= 1; s >>= 1) {
+    int s = h >> 1;
+    for (; s >= 32; s >>= 1) {
         __syncthreads();
         for (int i = tid; i < s; i += T) scratch[i] += scratch[i + s];
+    }
+    __syncthreads();
+    // the last 2s <= 32 partials: the same pairs (i, i + s), added through shuffles by warp 0
+    if (tid < 32) {
+        double v = (tid < 2 * s || (s == 0 && tid == 0)) ? scratch[tid] : 0.0;
+        for (; s >= 1; s >>= 1) v += __shfl_down_sync(0xffffffffu, v, s);
+        if (tid == 0) scratch[0] = v;
     }
     __syncthreads();
     const double r = scratch[0];
