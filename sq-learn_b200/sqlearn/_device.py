@@ -36,6 +36,47 @@ def to_device(a, dtype=torch.float64, pin=False):
     return t.to(dev, non_blocking=pin)
 
 
+def stream_to_device(a, on_chunk=None, chunk_bytes=256 << 20):
+    """Host matrix [n, d] (float64) -> device tensor, copied in row chunks on a side stream; ``on_chunk(out, r0,
+    r1)`` is called once per chunk with the current stream already waiting for that chunk, so the caller's
+    kernels on rows [r0, r1) overlap the copy of the next chunk.  Pageable input is staged through two pinned
+    chunk buffers instead of pinning (and copying) the whole array."""
+    dev = require_cuda()
+    t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64))
+    n, d = t.shape
+    out = torch.empty((n, d), dtype=torch.float64, device=dev)
+    if n == 0:
+        return out
+    rows = max(1, int(chunk_bytes) // (8 * d))
+    main = torch.cuda.current_stream()
+    copy = torch.cuda.Stream(device=dev)
+    copy.wait_stream(main)                      # the allocation above belongs to the current stream
+    out.record_stream(copy)
+    pinned = t.is_pinned()
+    ring, ring_ev = [], [None, None]
+    if not pinned:
+        ring = [torch.empty((min(rows, n), d), dtype=torch.float64).pin_memory() for _ in range(2 if n > rows else 1)]
+    for c, r0 in enumerate(range(0, n, rows)):
+        r1 = min(n, r0 + rows)
+        with torch.cuda.stream(copy):
+            if pinned:
+                out[r0:r1].copy_(t[r0:r1], non_blocking=True)
+            else:
+                slot = c % len(ring)
+                if ring_ev[slot] is not None:
+                    ring_ev[slot].synchronize()       # the buffer's previous upload has left the host
+                ring[slot][:r1 - r0].copy_(t[r0:r1])
+                out[r0:r1].copy_(ring[slot][:r1 - r0], non_blocking=True)
+                ring_ev[slot] = torch.cuda.Event()
+                ring_ev[slot].record(copy)
+            ev = torch.cuda.Event()
+            ev.record(copy)
+        main.wait_event(ev)
+        if on_chunk is not None:
+            on_chunk(out, r0, r1)
+    return out
+
+
 def empty(shape, dtype=torch.float64):
     return torch.empty(shape, dtype=dtype, device=require_cuda())
 

@@ -413,27 +413,53 @@ class qMeans_(BaseEstimator):
         return np.ascontiguousarray(centers, dtype=np.float64)
 
     # ---- fit (reference: _dmeans.py:1211-1325) --------------------------------
-    def _preamble(self, engine):
-        """eta, muA and condition_number of the uncentred data (:1242-1245).  The
-        reference takes a full LAPACK SVD for min(S); here min(S) = sqrt(lambda_min(X^T X))
-        from the tensor-core Gram kernel and a d x d cuSOLVER eigensolve."""
+    # best_mu(X, 0, 0.1): p = 0, 0.05, 0.1 (Utility.py:196-231), plus one row of exponents 2 for eta / Frobenius
+    _MU_GRID = [i for i in np.arange(0, 0.1, 0.05)] + [0.1]
+
+    def _preamble_chunk(self, engine, acc, r0, r1):
+        """The part of the preamble (:1242-1245, :1262-1266) that is a sum or a maximum over rows, for rows
+        [r0, r1) of the uncentred data: row norms, mu-norm partials, Gram partial, column sums."""
         from .. import _cabi
-        n, d = engine.n, engine.d
-        grid = [i for i in np.arange(0, 0.1, 0.05)] + [0.1]            # best_mu(X, 0, 0.1)
-        er = np.asarray([2 * p for p in grid] + [2.0])
-        ec = np.asarray([2 * (1 - p) for p in grid] + [2.0])
+        d = engine.d
+        n = r1 - r0
+        Xc = engine.X[r0:r1]
+        er = np.asarray([2 * p for p in self._MU_GRID] + [2.0])
+        ec = np.asarray([2 * (1 - p) for p in self._MU_GRID] + [2.0])
         npk = len(er)
+        _cabi.check(_cabi.lib.sq_row_sqnorms(dv.ptr(Xc), n, d, dv.ptr(engine.xnorm[r0:r1]), dv.stream_ptr()),
+                    "sq_row_sqnorms")
         rowmax, colsum, fr = dv.empty((npk,)), dv.empty((npk, d)), dv.empty((1,))
         nb = _cabi.lib.sq_mu_norms_workspace_bytes(n, d, npk)
         ws = dv.workspace(nb)
-        _cabi.check(_cabi.lib.sq_mu_norms(dv.ptr(engine.X), n, d, er.ctypes.data, ec.ctypes.data, npk,
+        _cabi.check(_cabi.lib.sq_mu_norms(dv.ptr(Xc), n, d, er.ctypes.data, ec.ctypes.data, npk,
                                           dv.ptr(rowmax), dv.ptr(colsum), dv.ptr(fr), dv.ptr(ws), nb,
                                           dv.stream_ptr()), "sq_mu_norms")
         G = dv.empty((d, d))
         nb = _cabi.lib.sq_gram_workspace_bytes(n, d)
         ws = dv.workspace(nb)
-        _cabi.check(_cabi.lib.sq_gram_centered(dv.ptr(engine.X), n, d, None, dv.ptr(G), dv.ptr(ws), nb,
+        _cabi.check(_cabi.lib.sq_gram_centered(dv.ptr(Xc), n, d, None, dv.ptr(G), dv.ptr(ws), nb,
                                                dv.stream_ptr()), "sq_gram_centered")
+        csum = dv.empty((d,))
+        nb = _cabi.lib.sq_col_sums_workspace_bytes(n, d)
+        ws = dv.workspace(nb)
+        _cabi.check(_cabi.lib.sq_col_sums(dv.ptr(Xc), n, d, dv.ptr(csum), dv.ptr(ws), nb, dv.stream_ptr()),
+                    "sq_col_sums")
+        engine.launches += 9
+        if not acc:
+            acc.update(rowmax=rowmax, colsum=colsum, fr=fr, G=G, csum=csum)
+        else:                                   # chunks are combined in row order: deterministic
+            acc["rowmax"] = torch.maximum(acc["rowmax"], rowmax)
+            acc["colsum"] += colsum
+            acc["fr"] += fr
+            acc["G"] += G
+            acc["csum"] += csum
+
+    def _preamble_finish(self, engine, acc):
+        """eta, muA and condition_number of the uncentred data (:1242-1245).  The reference takes a full LAPACK
+        SVD for min(S); here min(S) = sqrt(lambda_min(X^T X)) from the tensor-core Gram kernel and a d x d
+        cuSOLVER eigensolve.  Returns the column sums of this rank's rows (for the mean, :1264)."""
+        d = engine.d
+        rowmax, colsum, fr, G = acc["rowmax"], acc["colsum"], acc["fr"], acc["G"]
         if engine.world > 1:
             import torch.distributed as dist
             dist.all_reduce(rowmax, op=dist.ReduceOp.MAX)
@@ -449,6 +475,7 @@ class qMeans_(BaseEstimator):
         r = min(engine.n_total, d)
         smin = float(torch.sqrt(torch.clamp(lam[d - r], min=0.0)).item())
         self.condition_number = 1 / smin if smin > 0 else float('inf')
+        return acc["csum"]
 
     def fit(self, X, y=None, sample_weight=None):
         """Compute q-means clustering (reference: _dmeans.py:1211-1325)."""
@@ -457,15 +484,24 @@ class qMeans_(BaseEstimator):
         rank, world = dv.dist_info()
         if world > 1:
             qu._sync_state()
-        Xd = dv.to_device(X, pin=True)
-        if Xd.data_ptr() == 0 or X.shape[0] == 0:
+        if X.shape[0] == 0:
             raise ValueError("Found array with 0 sample(s)")
-        engine = QMeansEngine(Xd, self.n_clusters)
+        # The rows go up in chunks on a copy stream; everything the preamble needs from the uncentred data is a
+        # sum or a maximum over rows, so it is computed chunk by chunk underneath the upload.
+        state = {}
+
+        def on_chunk(out, r0, r1):
+            if "engine" not in state:
+                state["engine"] = QMeansEngine(out, self.n_clusters, norms=False)
+                state["acc"] = {}
+            self._preamble_chunk(state["engine"], state["acc"], r0, r1)
+        dv.stream_to_device(X, on_chunk)
+        engine = state["engine"]
         self._engine_launches = 0
         # _assert_all_finite of the reference's check_array, evaluated on the device: ||X||_F^2 is finite
         if not bool(torch.isfinite(engine.xnorm.sum()).item()):
             raise ValueError("Input contains NaN, infinity or a value too large for dtype('float64').")
-        self._preamble(engine)
+        csum = self._preamble_finish(engine, state["acc"])
 
         if self.delta == 0:
             warnings.warn("Attention! You are running classic version of kmeans!")
@@ -480,7 +516,6 @@ class qMeans_(BaseEstimator):
             self._validate_center_shape(X, init)
 
         # subtract the mean of X for more accurate distance computations (:1262-1269)
-        csum = engine.col_sums()
         dv.all_reduce_sum(csum)
         X_mean_dev = csum / float(engine.n_total)
         engine.subtract_rowvec(X_mean_dev)

@@ -18,7 +18,7 @@ MODE_EXACT, MODE_WINDOW, MODE_IPE = 0, 1, 2
 
 
 class QMeansEngine:
-    def __init__(self, X_dev, n_clusters):
+    def __init__(self, X_dev, n_clusters, norms=True):
         assert X_dev.is_cuda and X_dev.dtype == torch.float64 and X_dev.is_contiguous()
         self.X = X_dev
         self.n, self.d = X_dev.shape
@@ -50,7 +50,8 @@ class QMeansEngine:
             sizes = [int(s.item()) for s in sizes]
             self.row0, self.n_total = sum(sizes[:self.rank]), sum(sizes)
         self.launches = 0
-        self.refresh_norms()
+        if norms:                   # (fit fills xnorm chunk by chunk while the rows are still arriving)
+            self.refresh_norms()
 
     # ---- helpers ---------------------------------------------------------
     def refresh_norms(self):

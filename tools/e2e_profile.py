@@ -18,7 +18,7 @@ def wrap(obj, name):
         torch.cuda.synchronize(); t = time.perf_counter(); r = f(*a, **k); torch.cuda.synchronize()
         print(f"  {name}: {(time.perf_counter()-t)*1e3:.1f} ms"); return r
     setattr(obj, name, g)
-wrap(D.dv, "to_device"); wrap(qMeans_, "_preamble"); wrap(D, "_kmeans_single_lloyd"); wrap(D, "_tolerance"); wrap(D, "_validate_X")
+wrap(D.dv, "stream_to_device"); wrap(qMeans_, "_preamble_finish"); wrap(D, "_kmeans_single_lloyd"); wrap(D, "_tolerance"); wrap(D, "_validate_X")
 with warnings.catch_warnings():
     warnings.simplefilter("ignore")
     for rep in range(2):
