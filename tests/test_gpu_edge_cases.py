@@ -119,3 +119,24 @@ def test_workspace_too_small_is_reported(cuda, lib):
     rc = lib.lib.sq_qmeans_assign(X.data_ptr(), xn.data_ptr(), 100, 4, C.data_ptr(), 3, 1, 0.0, 0, 0, lab.data_ptr(),
                                   None, inertia.data_ptr(), None, ws.data_ptr(), 64, dv.stream_ptr())
     assert rc == 1 and b"delta > 0" in lib.lib.sq_last_error()
+
+
+def test_chunked_upload_pageable_and_pinned(cuda):
+    """stream_to_device: many chunks, both staging buffers reused, callbacks cover every row once and see the
+    chunk's data; pinned input takes the direct path"""
+    import torch
+    from sqlearn import _device as dv
+    rs = np.random.RandomState(0)
+    X = rs.randn(1003, 17)
+    for src in (X, torch.from_numpy(X.copy()).pin_memory().numpy()):
+        seen, sums = [], []
+
+        def on_chunk(out, r0, r1):
+            seen.append((r0, r1))
+            sums.append(out[r0:r1].sum())          # stream-ordered after the chunk's copy
+        out = dv.stream_to_device(src, on_chunk, chunk_bytes=17 * 8 * 100)
+        torch.cuda.synchronize()
+        assert np.array_equal(out.cpu().numpy(), X)
+        assert seen == [(r, min(r + 100, 1003)) for r in range(0, 1003, 100)]
+        np.testing.assert_allclose([float(v) for v in sums], [X[a:b].sum() for a, b in seen], rtol=1e-12, atol=1e-12)
+    assert dv.stream_to_device(np.zeros((0, 5))).shape == (0, 5)
