@@ -133,9 +133,13 @@ __device__ __noinline__ double ipe_median_replay(double M, double x, int T, uint
 
 // |x|^2 + |c|^2 - 2 ipe(x, c) for the pair held by each lane.  All 32 lanes of the warp must call
 // it together; lanes without a pair pass valid = false.  eps is ipe's epsilon (delta / 2).
+// LEAN = true keeps only the common case in the instruction stream (grid of >= 32 points, window away from
+// 0 and M/2, no tail draw inside the window's range): any other pair sets defer and is to be given to the
+// LEAN = false version later, which handles everything and regenerates the same keyed draws.
+template <bool LEAN>
 __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, double cn, double eps, bool valid,
-                                                 uint64_t seed, uint64_t rowkey, uint32_t col,
-                                                 bool force_replay = false) {
+                                                    uint64_t seed, uint64_t rowkey, uint32_t col, bool force_replay,
+                                                    bool& defer) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const double PI = 3.14159265358979323846;
@@ -148,6 +152,7 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
     for (int i = 0; i < 8; ++i) w[i] = 0.0;
     int T = 0;
     bool sorted = true;
+    defer = false;
     if (valid && S > 0.0) {
         double a = (S - 2.0 * dot) / (2.0 * S);
         if (a < 1e-15) a = 0.0;  // math.isclose(a, 0, abs_tol=1e-15) (Utility.py:487); negatives are rounding noise
@@ -159,14 +164,14 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
         t = x - j0;
         if (t == 0.0) {
             med = fmin(j0, M - j0);  // weight 1 at distance 0 (Utility.py:500-501)
-        } else if (M <= 9.0) {
+        } else if (M <= 9.0 || (LEAN && M < 32.0)) {
             status = REPLAY;
         } else {
             status = FAST;
             const double st = sinpi(t), s2 = st * st, invM = 1.0 / M;
             // p_i = (M sin(pi z_i / M))^2 at the offsets z_i = i - 3 - t
             double pw[8];
-            if (M >= 32.0) {
+            if (LEAN || M >= 32.0) {
                 // |pi z / M| < pi/8: M sin(pi z/M) = pi z P(u), u = (pi z/M)^2, Taylor to u^7 (next term < 2e-18)
                 const double piM = PI * invM;
 #pragma unroll
@@ -205,6 +210,7 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
             // r-order of the window: increasing with the offset unless it straddles 0 or M/2
             sorted = (j0 >= 3.0) && (2.0 * (j0 + 4.0) <= M);
             if (sorted) { rlo = j0 - 3.0; rhi = j0 + 4.0; }
+            else if (LEAN) { status = REPLAY; }
             else {
                 rlo = M; rhi = 0.0;
 #pragma unroll
@@ -282,7 +288,7 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
         const bool fast = (status == FAST);
         const int kk = fast ? k : 1, nmk = fast ? n - k : 0;
         const double iW = 1.0 / W;
-        const bool srt = __all_sync(FULL, sorted || !fast);
+        const bool srt = LEAN || __all_sync(FULL, sorted || !fast);
         if (srt) {
             // cumulative window CDF in offset order; smallest i with V <= G(F_i), by bisection (F_7 = 1)
             const double F0 = w[0] * iW, F1 = F0 + w[1] * iW, F2 = F1 + w[2] * iW, F3 = F2 + w[3] * iW,
@@ -293,7 +299,7 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
             const bool h3 = V <= ipe_order_cdf(Fq, kk, nmk);
             const int i = (h1 ? 0 : 4) + (h2 ? 0 : 2) + (h3 ? 0 : 1);
             if (fast) med = rlo + (double)i;
-        } else {
+        } else if (!LEAN) {
             double best = INFINITY;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -310,7 +316,10 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
             if (fast) med = (best <= rhi) ? best : rhi;   // rounding in F_i at the last point
         }
     }
-    if (status == REPLAY) med = ipe_median_replay(M, x, T, seed, rowkey, col);
+    if (status == REPLAY) {
+        if (LEAN) { defer = true; return 0.0; }
+        med = ipe_median_replay(M, x, T, seed, rowkey, col);
+    }
     if (!(valid && S > 0.0)) return 0.0;
     const double sn = sinpi(med / M);
     return 2.0 * S * sn * sn;

@@ -102,6 +102,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     int* run_cnt = run_a1 + BM;                              // [BM]
     double* cn_s = (double*)(run_cnt + BM);                  // [NT*BN] centroid norms (+inf past k)
     unsigned long long* full_bar = (unsigned long long*)(cn_s + a.NT * BN);  // [STAGES] TMA completion barriers
+    int* ipe_cnt = (int*)(full_bar + STAGES);                // [1] MODE_IPE: pairs left to the general pass
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp / WN_CNT, wn = warp % WN_CNT;
@@ -306,7 +307,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 // dot products is parked in this CTA's slice of the workspace (L2-resident), so that the
                 // sampler runs with the whole register file instead of beside 2*MI*NI live accumulators, and
                 // the pairs are dealt to the lanes as a flat list (no idle lanes for k < BN).
-                double* sc = a.ipe_scratch + (size_t)blockIdx.x * (BM * BN);
+                double* sc = a.ipe_scratch + (size_t)blockIdx.x * (BM * BN + BM * BN / 2);   // dots, then the pass-2 list
                 const int cl0 = wn * Cfg::WN + lr4 * 2;
 #pragma unroll
                 for (int i = 0; i < MI; ++i)
@@ -320,6 +321,12 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 const int pairs = rows * kk;
                 const int rounds = (pairs + Cfg::THREADS - 1) / Cfg::THREADS;
                 // (the dot product of the next round is fetched while this round's estimate is computed)
+                // Pass 1 runs the lean estimator; the few pairs it cannot take (tiny grid, window wrapping around
+                // 0 or M/2, a tail draw inside the window's range) are listed and done by the general one in
+                // pass 2, all together: the common path stays small and uniform.
+                int* list = reinterpret_cast<int*>(sc + BM * BN);
+                if (tid == 0) *ipe_cnt = 0;
+                __syncthreads();
                 int row = 0, cl = 0;
                 bool ok = tid < pairs;
                 if (ok) { row = tid / kk; cl = tid - row * kk; }
@@ -331,11 +338,30 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     const int row2 = ok2 ? idx2 / kk : 0, cl2 = ok2 ? idx2 - row2 * kk : 0;
                     const double dot2 = sc[row2 * BN + cl2];
                     const double xn = xn_s[row];
-                    const double v = ipe_estimate_warp(dot, xn, ok ? cn_s[n0 + cl] : 0.0, 0.5 * a.delta, ok,
-                                                       a.seed, a.offset + (unsigned long long)(r0 + row),
-                                                       (unsigned)(n0 + cl), a.ipe_force_replay != 0);
-                    if (ok) sc[row * BN + cl] = v - xn;
+                    bool defer;
+                    const double v = ipe_estimate_warp<true>(dot, xn, ok ? cn_s[n0 + cl] : 0.0, 0.5 * a.delta, ok,
+                                                             a.seed, a.offset + (unsigned long long)(r0 + row),
+                                                             (unsigned)(n0 + cl), a.ipe_force_replay != 0, defer);
+                    if (ok) {
+                        if (defer) list[atomicAdd(ipe_cnt, 1)] = row * BN + cl;
+                        else sc[row * BN + cl] = v - xn;
+                    }
                     row = row2; cl = cl2; ok = ok2; dot = dot2;
+                }
+                __syncthreads();
+                const int ndef = *ipe_cnt;
+#pragma unroll 1
+                for (int it = 0; it * Cfg::THREADS < ndef; ++it) {
+                    const int li = it * Cfg::THREADS + tid;
+                    const bool okd = li < ndef;
+                    const int pos = okd ? list[li] : 0;
+                    const int rowd = pos / BN, cld = pos - rowd * BN;
+                    const double xn = xn_s[rowd];
+                    bool defer;
+                    const double v = ipe_estimate_warp<false>(sc[pos], xn, okd ? cn_s[n0 + cld] : 0.0, 0.5 * a.delta, okd,
+                                                              a.seed, a.offset + (unsigned long long)(r0 + rowd),
+                                                              (unsigned)(n0 + cld), a.ipe_force_replay != 0, defer);
+                    if (okd) sc[pos] = v - xn;
                 }
                 __syncthreads();
 #pragma unroll
@@ -697,9 +723,9 @@ struct AssignWs {
     double* mindist;
 };
 static const int SUM_BLOCKS = 1024;
-// ipe mode parks one tile of dot products (<= 64 KB) per resident CTA behind the fixed part of the workspace;
+// ipe mode parks one tile of dot products and a list of as many ints (<= 96 KB) per resident CTA behind the fixed part;
 // sq_qmeans_assign_workspace_bytes asks for enough for 4 CTAs on each of 160 SMs, less still works (smaller grid)
-static const size_t IPE_SCRATCH_BYTES = (size_t)640 * 65536;
+static const size_t IPE_SCRATCH_BYTES = (size_t)640 * 98304;
 
 static size_t assign_ws_layout(long long n, int k, AssignWs* w, char* base) {
     size_t off = 0;
@@ -750,7 +776,7 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
         int r2 = make_tensor_map_2d(&tmB, a.C, (unsigned long long)a.d, (unsigned long long)a.k, 4, Cfg::BN);
         if (r1 || r2) use_tma = false;  // driver without the encoder: 8-byte cp.async path
     }
-    smem += Cfg::STAGES * sizeof(unsigned long long);
+    smem += Cfg::STAGES * sizeof(unsigned long long) + 8;
     // persistent grid: one CTA per resident slot, tiles handed out by static striding
 #define SQ_LAUNCH_ASSIGN(V, M, T)                                                                                     \
     do {                                                                                                            \
@@ -763,10 +789,10 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
         int grid = device_sm_count() * per_sm;                                                                      \
         if (grid > a.num_tiles) grid = a.num_tiles;                                                                 \
         if (M == MODE_IPE) {                                                                                        \
-            size_t fit = a.ipe_scratch_bytes / ((size_t)Cfg::BM * Cfg::BN * sizeof(double));                        \
+            size_t fit = a.ipe_scratch_bytes / ((size_t)Cfg::BM * Cfg::BN * 12);                                    \
             if (fit < 1 || !a.ipe_scratch) {                                                                        \
                 set_error("sq_qmeans_assign: ipe mode needs %zu more workspace bytes per resident CTA",             \
-                          (size_t)Cfg::BM * Cfg::BN * sizeof(double));                                              \
+                          (size_t)Cfg::BM * Cfg::BN * 12);                                                          \
                 return SQ_ERR_WORKSPACE;                                                                            \
             }                                                                                                       \
             if ((size_t)grid > fit) grid = (int)fit;                                                                \
