@@ -26,7 +26,7 @@ class _BasePCA(BaseEstimator):
         """(X - mean_) @ comp.T on the device (reference: _base.py:117-128), as X comp^T - mean.comp^T on the
         fp64 tensor cores (``sq_project``)."""
         from .. import _cabi
-        Xd = dv.to_device(np.asarray(X, dtype=np.float64))
+        Xd = dv.stream_to_device(np.asarray(X, dtype=np.float64))
         Vt = dv.to_device(np.ascontiguousarray(comp, dtype=np.float64))
         n, d = Xd.shape
         r = Vt.shape[0]

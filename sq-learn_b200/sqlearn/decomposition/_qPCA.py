@@ -121,8 +121,9 @@ class qPCA(_BasePCA):
         self.condition_number_est = condition_number_est
         if hasattr(X, "toarray") and not isinstance(X, np.ndarray):
             raise TypeError('PCA does not support sparse input. See TruncatedSVD for a possible alternative.')
-        X = np.array(X, dtype=np.float64, order='C', copy=True) if self.copy else \
-            np.ascontiguousarray(X, dtype=np.float64)
+        # copy=True protects the caller's array from the in-place centring of the reference (:578-579); here X is
+        # centred on the device and the host array is never written, so no host copy is taken either way
+        X = np.ascontiguousarray(X, dtype=np.float64)
         if X.ndim != 2:
             raise ValueError("Expected 2D array, got array with shape %r" % (X.shape,))
         if self.n_components is None:
@@ -153,7 +154,7 @@ class qPCA(_BasePCA):
         Returns (mean [d], S [r], Vt [r, d], U_rows(k) callable, frob_norm, Xd centred on the device)."""
         dev = dv.require_cuda()
         n, d = X.shape
-        Xd = dv.to_device(X, pin=False)
+        Xd = dv.stream_to_device(X)            # chunked; pageable input staged through pinned buffers
         nb = _cabi.lib.sq_col_sums_workspace_bytes(n, d)
         ws = dv.workspace(nb)
         csum = dv.empty((d,))
