@@ -479,7 +479,9 @@ class qMeans_(BaseEstimator):
 
     def fit(self, X, y=None, sample_weight=None):
         """Compute q-means clustering (reference: _dmeans.py:1211-1325)."""
-        X = _validate_X(X, copy=self.copy_x)
+        # copy_x protects the caller's array from the in-place centring (:1262-1269).  The device path never writes
+        # the host array, so the private copy is taken only where the host rows are centred (host-side init below).
+        X = _validate_X(X, copy=False)
         dv.require_cuda()
         rank, world = dv.dist_info()
         if world > 1:
@@ -533,7 +535,9 @@ class qMeans_(BaseEstimator):
         device_init = isinstance(init, str) and init == 'k-means++' and world == 1
         need_host = not hasattr(init, '__array__') and not device_init
         if need_host:
-            X -= X_mean                      # our private copy when copy_x=True, as in the reference
+            if self.copy_x:
+                X = X.copy()                 # a private copy when copy_x=True, as in the reference
+            X -= X_mean
             x_sq_host = np.einsum('ij,ij->i', X, X)
         best_inertia = None
         for _ in range(self._n_init):

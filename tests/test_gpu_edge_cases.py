@@ -140,3 +140,24 @@ def test_chunked_upload_pageable_and_pinned(cuda):
         assert seen == [(r, min(r + 100, 1003)) for r in range(0, 1003, 100)]
         np.testing.assert_allclose([float(v) for v in sums], [X[a:b].sum() for a, b in seen], rtol=1e-12, atol=1e-12)
     assert dv.stream_to_device(np.zeros((0, 5))).shape == (0, 5)
+
+
+@pytest.mark.parametrize("init", ["random", "k-means++", "array"])
+@pytest.mark.parametrize("copy_x", [True, False])
+def test_fit_leaves_the_callers_array_alone(cuda, init, copy_x):
+    """copy_x=True: X untouched; copy_x=False: the reference centres in place and adds the mean back, so X comes
+    back equal up to rounding (reference: _dmeans.py:1262-1269, :1311-1312)"""
+    import warnings
+    from sqlearn.cluster import qMeans_
+    rs = np.random.RandomState(3)
+    X = rs.randn(500, 6) + 5.0
+    X0 = X.copy()
+    ini = X[:4].copy() if init == "array" else init
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        qMeans_(n_clusters=4, init=ini, n_init=1, max_iter=3, delta=0.3, algorithm='full', copy_x=copy_x,
+                true_distance_estimate=False, random_state=0).fit(X)
+    if copy_x or init != "random":
+        assert np.array_equal(X, X0)
+    else:
+        np.testing.assert_allclose(X, X0, rtol=1e-12, atol=1e-12)
