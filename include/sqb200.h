@@ -118,6 +118,9 @@ int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, c
  * draw-by-draw replay path of csrc/ipe.cuh (the path taken when the median of the 13 outcomes may lie outside
  * the enumerated window), so that its law can be tested; results stay exact, only slower.                  */
 int sq_ipe_debug_force_replay(int on);
+/* Test hook: B draws of the amplitude-estimation outcome j conditioned on lying outside the 8-point window
+ * around the grid position x (offsets -3..4 from floor(x)), as the tail sampler of csrc/ipe.cuh makes them.   */
+int sq_ipe_debug_tail_sample(double M, double x, long long B, unsigned long long seed, double* out_j, void* stream);
 
 /* Same E-step as sq_qmeans_assign for callers that cannot give the library a workspace
  * (no counterpart in the reference).  Meant for hosts that are not allowed to allocate on

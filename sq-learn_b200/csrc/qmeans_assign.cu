@@ -931,6 +931,26 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     return SQ_OK;
 }
 
+namespace sq {
+__global__ void ipe_tail_test_kernel(double M, double x, long long B, unsigned long long seed, double* __restrict__ out) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B) return;
+    const double j0 = floor(x), t = x - j0;
+    out[i] = ipe_tail_draw(M, t, j0, seed, (unsigned long long)i, 0u, 0);
+}
+}  // namespace sq
+
+extern "C" int sq_ipe_debug_tail_sample(double M, double x, long long B, unsigned long long seed, double* out_j,
+                                        void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(out_j && B >= 0 && M >= 10.0 && x >= 0.0 && x < M && x != floor(x),
+               "sq_ipe_debug_tail_sample: needs M >= 10 and a non-integer grid position 0 <= x < M");
+    if (B == 0) return SQ_OK;
+    ipe_tail_test_kernel<<<(unsigned)((B + 127) / 128), 128, 0, stream>>>(M, x, B, seed, out_j);
+    SQ_LAUNCH_CHECK("ipe_tail_test_kernel");
+    return SQ_OK;
+}
+
 extern "C" int sq_ipe_debug_force_replay(int on) {
     g_ipe_force_replay = on ? 1 : 0;
     return SQ_OK;

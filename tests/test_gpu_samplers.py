@@ -139,3 +139,33 @@ def test_gram_and_column_sums(cuda, n, d):
     Y = torch.empty_like(Xd)
     _cabi.check(_cabi.lib.sq_sub_rowvec(Xd.data_ptr(), mu.data_ptr(), n, d, Y.data_ptr(), dv.stream_ptr()), "sub")
     np.testing.assert_allclose(Y.cpu().numpy(), X - mu.cpu().numpy(), rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("M,x", [(10, 2.3), (12, 0.41), (28, 13.76), (64, 5.5), (600, 151.27), (600, 299.9),
+                                  (19167, 4791.75), (1001, 500.2), (33, 0.05)])
+def test_ipe_tail_sampler_law(cuda, M, x):
+    """the rejection sampler for outcomes outside the 8-point window (csrc/ipe.cuh) against the exact conditional
+    pmf sin^2(pi t) / (M^2 sin^2(pi (j - x) / M)) restricted to the tail"""
+    import torch
+    from sqlearn import _cabi, _device as dv
+    B = 200000
+    out = torch.empty(B, dtype=torch.float64, device="cuda")
+    _cabi.check(_cabi.lib.sq_ipe_debug_tail_sample(float(M), float(x), B, 77, out.data_ptr(), dv.stream_ptr()), "tail")
+    j = out.cpu().numpy().astype(np.int64)
+    j0 = int(np.floor(x))
+    window = {(j0 + m) % M for m in range(-3, 5)}
+    assert j.min() >= 0 and j.max() < M and not (set(np.unique(j)) & window)
+    grid = np.arange(M)
+    pmf = 1.0 / (M * np.sin(np.pi * (grid - x) / M)) ** 2
+    pmf[list(window)] = 0.0
+    pmf /= pmf.sum()
+    obs = np.bincount(j, minlength=M).astype(float)
+    big = pmf * B >= 10
+    o = np.append(obs[big], obs[~big].sum())
+    e = np.append(pmf[big], pmf[~big].sum()) * B
+    keep = e > 0
+    assert stats.chisquare(o[keep], e[keep] * o[keep].sum() / e[keep].sum()).pvalue > P_MIN
+    # left / right split of the tail mass (what the fast path uses)
+    side = ((j - x + M / 2) % M) < M / 2          # True: counter-clockwise of x ... a fixed partition of the circle
+    p_side = pmf[((grid - x + M / 2) % M) < M / 2].sum()
+    assert abs(side.mean() - p_side) < 5 * np.sqrt(p_side * (1 - p_side) / B) + 1e-12
