@@ -354,6 +354,9 @@ def extra_measurements(eng, centers, D, Q, _cabi, torch):
     c2 = torch.empty_like(centers)
     eng.finalize(centers, c2)
     out["centroid_tomography_ms"] = _timed(torch, lambda: U.tomography(c2, DELTA / 2), 3)
+    # the reference's default E-step (true_distance_estimate=True) in the same iteration, from the phases above
+    out["lloyd_iterations_per_s_ipe_estep_from_phases"] = 1e3 / (
+        out["estep_ipe_ms"] + out["mstep_accumulate_ms"] + out["centroid_tomography_ms"])
     sweep = []
     g = torch.Generator(device=centers.device)
     g.manual_seed(1234)
