@@ -165,6 +165,12 @@ int sq_centroid_accumulate(const double* X, const int* labels, long long n, int 
  * no rows keeps c_old (the reference leaves that row uninitialised).        */
 int sq_centroid_finalize(const double* sums, const double* counts, const double* c_old, int k, int d,
                          double* c_new, void* stream);
+/* k-means++ step on the device (reference: _kmeans_plusplus, _dmeans.py:153-247, the euclidean_distances call at
+ * :222-224 and the np.minimum at :227): dots[n, T] = X . candidates^T comes from sq_project; this fills
+ * d2[t, i] = min(closest[i], max(|x_i|^2 + |c_t|^2 - 2 dots[i, t], 0)) ([T, n], one contiguous row per candidate).
+ * closest may be NULL (first centre).                                                                        */
+int sq_kpp_update(const double* dots, const double* xnorm, const double* cnorm, const double* closest, long long n,
+                  int T, double* d2, void* stream);
 /* euclidean_distances(X[cand], X, squared=True) of _kmeans_plusplus (_dmeans.py:209-211, :228-229):
  * out[t, i] = max(|x_i|^2 + |x_cand[t]|^2 - 2 x_i.x_cand[t], 0), T <= 16 candidates in one pass over X. */
 int sq_rows_sqdist(const double* X, const double* xnorm, long long n, int d, const int* cand, int T, double* out,

@@ -405,6 +405,34 @@ __global__ void rows_sqdist_kernel(const double* __restrict__ X, const double* _
 }
 }  // namespace sq
 
+// k-means++ step, second half: with dots[i, t] = x_i . c_t for the T candidates of the step (from sq_project),
+// d2[t, i] = min(closest[i], max(|x_i|^2 + |c_t|^2 - 2 dots[i, t], 0)) - the candidate's new closest-distance row.
+namespace sq {
+__global__ void kpp_update_kernel(const double* __restrict__ dots, const double* __restrict__ xnorm,
+                                  const double* __restrict__ cnorm, const double* __restrict__ closest, long long n,
+                                  int T, double* __restrict__ d2) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const double xn = xnorm[i], cl = closest ? closest[i] : INFINITY;
+        for (int t = 0; t < T; ++t) {
+            const double v = fmax(xn + cnorm[t] - 2.0 * dots[i * T + t], 0.0);
+            d2[(long long)t * n + i] = v < cl ? v : cl;
+        }
+    }
+}
+}  // namespace sq
+
+extern "C" int sq_kpp_update(const double* dots, const double* xnorm, const double* cnorm, const double* closest,
+                             long long n, int T, double* d2, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(dots && xnorm && cnorm && d2 && n >= 1 && T >= 1, "sq_kpp_update: bad arguments");
+    long long blocks = (n + 255) / 256;
+    int cap = device_sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    kpp_update_kernel<<<(int)blocks, 256, 0, stream>>>(dots, xnorm, cnorm, closest, n, T, d2);
+    SQ_LAUNCH_CHECK("kpp_update_kernel");
+    return SQ_OK;
+}
+
 extern "C" int sq_rows_sqdist(const double* X, const double* xnorm, long long n, int d, const int* cand, int T,
                               double* out, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;

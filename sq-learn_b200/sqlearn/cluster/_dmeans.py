@@ -136,24 +136,33 @@ def _kmeans_plusplus_device(engine, n_clusters, random_state, n_local_trials=Non
         raise ValueError("n_local_trials=%d exceeds the 16 candidates one pass handles" % T)
     dev = X.device
     centers = torch.empty((n_clusters, d), dtype=torch.float64, device=dev)
-    dist = torch.empty((T, n), dtype=torch.float64, device=dev)
+    dots = torch.empty((n, T), dtype=torch.float64, device=dev)
+    d2buf = torch.empty((T, n), dtype=torch.float64, device=dev)
+    zeros = torch.zeros((T,), dtype=torch.float64, device=dev)
 
-    def sqdist(ids):
-        cand = torch.as_tensor(np.asarray(ids, dtype=np.int32), device=dev)
-        _cabi.check(_cabi.lib.sq_rows_sqdist(dv.ptr(X), dv.ptr(engine.xnorm), n, d, dv.ptr(cand), len(ids),
-                                             dv.ptr(dist), dv.stream_ptr()), "sq_rows_sqdist")
-        return dist[:len(ids)]
+    def sqdist_min(ids, closest):
+        """min(closest, squared distance to X[ids[t]]) for every candidate t: the dot products on the tensor
+        cores (one pass over X), then one elementwise kernel"""
+        t = len(ids)
+        idx = torch.as_tensor(np.asarray(ids, dtype=np.int64), device=dev)
+        cand = X[idx].contiguous()
+        cn = engine.xnorm[idx].contiguous()
+        _cabi.check(_cabi.lib.sq_project(dv.ptr(X), n, d, dv.ptr(cand), t, dv.ptr(zeros), dv.ptr(dots),
+                                         dv.stream_ptr()), "sq_project")
+        _cabi.check(_cabi.lib.sq_kpp_update(dv.ptr(dots), dv.ptr(engine.xnorm), dv.ptr(cn), dv.ptr(closest), n, t,
+                                            dv.ptr(d2buf), dv.stream_ptr()), "sq_kpp_update")
+        return d2buf[:t]
 
     center_id = int(random_state.randint(n))
     centers[0] = X[center_id]
-    closest = sqdist([center_id])[0].clone()
+    closest = sqdist_min([center_id], None)[0].clone()
     current_pot = float(closest.sum().item())
     for c in range(1, n_clusters):
         rand_vals = random_state.random_sample(T) * current_pot
         cum = torch.cumsum(closest, dim=0)
         cand = torch.searchsorted(cum, torch.as_tensor(rand_vals, device=dev))
         cand = torch.clamp(cand, max=n - 1).cpu().numpy()
-        d2 = torch.minimum(sqdist(cand), closest[None, :])
+        d2 = sqdist_min(cand, closest)
         pots = d2.sum(dim=1)
         best = int(torch.argmin(pots).item())
         current_pot = float(pots[best].item())
