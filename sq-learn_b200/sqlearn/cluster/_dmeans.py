@@ -541,7 +541,9 @@ class qMeans_(BaseEstimator):
             raise TypeError("_kmeans_single_elkan() got an unexpected keyword argument 'delta' "
                             "(use algorithm='full' for q-means, as in the reference)")
 
-        device_init = isinstance(init, str) and init == 'k-means++' and world == 1
+        # k-means++ seeds on the device; with several ranks every rank seeds from its own rows and rank 0's
+        # centres are broadcast below (as with the host-side inits)
+        device_init = isinstance(init, str) and init == 'k-means++'
         need_host = not hasattr(init, '__array__') and not device_init
         if need_host:
             if self.copy_x:
