@@ -52,6 +52,13 @@ def main():
         gathered = [torch.empty_like(c) for _ in range(world)]
         dist.all_gather(gathered, c)
         ok &= all(torch.equal(g, gathered[0]) for g in gathered)
+        # default seeding (k-means++ on the device, rank 0's centres broadcast): same centres on every rank
+        e3 = qMeans_(n_clusters=k, n_init=2, max_iter=4, delta=0.3, algorithm='full', true_distance_estimate=False,
+                     random_state=3).fit(X[lo:hi])
+        c = torch.as_tensor(e3.cluster_centers_).cuda()
+        gathered = [torch.empty_like(c) for _ in range(world)]
+        dist.all_gather(gathered, c)
+        ok &= all(torch.equal(g, gathered[0]) for g in gathered) and bool(np.isfinite(e3.inertia_))
         pca = qPCA(n_components=8, svd_solver='full').fit(X[lo:hi])
         w = oqp.fit_full(X, 8)
         ok &= np.allclose(pca.singular_values_, w["singular_values_"], rtol=1e-10)
