@@ -617,13 +617,25 @@ class qMeans_(BaseEstimator):
     def _transform(self, X):
         """Distances to the centres, n x k (reference: euclidean_distances, :1349-1351).
         Classical and off the hot path: a library call."""
-        Xd = dv.to_device(X)
+        Xd = dv.stream_to_device(X)
         C = dv.to_device(self.cluster_centers_)
         return torch.cdist(Xd, C, compute_mode='donot_use_mm_for_euclid_dist').cpu().numpy()
 
     def _predict_engine(self, X, delta):
-        Xd = dv.to_device(self._check_test_data(X), pin=True)
-        engine = QMeansEngine(Xd, self.n_clusters)
+        from .. import _cabi
+        X = self._check_test_data(X)
+        if X.shape[0] == 0:
+            raise ValueError("Found array with 0 sample(s)")
+        state = {}
+
+        def on_chunk(out, r0, r1):          # row norms of each chunk while the next one is on its way
+            if "engine" not in state:
+                state["engine"] = QMeansEngine(out, self.n_clusters, norms=False)
+            e = state["engine"]
+            _cabi.check(_cabi.lib.sq_row_sqnorms(dv.ptr(e.X[r0:r1]), r1 - r0, e.d, dv.ptr(e.xnorm[r0:r1]),
+                                                 dv.stream_ptr()), "sq_row_sqnorms")
+        dv.stream_to_device(X, on_chunk)
+        engine = state["engine"]
         C = dv.to_device(self.cluster_centers_)
         labels, mind, inertia = _labels_inertia(engine, C, delta=delta, pool=None,
                                                 true_distance_estimate=self.true_distance_estimate)
