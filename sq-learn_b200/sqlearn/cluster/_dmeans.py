@@ -648,7 +648,7 @@ class qMeans_(BaseEstimator):
         if delta == None:  # noqa: E711
             delta = 0
         labels, _ = self._predict_engine(X, delta)
-        return [int(lb) for lb in labels.cpu().numpy()]
+        return labels.cpu().numpy().tolist()
 
     def score(self, X, y=None, sample_weight=None):
         """Opposite of the k-means objective on X (intent of :1393-1402)."""
