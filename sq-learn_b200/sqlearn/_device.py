@@ -1,11 +1,9 @@
 """Device plumbing: torch owns memory, streams and the process group; the
 kernels are reached through :mod:`sqlearn._cabi` only."""
-import os
-
 import numpy as np
 import torch
 
-from . import _cabi
+from . import _cabi  # noqa: F401  (fails loudly when the library is missing)
 
 
 def require_cuda():

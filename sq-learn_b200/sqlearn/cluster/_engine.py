@@ -8,7 +8,6 @@ no allocation.  With torch.distributed initialised the rows are sharded over
 ranks and the only exchange per iteration is one all-reduce of
 ``[k*d sums | k counts | inertia]``.
 """
-import numpy as np
 import torch
 
 from .. import _cabi

@@ -1,6 +1,5 @@
 """QLSSVC on the GPU against the reference's own outputs (tests/golden/qsvm_reference.npz) and the CPU oracle."""
 import os
-import warnings
 
 import numpy as np
 import pytest

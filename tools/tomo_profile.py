@@ -2,7 +2,6 @@
 usage: python tools/tomo_profile.py B d delta [incremental=0] [norm=L2] [reps=5]"""
 import os
 import sys
-import time
 
 import torch
 
