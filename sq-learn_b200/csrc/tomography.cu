@@ -217,7 +217,8 @@ __device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL
 // and reduction scratch on the direct path) | tot [L/32 + 1 <= 160]
 __host__ __device__ inline size_t tomo_smem_doubles(int L) { return (size_t)3 * L + 160; }
 
-__global__ void tomo_fused_kernel(TomoArgs a) {
+template <int MAXT, int MINB>
+__global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
     extern __shared__ double sm[];
     const int L = a.L, d = a.d, tid = threadIdx.x, T = blockDim.x, H = L >> 1;
     double* P = sm;             // [L]
@@ -355,8 +356,15 @@ static int tomo_launch(const TomoArgs& a, long long B, int lanes, cudaStream_t s
     int threads = many ? L / 8 : L;
     threads = threads < 32 ? 32 : (threads > 512 ? 512 : threads);
     const size_t smem = tomo_smem_doubles(L) * sizeof(double);
-    SQ_CUDA(cudaFuncSetAttribute(tomo_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    tomo_fused_kernel<<<dim3((unsigned)B, lanes), threads, smem, stream>>>(a);
+    // up to 128 threads per vector: capped at 64 registers (a few spilled words), 8+ CTAs per SM - the kernel is
+    // bound by dependent FP64 latency, and 64 registers measured best against 48, 80, 96 and 126
+    if (threads <= 128) {
+        SQ_CUDA(cudaFuncSetAttribute(tomo_fused_kernel<128, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        tomo_fused_kernel<128, 8><<<dim3((unsigned)B, lanes), threads, smem, stream>>>(a);
+    } else {
+        SQ_CUDA(cudaFuncSetAttribute(tomo_fused_kernel<512, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        tomo_fused_kernel<512, 1><<<dim3((unsigned)B, lanes), threads, smem, stream>>>(a);
+    }
     SQ_LAUNCH_CHECK("tomo_fused_kernel");
     return SQ_OK;
 }
