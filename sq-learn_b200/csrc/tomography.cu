@@ -348,12 +348,12 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
 }
 
 // Threads per vector: with few vectors in flight the latency of a vector counts (one thread per leaf, at most 512);
-// with many, throughput does (few threads per vector keep every lane busy through the upper
+// with many, throughput does (L/4 threads, at most 128: few threads per vector keep the lanes busy through the upper
 // levels of the tree and let 9+ vectors share an SM).  The results do not depend on the choice.
 static int tomo_launch(const TomoArgs& a, long long B, int lanes, cudaStream_t stream) {
     const int L = a.L;
     const bool many = B * (long long)lanes >= 4096;
-    int threads = many ? L / 8 : L;
+    int threads = many ? (L / 4 > 128 ? 128 : L / 4) : L;     // (128 = the widest launch of the 64-register build)
     threads = threads < 32 ? 32 : (threads > 512 ? 512 : threads);
     const size_t smem = tomo_smem_doubles(L) * sizeof(double);
     // up to 128 threads per vector: capped at 64 registers (a few spilled words), 8+ CTAs per SM - the kernel is
