@@ -113,3 +113,21 @@ def test_kmeans_plusplus_consumes_random_state_like_reference():
     c_me, i_me = _kmeans_plusplus(X, 7, xs, np.random.RandomState(42))
     assert list(i_ref) == list(i_me)
     np.testing.assert_array_equal(c_ref, c_me)
+
+
+def test_committed_bench_line_has_the_contract_keys():
+    """the bench line committed under profiles/ carries every key the measurement contract names"""
+    import json
+    import os
+    path = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "profiles", "r01_bench_final_1gpu.json")
+    line = json.load(open(path))
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
+        assert key in line, key
+    assert line["n_gpus"] == 1 and line["dtype"] == "f64" and line["vs_baseline"] is None
+    assert set(("bound", "achieved", "peak", "unit", "frac", "traffic")) <= set(line["roofline"])
+    assert abs(line["roofline"]["frac"] - line["roofline"]["achieved"] / line["roofline"]["peak"]) < 1e-9
+    assert set(("value", "unit", "h2d_bytes_per_step", "d2h_bytes_per_step")) <= set(line["e2e"])
+    assert set(("value", "unit", "cores", "kind", "sample")) <= set(line["cpu_baseline"])
+    assert line["gpu_launches"] > 0 and "workload" in line["config"]
+    assert not set(line["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
