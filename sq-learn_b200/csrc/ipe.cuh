@@ -16,8 +16,11 @@
 //     is the (7 - b)-th smallest of the n = 13 - T window draws, whose CDF at a window point is
 //     P(Binomial(n, F) >= 7 - b), F the window CDF in r-order: one more uniform.
 // Anything else (tiny grid, a tail draw inside the window's r-range, the median itself in a
-// tail: ~1e-6 of pairs on ordinary data) replays the same tail draws and samples the window
-// draws one by one.  Every draw is keyed by (seed, row, column, purpose), so the estimate of a
+// tail) replays the same tail draws and samples the window draws one by one.  The estimator comes
+// in two builds: LEAN (grids of >= 32 points, window away from 0 and M/2; any other pair is
+// flagged and left alone) and general; the E-step kernel runs the lean one over a tile and hands
+// the flagged pairs to the general one together (one pair per row when the centroids are plain
+// means: the row's own centroid sits at x ~ 1).  Every draw is keyed by (seed, row, column, purpose), so the estimate of a
 // pair does not depend on which lane, warp, CTA or GPU computes it.
 #pragma once
 #include "common.cuh"
