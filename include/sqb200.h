@@ -171,10 +171,6 @@ int sq_centroid_finalize(const double* sums, const double* counts, const double*
  * closest may be NULL (first centre).                                                                        */
 int sq_kpp_update(const double* dots, const double* xnorm, const double* cnorm, const double* closest, long long n,
                   int T, double* d2, void* stream);
-/* euclidean_distances(X[cand], X, squared=True) of _kmeans_plusplus (_dmeans.py:209-211, :228-229):
- * out[t, i] = max(|x_i|^2 + |x_cand[t]|^2 - 2 x_i.x_cand[t], 0), T <= 16 candidates in one pass over X. */
-int sq_rows_sqdist(const double* X, const double* xnorm, long long n, int d, const int* cand, int T, double* out,
-                   void* stream);
 /* squared_norm(a - b) (_dmeans.py:651), single deterministic reduction      */
 int sq_sqdiff_sum(const double* a, const double* b, long long n, double* out, void* stream);
 

@@ -367,44 +367,6 @@ extern "C" int sq_sqdiff_sum(const double* a, const double* b, long long n, doub
 }
 
 // ---------------------------------------------------------------------------
-// k-means++ support: squared distances from every row to a few candidate rows
-// ---------------------------------------------------------------------------
-// _kmeans_plusplus (sklearn/cluster/_dmeans.py:153-247) evaluates, per step,
-// euclidean_distances(X[candidates], X, squared=True) = |x|^2 + |c|^2 - 2 x.c clamped at 0.
-// One pass over X for all T candidates (T = 2 + log k, at most 16): out[t, i].
-namespace sq {
-static const int KPP_MAXT = 16;
-__global__ void rows_sqdist_kernel(const double* __restrict__ X, const double* __restrict__ xnorm, long long n, int d,
-                                   const int* __restrict__ cand, int T, double* __restrict__ out) {
-    extern __shared__ double cs[];  // [T][d] candidate rows
-    for (int i = threadIdx.x; i < T * d; i += blockDim.x) cs[i] = X[(long long)cand[i / d] * d + (i % d)];
-    __syncthreads();
-    const int lane = threadIdx.x & 31;
-    long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
-    for (; w < n; w += nw) {
-        const double* x = X + w * (long long)d;
-        double acc[KPP_MAXT];
-#pragma unroll
-        for (int t = 0; t < KPP_MAXT; ++t) acc[t] = 0.0;
-        for (int f = lane; f < d; f += 32) {
-            double v = x[f];
-#pragma unroll
-            for (int t = 0; t < KPP_MAXT; ++t)
-                if (t < T) acc[t] = fma(v, cs[t * d + f], acc[t]);
-        }
-        double xn = xnorm[w];
-#pragma unroll
-        for (int t = 0; t < KPP_MAXT; ++t) {
-            if (t < T) {
-                double s = warp_sum(acc[t]);
-                if (lane == 0) out[(long long)t * n + w] = fmax(xn + xnorm[cand[t]] - 2.0 * s, 0.0);
-            }
-        }
-    }
-}
-}  // namespace sq
-
 // k-means++ step, second half: with dots[i, t] = x_i . c_t for the T candidates of the step (from sq_project),
 // d2[t, i] = min(closest[i], max(|x_i|^2 + |c_t|^2 - 2 dots[i, t], 0)) - the candidate's new closest-distance row.
 namespace sq {
@@ -430,21 +392,5 @@ extern "C" int sq_kpp_update(const double* dots, const double* xnorm, const doub
     if (blocks > cap) blocks = cap;
     kpp_update_kernel<<<(int)blocks, 256, 0, stream>>>(dots, xnorm, cnorm, closest, n, T, d2);
     SQ_LAUNCH_CHECK("kpp_update_kernel");
-    return SQ_OK;
-}
-
-extern "C" int sq_rows_sqdist(const double* X, const double* xnorm, long long n, int d, const int* cand, int T,
-                              double* out, void* stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    SQ_REQUIRE(X && xnorm && cand && out && n >= 1 && d >= 1, "sq_rows_sqdist: bad arguments");
-    SQ_REQUIRE(T >= 1 && T <= KPP_MAXT, "sq_rows_sqdist: T=%d outside [1,%d]", T, KPP_MAXT);
-    size_t sh = (size_t)T * d * sizeof(double);
-    if (sh > 200 * 1024) { set_error("sq_rows_sqdist: T*d=%d exceeds shared memory", T * d); return SQ_ERR_UNSUPPORTED; }
-    SQ_CUDA(cudaFuncSetAttribute(rows_sqdist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
-    long long blocks = (n + 7) / 8;
-    int cap = device_sm_count() * 8;
-    if (blocks > cap) blocks = cap;
-    rows_sqdist_kernel<<<(int)blocks, 256, sh, stream>>>(X, xnorm, n, d, cand, T, out);
-    SQ_LAUNCH_CHECK("rows_sqdist_kernel");
     return SQ_OK;
 }

@@ -48,7 +48,6 @@ SIGNATURES = {
                                        c_void_p, c_size_t, c_void_p]),
     "sq_centroid_finalize": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "sq_kpp_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_void_p, c_void_p]),
-    "sq_rows_sqdist": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "sq_sqdiff_sum": (c_int, [c_void_p, c_void_p, c_ll, c_void_p, c_void_p]),
     "sq_fejer_sample": (c_int, [c_void_p, c_void_p, c_ll, c_ull, c_ull, c_void_p, c_void_p]),
     "sq_fejer_sample_bruteforce": (c_int, [c_void_p, c_void_p, c_ll, c_ull, c_ull, c_void_p, c_void_p]),

@@ -125,8 +125,9 @@ def _kmeans_plusplus(X, n_clusters, x_squared_norms, random_state, n_local_trial
 def _kmeans_plusplus_device(engine, n_clusters, random_state, n_local_trials=None):
     """k-means++ seeding with X on the device (same algorithm and same consumption of
     ``random_state`` as :func:`_kmeans_plusplus` / the reference's _dmeans.py:153-247).  Per step one
-    pass over X gives the squared distances to all candidates (``sq_rows_sqdist``); the prefix sum,
-    the binary search and the reductions over n run as device tensor ops.  Returns device centres."""
+    pass over X on the tensor cores gives the dot products with all candidates (``sq_project``) and one
+    elementwise kernel the new closest distances (``sq_kpp_update``); the prefix sum, the binary search and
+    the reductions over n run as device tensor ops.  Returns device centres."""
     from .. import _cabi
     X, n, d = engine.X, engine.n, engine.d
     if n_local_trials is None:
