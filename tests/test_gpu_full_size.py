@@ -125,3 +125,22 @@ def test_config4_10Mx128_k256_properties(cuda):
     est = U.tomography(c2, 0.25)
     unit = c2 / c2.norm(dim=1, keepdim=True)
     assert float((est - unit).norm(dim=1).max().item()) <= 0.25
+    # IPE mode at full size: the reported minimum is an amplitude-estimation grid value of the chosen pair,
+    # 2 S sin^2(pi r / M) with integer r, and the estimate of the inner product is within epsilon * max(1, |x.c|)
+    # of the truth for nearly every row (each amplitude estimate holds with probability >= 8/pi^2, the median of 13
+    # with probability >= 0.9: median_evaluation's gamma = 0.1, Utility.py:534-572)
+    labels, mind, inertia = D._labels_inertia(eng, C, delta=0.5, true_distance_estimate=True)
+    ls = labels[sub].cpu().numpy()
+    ms = mind[sub].cpu().numpy()
+    xn = (Xs * Xs).sum(axis=1)
+    cn = (Ch * Ch).sum(axis=1)[ls]
+    dot = np.einsum("ij,ij->i", Xs, Ch[ls])
+    S = xn + cn
+    eps_a = 0.25 * np.maximum(1.0, np.abs(dot)) / S
+    M = np.ceil((np.pi / (2 * eps_a)) * (1 + np.sqrt(1 + 4 * eps_a)))
+    r = M * np.arcsin(np.sqrt(np.clip(ms / (2 * S), 0, 1))) / np.pi
+    assert np.abs(r - np.rint(r)).max() < 1e-6
+    ip_est = (S - ms) / 2
+    ok = np.abs(ip_est - dot) <= 0.25 * np.maximum(1.0, np.abs(dot))
+    assert ok.mean() > 0.9
+    assert float(inertia.item()) == pytest.approx(float(mind.sum().item()), rel=1e-12)
