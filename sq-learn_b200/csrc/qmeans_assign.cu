@@ -223,10 +223,24 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     unsigned c_phase = 0;
     const unsigned stages_u32 = (unsigned)__cvta_generic_to_shared(stages);
     for (int q = 0; q < total; ++q) {
-        if (TMA) mbar_wait(&full_bar[c_stage], c_phase);
-        else cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        issue();
+        if (TMA) {
+            // The stage about to be refilled was read in the previous iteration.  Only the warp that issues
+            // the TMA has to wait for everybody to be done with it: the others just say so and go on
+            // (one named barrier per stage of the ring: a warp can run at most STAGES - 1 iterations ahead of the
+            // slowest one - it needs the load issued after that barrier completed - so an arrival for iteration
+            // q + STAGES can never be counted in iteration q).
+            if (warp == 0) {
+                asm volatile("barrier.sync %0, %1;" ::"r"(1 + c_stage), "r"(Cfg::THREADS) : "memory");
+                issue();
+            } else {
+                asm volatile("barrier.arrive %0, %1;" ::"r"(1 + c_stage), "r"(Cfg::THREADS) : "memory");
+            }
+            mbar_wait(&full_bar[c_stage], c_phase);
+        } else {
+            cp_async_wait<STAGES - 2>();
+            __syncthreads();
+            issue();
+        }
 
         const unsigned st_u32 = stages_u32 + (unsigned)c_stage * (Cfg::STAGE_DOUBLES * 8);
         const unsigned fa_u32 = st_u32 + fragA * 8, fb_u32 = st_u32 + fragB * 8;
@@ -828,7 +842,7 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
 
 // tile shapes: wide (all of k <= 256 in one sweep) down to narrow for tiny k
 // Two CTAs share an SM so that one CTA's epilogue (tensor pipe idle) overlaps the other's main loop.
-using CfgN256 = TileCfg<32, 256, 1, 8, 2, 16, 2>;  // 256 threads, 2 x 36 KB stages (half the barriers of 5 x 18 KB: +1.7 %), 2 CTAs/SM
+using CfgN256 = TileCfg<32, 256, 1, 8, 2, 16, 2>;  // 256 threads, 2 x 36 KB stages, 2 CTAs/SM
 using CfgN128 = TileCfg<64, 128, 2, 4, 5, 8, 2>;   // 256 threads, 5 x 12 KB ring
 using CfgN64 = TileCfg<128, 64, 4, 2, 4, 16, 2>;   // 256 threads, 4 x 24 KB ring
 using CfgN32 = TileCfg<128, 32, 4, 1, 4, 16, 2>;   // 128 threads
