@@ -843,7 +843,7 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
 // tile shapes: wide (all of k <= 256 in one sweep) down to narrow for tiny k
 // Two CTAs share an SM so that one CTA's epilogue (tensor pipe idle) overlaps the other's main loop.
 using CfgN256 = TileCfg<32, 256, 1, 8, 2, 16, 2>;  // 256 threads, 2 x 36 KB stages, 2 CTAs/SM
-using CfgN128 = TileCfg<64, 128, 2, 4, 5, 8, 2>;   // 256 threads, 5 x 12 KB ring
+using CfgN128 = TileCfg<64, 128, 2, 4, 3, 16, 2>;  // 256 threads, 3 x 24 KB stages
 using CfgN64 = TileCfg<128, 64, 4, 2, 4, 16, 2>;   // 256 threads, 4 x 24 KB ring
 using CfgN32 = TileCfg<128, 32, 4, 1, 4, 16, 2>;   // 128 threads
 using CfgN16 = TileCfg<256, 16, 8, 1, 3, 16, 2>;   // 256 threads, k <= 16
