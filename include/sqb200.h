@@ -97,6 +97,14 @@ int sq_tomography_batched_spec(const double* V, long long B, int d, double delta
                                unsigned long long vec_offset, double* est, double* n_used, double* err,
                                int* attempts, int* stop_idx, void* stream);
 
+/* Measurement hook (no reference counterpart; process-wide and NOT thread-safe - meant for tools/, not for
+ * callers): what = 0 sets the factor f of the rule "an attempt with N <= f * clamp(L, 32, 512) measurements
+ * draws them one by one instead of splitting counts down the tree" (L = d rounded up to a power of two;
+ * both samplers are exact, so the law does not change, the draws do); 1 and 2 set the divisor and the cap of
+ * the threads-per-vector rule for large batches (threads = min(L / divisor, cap); results do not depend on
+ * them).                                                                                                   */
+int sq_tomography_tune(int what, double value);
+
 /* ---- q-means E-step ------------------------------------------------------ *
  * labels_estimation (sklearn/cluster/_dmeans.py:732-777) with ipe /
  * amplitude_estimation / median_evaluation (Utility.py:697-737, :442-531,

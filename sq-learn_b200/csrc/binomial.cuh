@@ -103,4 +103,36 @@ __host__ __device__ inline double binomial_split(double n, double pl, double pr,
     return flip ? n - k : k;
 }
 
+// First step of binomial_split, for callers that handle many nodes at once: settles the trivial cases and the
+// (common) immediate acceptance of BTRS's first candidate, which needs one sqrt, four divisions and no logarithm.
+// Returns BINOM_DONE with the count in `out`, or says which branch of binomial_split the node needs.  A node
+// that is not done is handed, with a FRESH generator of the same stream, to binomial_split, which replays the
+// first candidate and carries on - so head + split together return exactly what binomial_split alone returns.
+// (tomography.cu gathers the unfinished nodes of a tree level and runs them densely, instead of letting one
+// rejected lane hold its 31 neighbours through the logarithms of the full acceptance test.)
+enum { BINOM_DONE = 0, BINOM_NEEDS_BINV = 1, BINOM_NEEDS_BTRS = 2 };
+__host__ __device__ inline int binomial_head(double n, double pl, double pr, Philox& rng, double& out) {
+    if (n <= 0.0 || pl <= 0.0) { out = 0.0; return BINOM_DONE; }
+    if (pr <= 0.0) { out = n; return BINOM_DONE; }
+    double tot = pl + pr;
+    bool flip = pl > pr;
+    double p = (flip ? pr : pl) / tot;
+    double q = (flip ? pl : pr) / tot;
+    double np = n * p;
+    if (np < 10.0) return BINOM_NEEDS_BINV;
+    double npq = np * q;
+    double spq = sqrt(npq);
+    double b = 1.15 + 2.53 * spq;
+    double a = -0.0873 + 0.0248 * b + 0.01 * p;
+    double c = np + 0.5;
+    double vr = 0.92 - 4.2 / b;
+    double u, v;
+    rng.uniform2(u, v);
+    u -= 0.5;
+    double us = 0.5 - fabs(u);
+    double k = floor((2.0 * a / us + b) * u + c);
+    if (us >= 0.07 && v <= vr) { out = flip ? n - k : k; return BINOM_DONE; }
+    return BINOM_NEEDS_BTRS;
+}
+
 }  // namespace sq

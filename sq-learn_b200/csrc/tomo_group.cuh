@@ -1,0 +1,28 @@
+// Interface between tomography.cu (C ABI, dispatch) and tomo_group.cu (the group kernel).
+#pragma once
+#include "common.cuh"
+
+namespace sq {
+
+struct TomoGroupArgs {
+    const double* V;      // [B, d]
+    double* est;          // [B, d]
+    double* n_used;       // [B]
+    double* err;          // [B]
+    double* ws;           // ctas * G * tomo_group_wsv(L) doubles
+    long long B;
+    int d, L, logL;
+    int G;                // vectors per group
+    int norm_inf;
+    int attempt;          // index of the attempt in the schedule (keys the Philox streams 2*attempt, 2*attempt + 1)
+    double N;             // measurements of the attempt
+    unsigned long long seed, vec_offset;
+};
+
+// doubles of workspace per vector: the sum tree / counts [2L] and the partial sums of the ordered reductions [L/2]
+__host__ __device__ inline size_t tomo_group_wsv(int L) { return (size_t)2 * L + (L / 2 < 2 ? 2 : L / 2); }
+size_t tomo_group_ws_bytes(int L, int G, int ctas);
+int tomo_group_size(long long B, int L, int sms);
+int tomo_group_launch(TomoGroupArgs a, int ctas, cudaStream_t stream);
+
+}  // namespace sq

@@ -19,6 +19,7 @@
 #include "binomial.cuh"
 #include "common.cuh"
 #include "sqb200.h"
+#include "tomo_group.cuh"
 
 namespace sq {
 
@@ -39,6 +40,7 @@ struct TomoArgs {
     int sched_len;
     int norm_inf;         // 0: L2, 1: L-infinity
     int stop;             // stop at the first attempt with err <= delta
+    double direct_factor; // attempts with N <= direct_factor * clamp(L, 32, 512) draw their samples one by one
     double delta;
     unsigned long long seed;
     unsigned long long vec_offset;  // global id of vector 0 (sharding / call offset)
@@ -84,21 +86,74 @@ __device__ __forceinline__ void build_tree(double* mass, int L, int logL, int ti
     __syncthreads();
 }
 
+// Scratch of split_tree: ids of the nodes of a level whose draw binomial_head did not settle (BINV nodes from
+// the front, BTRS nodes from the back), and two pairs of counters used by alternate levels.
+struct SplitScratch {
+    unsigned short* ids;   // [cap]
+    int* ctr;              // [4]
+    int cap;               // nodes of the widest level (L/2)
+};
+__host__ __device__ inline size_t split_scratch_doubles(int L) { return (size_t)(L / 8 > 2 ? L / 8 : 2) + 2; }
+__device__ __forceinline__ SplitScratch split_scratch_at(double* mem, int L) {
+    SplitScratch sc;
+    sc.ctr = reinterpret_cast<int*>(mem);
+    sc.ids = reinterpret_cast<unsigned short*>(mem + 2);
+    sc.cap = L >> 1;
+    return sc;
+}
+
 // top-down conditional binomial splitting; cnt[1] must be set by the caller.  cnt may alias mass: a node's
 // two child masses are read by that node alone, right before it stores the two child counts over them.
+// A level takes two passes.  Pass 1, one thread per node: binomial_head settles empty nodes and the nodes
+// whose first BTRS candidate is accepted at once (most of them when n p is large); the others are listed.
+// Pass 2 runs binomial_split on the listed nodes, packed densely over the threads and sorted by branch,
+// so the logarithms of the full acceptance test are paid per rejected node, not per warp holding one.
+// Every node draws from its own Philox stream (vec, stream, key_base + node), so neither the pass a node
+// is settled in nor its place in the list changes the result.
 __device__ __forceinline__ void split_tree(const double* mass, double* cnt, int logL, int tid, int T,
-                                           unsigned long long seed, unsigned long long vec, unsigned stream) {
+                                           unsigned long long seed, unsigned long long vec, unsigned stream,
+                                           unsigned key_base, SplitScratch sc) {
+    const int lane = tid & 31;
+    if (tid == 0) { sc.ctr[0] = 0; sc.ctr[1] = 0; sc.ctr[2] = 0; sc.ctr[3] = 0; }
     for (int lev = 0; lev < logL; ++lev) {
         __syncthreads();
-        int first = 1 << lev;
-        for (int i = first + tid; i < 2 * first; i += T) {
-            double n = cnt[i];
-            double left = 0.0;
-            const double ml = mass[2 * i], mr = mass[2 * i + 1];
-            if (n > 0.0) {
-                Philox rng(seed, vec, stream, (unsigned)i);
-                left = binomial_split(n, ml, mr, rng);
+        const int first = 1 << lev;
+        int* ctr = sc.ctr + 2 * (lev & 1);
+        if (tid == 0) { sc.ctr[2 * ((lev + 1) & 1)] = 0; sc.ctr[2 * ((lev + 1) & 1) + 1] = 0; }
+        for (int base = first; base < 2 * first; base += T) {
+            const int i = base + tid;
+            int st = BINOM_DONE;
+            if (i < 2 * first) {
+                const double n = cnt[i];
+                double left = 0.0;
+                if (n > 0.0) {
+                    Philox rng(seed, vec, stream, key_base + (unsigned)i);
+                    st = binomial_head(n, mass[2 * i], mass[2 * i + 1], rng, left);
+                }
+                if (st == BINOM_DONE) { cnt[2 * i] = left; cnt[2 * i + 1] = n - left; }
             }
+            const unsigned m1 = __ballot_sync(0xffffffffu, st == BINOM_NEEDS_BINV);
+            const unsigned m2 = __ballot_sync(0xffffffffu, st == BINOM_NEEDS_BTRS);
+            if (m1 | m2) {
+                int b1 = 0, b2 = 0;
+                if (lane == 0) {
+                    if (m1) b1 = atomicAdd(&ctr[0], __popc(m1));
+                    if (m2) b2 = atomicAdd(&ctr[1], __popc(m2));
+                }
+                b1 = __shfl_sync(0xffffffffu, b1, 0);
+                b2 = __shfl_sync(0xffffffffu, b2, 0);
+                const unsigned lt = (1u << lane) - 1u;
+                if (st == BINOM_NEEDS_BINV) sc.ids[b1 + __popc(m1 & lt)] = (unsigned short)i;
+                if (st == BINOM_NEEDS_BTRS) sc.ids[sc.cap - 1 - (b2 + __popc(m2 & lt))] = (unsigned short)i;
+            }
+        }
+        __syncthreads();
+        const int nf = ctr[0], nb = ctr[1];
+        for (int j = tid; j < nf + nb; j += T) {
+            const int i = j < nf ? sc.ids[j] : sc.ids[sc.cap - 1 - (j - nf)];
+            const double n = cnt[i];
+            Philox rng(seed, vec, stream, key_base + (unsigned)i);
+            const double left = binomial_split(n, mass[2 * i], mass[2 * i + 1], rng);
             cnt[2 * i] = left;
             cnt[2 * i + 1] = n - left;
         }
@@ -214,8 +269,8 @@ __device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL
 }
 
 // shared memory of one vector, in doubles: P [L] | A [2L] (sum tree, then counts in place; CDF, int counts
-// and reduction scratch on the direct path) | tot [L/32 + 1 <= 160]
-__host__ __device__ inline size_t tomo_smem_doubles(int L) { return (size_t)3 * L + 160; }
+// and reduction scratch on the direct path) | tot [L/32 + 1 <= 160] | split_tree's node list
+__host__ __device__ inline size_t tomo_smem_doubles(int L) { return (size_t)3 * L + 160 + split_scratch_doubles(L); }
 
 template <int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
@@ -224,6 +279,7 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
     double* P = sm;             // [L]
     double* A = P + L;          // [2L]
     double* tot = A + 2 * L;    // [160]
+    const SplitScratch sc = split_scratch_at(tot + 160, L);
     double* mass = A;
     double* cnt = A;
 
@@ -267,7 +323,7 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
         // Few measurements: draw them one by one (N/T categorical draws per thread, log2(d) probes each)
         // instead of walking the tree, whose log2(d) dependent binomial draws cost more than that.
         // The rule depends on (N, L) only.
-        const bool direct = N <= 64.0 * (L < 32 ? 32 : (L > 512 ? 512 : L));
+        const bool direct = N <= a.direct_factor * (L < 32 ? 32 : (L > 512 ? 512 : L));
         int* cnt_i = reinterpret_cast<int*>(A + L);      // [L] ints = A[L .. L + L/2)
         int* guide = reinterpret_cast<int*>(A + L + H);  // [L] ints = A[L + L/2 .. 2L), shared with the reduction scratch
         double e;
@@ -295,7 +351,7 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
             for (int i = tid; i < L; i += T) { double x = vin(i); mass[L + i] = x * x; }
             build_tree(mass, L, a.logL, tid, T);
             if (tid == 0) cnt[1] = N;
-            split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at));
+            split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at), 0u, sc);
             // ---- stage 2 ----
             const double sminus = canon_sum([&](int i) {
                 double p = sqrt(cnt[L + i] / N), x = vin(i);
@@ -309,7 +365,7 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
                 Philox rng(a.seed, vec, (unsigned)(2 * at + 1), 0u);
                 cnt[1] = binomial_split(N, mass[1], sminus, rng);
             }
-            split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at + 1));
+            split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at + 1), 0u, sc);
         }
         // ---- sign rule + error ----
         auto sign_and_diff = [&](int i) {
@@ -350,10 +406,20 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
 // Threads per vector: with few vectors in flight the latency of a vector counts (one thread per leaf, at most 512);
 // with many, throughput does (L/4 threads, at most 128: few threads per vector keep the lanes busy through the upper
 // levels of the tree and let 9+ vectors share an SM).  The results do not depend on the choice.
-static int tomo_launch(const TomoArgs& a, long long B, int lanes, cudaStream_t stream) {
+// Tunables (sq_tomography_tune; process-wide, not thread-safe: a tool for measurements, not part of the API
+// a caller needs).  They change how the work is arranged, and direct_factor which of the two exact samplers
+// an attempt uses - never the law of the result.
+static double g_direct_factor = 64.0;
+static int g_many_div = 4, g_many_cap = 128;
+static int g_group_on = 1;            // single attempts of many vectors go to the group kernel (tomo_group.cu)
+static long long g_group_min_B = 296; // ... from this many vectors on
+
+static int tomo_launch(TomoArgs a, long long B, int lanes, cudaStream_t stream) {
     const int L = a.L;
+    a.direct_factor = g_direct_factor;
     const bool many = B * (long long)lanes >= 4096;
-    int threads = many ? (L / 4 > 128 ? 128 : L / 4) : L;     // (128 = the widest launch of the 64-register build)
+    int threads = many ? (L / g_many_div > g_many_cap ? g_many_cap : L / g_many_div) : L;   // (128 = the widest launch of the 64-register build)
+    threads = (threads + 31) & ~31;
     threads = threads < 32 ? 32 : (threads > 512 ? 512 : threads);
     const size_t smem = tomo_smem_doubles(L) * sizeof(double);
     // up to 128 threads per vector: capped at 64 registers (a few spilled words), 8+ CTAs per SM - the kernel is
@@ -445,6 +511,7 @@ __global__ void tomo_big_top_kernel(TomoBigArgs a, int stage) {
     double* mass = sm;            // [2 NB]
     double* cnt = mass + 2 * NB;  // [2 NB]
     double* red = cnt + 2 * NB;   // [32]
+    const SplitScratch sc = split_scratch_at(red + 32, NB);
     const unsigned long long vec = a.vec_offset + (unsigned long long)b;
     double sminus = 0.0;
     for (int i = tid; i < NB; i += T) {
@@ -460,7 +527,7 @@ __global__ void tomo_big_top_kernel(TomoBigArgs a, int stage) {
             cnt[1] = binomial_split(a.N, mass[1], sminus, rng);
         }
     }
-    split_tree(mass, cnt, a.logNB, tid, T, a.seed, vec, (unsigned)(4 * a.at + (stage == 1 ? 0 : 2)));
+    split_tree(mass, cnt, a.logNB, tid, T, a.seed, vec, (unsigned)(4 * a.at + (stage == 1 ? 0 : 2)), 0u, sc);
     for (int i = tid; i < a.nblk; i += T) a.bcnt[b * a.nblk + i] = cnt[NB + i];
 }
 
@@ -475,6 +542,7 @@ __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
     double* mass = P + TB;        // [2 TB]
     double* cnt = mass + 2 * TB;  // [2 TB]
     double* red = cnt + 2 * TB;   // [32]
+    const SplitScratch sc = split_scratch_at(red + 32, TB);
     bool zero;
     const double div = big_scale(a.sumsq[b], zero);
     const unsigned long long vec = a.vec_offset + (unsigned long long)b;
@@ -494,23 +562,8 @@ __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
     build_tree(mass, TB, TB_LOG, tid, T);
     if (tid == 0) cnt[1] = a.bcnt[b * a.nblk + blk];
     // node ids are offset by the block so that every (vector, block, node) owns its own Philox stream
-    {
-        for (int lev = 0; lev < TB_LOG; ++lev) {
-            __syncthreads();
-            int first = 1 << lev;
-            for (int i = first + tid; i < 2 * first; i += T) {
-                double n = cnt[i];
-                double left = 0.0;
-                if (n > 0.0) {
-                    Philox rng(a.seed, vec, (unsigned)(4 * a.at + (stage == 1 ? 1 : 3)), (unsigned)(blk * (2 * TB) + i));
-                    left = binomial_split(n, mass[2 * i], mass[2 * i + 1], rng);
-                }
-                cnt[2 * i] = left;
-                cnt[2 * i + 1] = n - left;
-            }
-        }
-        __syncthreads();
-    }
+    split_tree(mass, cnt, TB_LOG, tid, T, a.seed, vec, (unsigned)(4 * a.at + (stage == 1 ? 1 : 3)),
+               (unsigned)(blk * (2 * TB)), sc);
     if (stage == 1) {
         double sp = 0.0, smn = 0.0;
         for (int i = tid; i < TB; i += T) {
@@ -567,6 +620,18 @@ __global__ void tomo_big_finish_kernel(TomoBigArgs a) {
 using namespace sq;
 
 extern "C" int sq_tomography_max_fused_dim(void) { return 4096; }
+
+extern "C" int sq_tomography_tune(int what, double value) {
+    switch (what) {
+        case 0: SQ_REQUIRE(value >= 0.0, "sq_tomography_tune: direct_factor >= 0"); g_direct_factor = value; break;
+        case 1: SQ_REQUIRE(value >= 1.0 && value <= 64.0, "sq_tomography_tune: divisor in [1, 64]"); g_many_div = (int)value; break;
+        case 2: SQ_REQUIRE(value >= 32.0 && value <= 128.0, "sq_tomography_tune: cap in [32, 128]"); g_many_cap = (int)value; break;
+        case 3: g_group_on = value != 0.0; break;
+        case 4: SQ_REQUIRE(value >= 1.0, "sq_tomography_tune: minimum batch >= 1"); g_group_min_B = (long long)value; break;
+        default: SQ_REQUIRE(false, "sq_tomography_tune: unknown tunable %d", what);
+    }
+    return SQ_OK;
+}
 
 extern "C" int sq_tomography_batched(const double* V, long long B, int d, double delta, int norm_inf, int stop,
                                      const double* sched_host, int sched_len, unsigned long long seed,
@@ -630,8 +695,28 @@ static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, 
     *total = o;
 }
 
+// group kernel (d <= the fused limit): geometry for a batch of B vectors of L leaves
+static void tomo_group_geometry(long long B, int L, int* G, int* ctas) {
+    const int sms = device_sm_count();
+    *G = tomo_group_size(B, L, sms);
+    long long groups = (B + *G - 1) / *G;
+    *ctas = (int)(groups < sms ? groups : sms);
+}
+static void tomo_leaves(int d, int* L, int* logL) {
+    int l = 2, lg = 1;
+    while (l < d) { l <<= 1; ++lg; }
+    *L = l; *logL = lg;
+}
+
 extern "C" size_t sq_tomography_workspace_bytes(long long B, int d) {
-    if (d <= sq_tomography_max_fused_dim() || B <= 0) return 0;
+    if (B <= 0 || d < 1) return 0;
+    if (d <= sq_tomography_max_fused_dim()) {
+        if (!g_group_on || B < g_group_min_B) return 0;
+        int L, logL, G, ctas;
+        tomo_leaves(d, &L, &logL);
+        tomo_group_geometry(B, L, &G, &ctas);
+        return tomo_group_ws_bytes(L, G, ctas);
+    }
     int nblk, NB, logNB;
     size_t off[6], total;
     tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
@@ -657,8 +742,8 @@ static int tomo_big_prepare(TomoBigArgs& a, const double* V, long long B, int d,
 }
 
 static int tomo_big_phase(TomoBigArgs a, int phase, int blk_lo, int blk_hi, cudaStream_t stream) {
-    const size_t sm_top = (size_t)(4 * a.NB + 32) * sizeof(double);
-    const size_t sm_blk = (size_t)(6 * TB + 32) * sizeof(double);
+    const size_t sm_top = (size_t)(4 * a.NB + 32 + split_scratch_doubles(a.NB)) * sizeof(double);
+    const size_t sm_blk = (size_t)(6 * TB + 32 + split_scratch_doubles(TB)) * sizeof(double);
     const int ttop = a.NB < 64 ? 64 : (a.NB > 512 ? 512 : a.NB);   // register budget: ~96 per thread
     const dim3 gall(a.nblk, (unsigned)a.B), gown(blk_hi - blk_lo, (unsigned)a.B);
     a.blk_lo = blk_lo;
@@ -689,10 +774,31 @@ extern "C" int sq_tomography_batched_ws(const double* V, long long B, int d, dou
                                         const double* sched_host, int sched_len, unsigned long long seed,
                                         unsigned long long vec_offset, double* est, double* n_used, double* err,
                                         void* ws, size_t ws_bytes, void* stream_) {
-    if (d <= sq_tomography_max_fused_dim())
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (d <= sq_tomography_max_fused_dim()) {
+        // One attempt (single-shot, or the last of a schedule without the stop rule) of many vectors, with more
+        // measurements than the one-by-one sampler takes: the group kernel.  Its results are bit-identical to the
+        // fused kernel's, so which of the two runs is a matter of speed only.
+        const bool one = sched_len == 1 || !stop;
+        if (one && g_group_on && B >= g_group_min_B && V && est && n_used && err && sched_host && ws &&
+            sched_len >= 1 && sched_len <= 128 && d >= 1 && delta > 0.0) {
+            int L, logL, G, ctas;
+            tomo_leaves(d, &L, &logL);
+            const double N = sched_host[sched_len - 1];
+            SQ_REQUIRE(N >= 1.0 && N < 9.0e15, "sq_tomography_batched_ws: schedule entry out of range");
+            const bool direct = N <= g_direct_factor * (L < 32 ? 32 : (L > 512 ? 512 : L));
+            tomo_group_geometry(B, L, &G, &ctas);
+            if (!direct && ws_bytes >= tomo_group_ws_bytes(L, G, ctas)) {
+                TomoGroupArgs g;
+                g.V = V; g.est = est; g.n_used = n_used; g.err = err; g.ws = (double*)ws; g.B = B; g.d = d; g.L = L;
+                g.logL = logL; g.G = G; g.norm_inf = norm_inf; g.attempt = sched_len - 1; g.N = N; g.seed = seed;
+                g.vec_offset = vec_offset;
+                return tomo_group_launch(g, ctas, stream);
+            }
+        }
         return sq_tomography_batched(V, B, d, delta, norm_inf, stop, sched_host, sched_len, seed, vec_offset, est,
                                      n_used, err, nullptr, nullptr, stream_);
-    cudaStream_t stream = (cudaStream_t)stream_;
+    }
     SQ_REQUIRE(V && est && n_used && err && sched_host, "sq_tomography_batched_ws: null pointer");
     SQ_REQUIRE(B >= 0 && B <= 65535, "sq_tomography_batched_ws: B=%lld outside [0, 65535] for d > %d", B,
                sq_tomography_max_fused_dim());

@@ -271,6 +271,16 @@ def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, v
             vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err), None, dv.ptr(scratch), dv.stream_ptr()),
             "sq_tomography_batched_spec")
         return est, n_used, err, tr, att, sched
+    if not trace:
+        # a single attempt of many vectors runs in the group kernel, which keeps its trees in a workspace
+        # (0 bytes asked for when the fused kernel will be used)
+        nb = _cabi.lib.sq_tomography_workspace_bytes(B, d)
+        ws = dv.workspace(nb) if nb else None
+        _cabi.check(_cabi.lib.sq_tomography_batched_ws(
+            dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, 1 if (stop and incremental) else 0,
+            sched.ctypes.data, len(sched), seed_, vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err),
+            dv.ptr(ws), nb, dv.stream_ptr()), "sq_tomography_batched_ws")
+        return est, n_used, err, tr, att, sched
     _cabi.check(_cabi.lib.sq_tomography_batched(
         dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, 1 if (stop and incremental) else 0,
         sched.ctypes.data, len(sched), seed_, vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err),
