@@ -20,27 +20,26 @@
 
 namespace sq {
 
-static const int GT = 1024;          // threads per CTA
 static const int GCH = 4;            // nodes per thread and chunk of a level
 static const int GMAXV = 1024;       // most vectors in a group
 
 // sum_{i<L} f(v, i) for every vector v of the group, in canon_sum's order (tomography.cu): partial[i] = f(i) +
 // f(i + L/2), then partial[i] += partial[i + s] for s = L/4, L/8, ..., 1.  Partials of vector v at scr + v * stride
 // (L/2 doubles).  Result in out[v].
-template <class F>
-__device__ __forceinline__ void group_canon_sum(F f, double* scr, size_t stride, double* out, int Gc, int L, int logL,
+template <int GT, class F>
+__device__ __forceinline__ void group_canon_sum(F f, double* scr, int stride, double* out, int Gc, int L, int logL,
                                                 int tid) {
     const int h = L >> 1, logh = logL - 1;
-    for (long long q = tid; q < (long long)Gc * h; q += GT) {
-        const int v = (int)(q >> logh), i = (int)(q & (h - 1));
+    for (int q = tid; q < Gc * h; q += GT) {
+        const int v = q >> logh, i = q & (h - 1);
         const double lo = f(v, i), hi = f(v, i + h);
-        scr[(size_t)v * stride + i] = lo + hi;
+        scr[v * stride + i] = lo + hi;
     }
     __syncthreads();
     // one warp per vector from here on: the strided halving needs only warp-level ordering
     const int lane = tid & 31, warp = tid >> 5;
     for (int v = warp; v < Gc; v += GT / 32) {
-        double* p = scr + (size_t)v * stride;
+        double* p = scr + v * stride;
         int s = h >> 1;
         for (; s >= 32; s >>= 1) {
             for (int i = lane; i < s; i += 32) p[i] += p[i + s];
@@ -54,13 +53,14 @@ __device__ __forceinline__ void group_canon_sum(F f, double* scr, size_t stride,
 }
 
 // tree[v][i] = tree[v][2i] + tree[v][2i+1], bottom-up, for every vector of the group
-__device__ __forceinline__ void group_build(double* ws, size_t wsv, int Gc, int L, int logL, int tid) {
+template <int GT>
+__device__ __forceinline__ void group_build(double* ws, int wsv, int Gc, int L, int logL, int tid) {
     for (int lev = logL - 1; lev >= 0; --lev) {
         __syncthreads();
         const int first = 1 << lev;
-        for (long long q = tid; q < (long long)Gc << lev; q += GT) {
-            const int v = (int)(q >> lev), i = first + (int)(q & (first - 1));
-            double* t = ws + (size_t)v * wsv;
+        for (int q = tid; q < Gc << lev; q += GT) {
+            const int v = q >> lev, i = first + (q & (first - 1));
+            double* t = ws + v * wsv;
             const double2 c = *reinterpret_cast<const double2*>(t + 2 * i);
             t[i] = c.x + c.y;
         }
@@ -70,23 +70,27 @@ __device__ __forceinline__ void group_build(double* ws, size_t wsv, int Gc, int 
 
 // top-down splitting of every tree of the group; tree[v][1] holds the count to split.  Counts overwrite the
 // masses in place (a node reads its two child masses right before it stores the two child counts).
-__device__ __forceinline__ void group_split(double* ws, size_t wsv, int Gc, int logL, int tid, unsigned long long seed,
+template <int GT>
+__device__ __forceinline__ void group_split(double* ws, int wsv, int Gc, int logL, int tid, unsigned long long seed,
                                             unsigned long long vec0, unsigned stream, int* list, int* ctr) {
     const int lane = tid & 31;
+    int flip = 0;                                  // two pairs of counters, used by alternate chunks
+    if (tid == 0) { ctr[0] = 0; ctr[1] = 0; ctr[2] = 0; ctr[3] = 0; }
     for (int lev = 0; lev < logL; ++lev) {
         const int first = 1 << lev;
-        const long long total = (long long)Gc << lev;
-        for (long long base = 0; base < total; base += (long long)GT * GCH) {
+        const int total = Gc << lev;
+        for (int base = 0; base < total; base += GT * GCH) {
             __syncthreads();                       // previous level / chunk complete; list free
-            if (tid == 0) { ctr[0] = 0; ctr[1] = 0; }
-            __syncthreads();
+            int* ctr_cur = ctr + 2 * flip;
+            if (tid == 0) { ctr[2 * (flip ^ 1)] = 0; ctr[2 * (flip ^ 1) + 1] = 0; }
+            flip ^= 1;
 #pragma unroll 1
             for (int c = 0; c < GCH; ++c) {
-                const long long q = base + (long long)c * GT + tid;
+                const int q = base + c * GT + tid;
                 int st = BINOM_DONE;
                 if (q < total) {
-                    const int v = (int)(q >> lev), i = first + (int)(q & (first - 1));
-                    double* t = ws + (size_t)v * wsv;
+                    const int v = q >> lev, i = first + (q & (first - 1));
+                    double* t = ws + v * wsv;
                     const double n = t[i];
                     double left = 0.0;
                     if (n > 0.0) {
@@ -101,22 +105,22 @@ __device__ __forceinline__ void group_split(double* ws, size_t wsv, int Gc, int 
                 if (m1 | m2) {
                     int b1 = 0, b2 = 0;
                     if (lane == 0) {
-                        if (m1) b1 = atomicAdd(&ctr[0], __popc(m1));
-                        if (m2) b2 = atomicAdd(&ctr[1], __popc(m2));
+                        if (m1) b1 = atomicAdd(&ctr_cur[0], __popc(m1));
+                        if (m2) b2 = atomicAdd(&ctr_cur[1], __popc(m2));
                     }
                     b1 = __shfl_sync(0xffffffffu, b1, 0);
                     b2 = __shfl_sync(0xffffffffu, b2, 0);
                     const unsigned lt = (1u << lane) - 1u;
-                    if (st == BINOM_NEEDS_BINV) list[b1 + __popc(m1 & lt)] = (int)(q - base);
-                    if (st == BINOM_NEEDS_BTRS) list[GT * GCH - 1 - (b2 + __popc(m2 & lt))] = (int)(q - base);
+                    if (st == BINOM_NEEDS_BINV) list[b1 + __popc(m1 & lt)] = q - base;
+                    if (st == BINOM_NEEDS_BTRS) list[GT * GCH - 1 - (b2 + __popc(m2 & lt))] = q - base;
                 }
             }
             __syncthreads();
-            const int nf = ctr[0], nb = ctr[1];
+            const int nf = ctr_cur[0], nb = ctr_cur[1];
             for (int j = tid; j < nf + nb; j += GT) {
-                const long long q = base + (j < nf ? list[j] : list[GT * GCH - 1 - (j - nf)]);
-                const int v = (int)(q >> lev), i = first + (int)(q & (first - 1));
-                double* t = ws + (size_t)v * wsv;
+                const int q = base + (j < nf ? list[j] : list[GT * GCH - 1 - (j - nf)]);
+                const int v = q >> lev, i = first + (q & (first - 1));
+                double* t = ws + v * wsv;
                 const double n = t[i];
                 const double2 m = *reinterpret_cast<const double2*>(t + 2 * i);
                 Philox rng(seed, vec0 + (unsigned long long)v, stream, (unsigned)i);
@@ -128,14 +132,15 @@ __device__ __forceinline__ void group_split(double* ws, size_t wsv, int Gc, int 
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(GT, 1) tomo_group_kernel(TomoGroupArgs a) {
+template <int GT>
+__global__ void __launch_bounds__(GT, 1024 / GT) tomo_group_kernel(TomoGroupArgs a) {
     __shared__ int list[GT * GCH];
-    __shared__ int ctr[2];
+    __shared__ int ctr[4];
     __shared__ double s_div[GMAXV];      // divisor of the vector (1 when its norm is within rtol 1e-2 of 1), 0 = zero vector
     __shared__ double s_aux[GMAXV];      // sminus of stage 2, then the error
     __shared__ int s_rescale;
     const int tid = threadIdx.x, L = a.L, logL = a.logL, d = a.d, G = a.G;
-    const size_t wsv = tomo_group_wsv(L);
+    const int wsv = (int)tomo_group_wsv(L);
     double* ws = a.ws + (size_t)blockIdx.x * G * wsv;
     const double N = a.N;
     const unsigned st1 = (unsigned)(2 * a.attempt), st2 = st1 + 1u;
@@ -148,14 +153,14 @@ __global__ void __launch_bounds__(GT, 1) tomo_group_kernel(TomoGroupArgs a) {
         __syncthreads();                  // the previous group is done with the shared arrays
         if (tid == 0) s_rescale = 0;
         // ---- ||V||^2 by the sum tree ----
-        for (long long q = tid; q < (long long)Gc << logL; q += GT) {
-            const int v = (int)(q >> logL), i = (int)(q & (L - 1));
-            const double x = (i < d) ? Vg[(size_t)v * d + i] : 0.0;
-            ws[(size_t)v * wsv + L + i] = x * x;
+        for (int q = tid; q < Gc << logL; q += GT) {
+            const int v = q >> logL, i = q & (L - 1);
+            const double x = (i < d) ? Vg[v * d + i] : 0.0;
+            ws[v * wsv + L + i] = x * x;
         }
-        group_build(ws, wsv, Gc, L, logL, tid);
+        group_build<GT>(ws, wsv, Gc, L, logL, tid);
         for (int v = tid; v < Gc; v += GT) {
-            const double nrm = sqrt(ws[(size_t)v * wsv + 1]);
+            const double nrm = sqrt(ws[v * wsv + 1]);
             const bool keep = fabs(nrm - 1.0) <= (1e-8 + 1e-2);      // np.isclose(nrm, 1, rtol=1e-2)
             s_div[v] = !(nrm > 0.0) ? 0.0 : (keep ? 1.0 : nrm);
             if (nrm > 0.0 && !keep) s_rescale = 1;
@@ -164,35 +169,35 @@ __global__ void __launch_bounds__(GT, 1) tomo_group_kernel(TomoGroupArgs a) {
         auto vin = [&](int v, int i) {
             const double dv = s_div[v];
             if (i >= d || dv == 0.0) return 0.0;
-            const double x = Vg[(size_t)v * d + i];
+            const double x = Vg[v * d + i];
             return dv == 1.0 ? x : x / dv;
         };
         if (s_rescale) {                  // (uniform) some vector is normalised first: its tree is rebuilt
-            for (long long q = tid; q < (long long)Gc << logL; q += GT) {
-                const int v = (int)(q >> logL), i = (int)(q & (L - 1));
+            for (int q = tid; q < Gc << logL; q += GT) {
+                const int v = q >> logL, i = q & (L - 1);
                 const double x = vin(v, i);
-                ws[(size_t)v * wsv + L + i] = x * x;
+                ws[v * wsv + L + i] = x * x;
             }
-            group_build(ws, wsv, Gc, L, logL, tid);
+            group_build<GT>(ws, wsv, Gc, L, logL, tid);
         }
 #pragma unroll 1
         for (int stage = 0; stage < 2; ++stage) {
             if (stage == 0) {
                 // ---- stage 1: N measurements over the masses x_i^2 ----
-                for (int v = tid; v < Gc; v += GT) ws[(size_t)v * wsv + 1] = (s_div[v] == 0.0) ? 0.0 : N;
+                for (int v = tid; v < Gc; v += GT) ws[v * wsv + 1] = (s_div[v] == 0.0) ? 0.0 : N;
             } else {
                 // ---- stage 2: P = sqrt(n_i / N) (parked in est), masses ((x + P)/2)^2, lump sum of ((x - P)/2)^2 ----
-                group_canon_sum([&](int v, int i) {
-                    double* t = ws + (size_t)v * wsv;
+                group_canon_sum<GT>([&](int v, int i) {
+                    double* t = ws + v * wsv;
                     const double p = sqrt(t[L + i] / N), x = vin(v, i);
-                    if (i < d) Eg[(size_t)v * d + i] = p;
+                    if (i < d) Eg[v * d + i] = p;
                     const double ap = 0.5 * (x + p), am = 0.5 * (x - p);
                     t[L + i] = ap * ap;
                     return am * am;
                 }, ws + 2 * L, wsv, s_aux, Gc, L, logL, tid);
-                group_build(ws, wsv, Gc, L, logL, tid);
+                group_build<GT>(ws, wsv, Gc, L, logL, tid);
                 for (int v = tid; v < Gc; v += GT) {
-                    double* t = ws + (size_t)v * wsv;
+                    double* t = ws + v * wsv;
                     double c = 0.0;
                     if (s_div[v] != 0.0) {
                         Philox rng(a.seed, vec0 + (unsigned long long)v, st2, 0u);
@@ -201,15 +206,15 @@ __global__ void __launch_bounds__(GT, 1) tomo_group_kernel(TomoGroupArgs a) {
                     t[1] = c;
                 }
             }
-            group_split(ws, wsv, Gc, logL, tid, a.seed, vec0, stage == 0 ? st1 : st2, list, ctr);
+            group_split<GT>(ws, wsv, Gc, logL, tid, a.seed, vec0, stage == 0 ? st1 : st2, list, ctr);
         }
         // ---- sign rule, estimate, error ----
         auto sign_and_diff = [&](int v, int i) {
             if (i >= d) return 0.0;
-            const double p = Eg[(size_t)v * d + i];
-            const double c2 = ws[(size_t)v * wsv + L + i];
+            const double p = Eg[v * d + i];
+            const double c2 = ws[v * wsv + L + i];
             const double est = (s_div[v] == 0.0) ? 0.0 : ((c2 > 0.4 * p * p * N) ? p : -p);
-            Eg[(size_t)v * d + i] = est;
+            Eg[v * d + i] = est;
             return vin(v, i) - est;
         };
         if (a.norm_inf) {
@@ -223,7 +228,7 @@ __global__ void __launch_bounds__(GT, 1) tomo_group_kernel(TomoGroupArgs a) {
             }
             __syncthreads();
         } else {
-            group_canon_sum([&](int v, int i) { const double df = sign_and_diff(v, i); return df * df; },
+            group_canon_sum<GT>([&](int v, int i) { const double df = sign_and_diff(v, i); return df * df; },
                             ws + 2 * L, wsv, s_aux, Gc, L, logL, tid);
         }
         for (int v = tid; v < Gc; v += GT) {
@@ -238,18 +243,21 @@ size_t tomo_group_ws_bytes(int L, int G, int ctas) { return (size_t)ctas * G * t
 
 // vectors per group: enough to fill 1024 threads from the upper levels on (G * L ~ 32768), not more than
 // leaves every SM a group, at most GMAXV
-int tomo_group_size(long long B, int L, int sms) {
+int tomo_group_size(long long B, int L, int sms, int threads) {
     long long g = 32768 / L;
     if (g < 8) g = 8;
-    long long per_sm = (B + sms - 1) / sms;
-    if (g > per_sm) g = per_sm;
+    const int per = 1024 / threads;               // CTAs per SM
+    long long per_cta = (B + (long long)sms * per - 1) / ((long long)sms * per);
+    if (g > per_cta) g = per_cta;
     if (g > GMAXV) g = GMAXV;
     if (g < 1) g = 1;
     return (int)g;
 }
 
-int tomo_group_launch(TomoGroupArgs a, int ctas, cudaStream_t stream) {
-    tomo_group_kernel<<<ctas, GT, 0, stream>>>(a);
+int tomo_group_launch(TomoGroupArgs a, int ctas, int threads, cudaStream_t stream) {
+    if (threads == 256) tomo_group_kernel<256><<<ctas, 256, 0, stream>>>(a);
+    else if (threads == 512) tomo_group_kernel<512><<<ctas, 512, 0, stream>>>(a);
+    else tomo_group_kernel<1024><<<ctas, 1024, 0, stream>>>(a);
     SQ_LAUNCH_CHECK("tomo_group_kernel");
     return SQ_OK;
 }

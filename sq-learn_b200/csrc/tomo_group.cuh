@@ -22,7 +22,7 @@ struct TomoGroupArgs {
 // doubles of workspace per vector: the sum tree / counts [2L] and the partial sums of the ordered reductions [L/2]
 __host__ __device__ inline size_t tomo_group_wsv(int L) { return (size_t)2 * L + (L / 2 < 2 ? 2 : L / 2); }
 size_t tomo_group_ws_bytes(int L, int G, int ctas);
-int tomo_group_size(long long B, int L, int sms);
-int tomo_group_launch(TomoGroupArgs a, int ctas, cudaStream_t stream);
+int tomo_group_size(long long B, int L, int sms, int threads);
+int tomo_group_launch(TomoGroupArgs a, int ctas, int threads, cudaStream_t stream);
 
 }  // namespace sq

@@ -41,6 +41,8 @@ struct TomoArgs {
     int norm_inf;         // 0: L2, 1: L-infinity
     int stop;             // stop at the first attempt with err <= delta
     double direct_factor; // attempts with N <= direct_factor * clamp(L, 32, 512) draw their samples one by one
+    int cache;            // keep the normalised input and its stage-1 CDF in shared memory across attempts
+    int early;            // give up an attempt after stage 1 when no choice of signs could meet delta
     double delta;
     unsigned long long seed;
     unsigned long long vec_offset;  // global id of vector 0 (sharding / call offset)
@@ -269,8 +271,11 @@ __device__ __forceinline__ void sample_direct(const double* cdf, int L, int logL
 }
 
 // shared memory of one vector, in doubles: P [L] | A [2L] (sum tree, then counts in place; CDF, int counts
-// and reduction scratch on the direct path) | tot [L/32 + 1 <= 160] | split_tree's node list
-__host__ __device__ inline size_t tomo_smem_doubles(int L) { return (size_t)3 * L + 160 + split_scratch_doubles(L); }
+// and reduction scratch on the direct path) | tot [L/32 + 1 <= 160] | split_tree's node list | with `cache`:
+// X [L] (the normalised input) and C1 [L] (its stage-1 CDF), which do not change from attempt to attempt
+__host__ __device__ inline size_t tomo_smem_doubles(int L, int cache) {
+    return (size_t)3 * L + 160 + split_scratch_doubles(L) + (cache ? 2 * (size_t)L : 0);
+}
 
 template <int MAXT, int MINB>
 __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
@@ -280,8 +285,11 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
     double* A = P + L;          // [2L]
     double* tot = A + 2 * L;    // [160]
     const SplitScratch sc = split_scratch_at(tot + 160, L);
+    double* X = tot + 160 + split_scratch_doubles(L);   // [L], only with a.cache
+    double* C1 = X + L;                                 // [L], only with a.cache
     double* mass = A;
     double* cnt = A;
+    const bool cache = a.cache != 0;
 
     const long long b = blockIdx.x;
     const unsigned long long vec = a.vec_offset + (unsigned long long)b;
@@ -300,8 +308,29 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
         if (tid == 0 && a.spec != 1) { a.n_used[b] = 0.0; a.err[b] = 0.0; if (a.attempts) a.attempts[b] = 0; }
         return;
     }
-    auto vin = [&](int i) { return (i < d) ? (keep ? Vg[i] : Vg[i] / nrm) : 0.0; };
+    auto vin_g = [&](int i) { return (i < d) ? (keep ? Vg[i] : Vg[i] / nrm) : 0.0; };
     __syncthreads();
+    double xmax2 = 0.0;
+    if (cache) {
+        for (int i = tid; i < L; i += T) { const double x = vin_g(i); X[i] = x; C1[i] = x * x; xmax2 = fmax(xmax2, x * x); }
+        __syncthreads();
+        canon_scan(C1, L, tot, tid, T);                            // stage-1 CDF, the same for every attempt
+    }
+    auto vin = [&](int i) { return cache ? X[i] : vin_g(i); };
+    // An attempt whose stage-1 magnitudes P already miss delta for EVERY choice of signs, sum_i (|x_i| - P_i)^2 >
+    // delta^2 (or max_i ||x_i| - P_i| > delta), fails whatever stage 2 draws; its stage 2 is skipped.  Attempts
+    // are independent fresh draws, so this does not touch the law of the attempt that is returned - nor a bit of
+    // it.  Not for the last attempt (returned even when it fails), nor when every attempt's estimate is wanted.
+    const bool early = a.early && a.stop && a.spec != 2 && a.trace == nullptr;
+    const double early_thr = (a.norm_inf ? a.delta : a.delta * a.delta) * (1.0 + 1e-9);
+    // The same before any draw: N measurements leave at least d - N components at zero, so the squared error
+    // is at least ||x||^2 - N max_i x_i^2.
+    double n_hopeless = 0.0;
+    if (early && cache && !a.norm_inf) {
+        xmax2 = block_max(xmax2, tot, tid, T);
+        n_hopeless = (C1[L - 1] - early_thr) / xmax2 * (1.0 - 1e-9);   // attempts with N < n_hopeless cannot succeed
+        __syncthreads();
+    }
 
     double n_last = 0.0, err_last = 0.0;
     int n_att = 0;
@@ -320,6 +349,8 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
             if (at > s_cut) break;          // an earlier attempt already succeeded
         }
         const double N = a.sched[at];
+        const bool may_skip = early && at + 1 < a.sched_len;
+        if (may_skip && N < n_hopeless) { n_att = at + 1; continue; }
         // Few measurements: draw them one by one (N/T categorical draws per thread, log2(d) probes each)
         // instead of walking the tree, whose log2(d) dependent binomial draws cost more than that.
         // The rule depends on (N, L) only.
@@ -328,11 +359,27 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
         int* guide = reinterpret_cast<int*>(A + L + H);  // [L] ints = A[L + L/2 .. 2L), shared with the reduction scratch
         double e;
         if (direct) {
-            for (int i = tid; i < L; i += T) { double x = vin(i); A[i] = x * x; cnt_i[i] = 0; }
+            const double* cdf1 = cache ? C1 : A;
+            if (cache) {
+                for (int i = tid; i < L; i += T) cnt_i[i] = 0;
+                __syncthreads();
+            } else {
+                for (int i = tid; i < L; i += T) { double x = vin(i); A[i] = x * x; cnt_i[i] = 0; }
+                __syncthreads();
+                canon_scan(A, L, tot, tid, T);                     // stage-1 CDF in A[0..L)
+            }
+            sample_direct(cdf1, L, a.logL, cdf1[L - 1], cnt_i, guide, (long long)N, tid, T, a.seed, vec, (unsigned)(2 * at));
             __syncthreads();
-            canon_scan(A, L, tot, tid, T);                         // stage-1 CDF in A[0..L)
-            sample_direct(A, L, a.logL, A[L - 1], cnt_i, guide, (long long)N, tid, T, a.seed, vec, (unsigned)(2 * at));
-            __syncthreads();
+            if (may_skip) {
+                double lb = 0.0;
+                for (int i = tid; i < L; i += T) {
+                    const double g = fabs(vin(i)) - sqrt((double)cnt_i[i] / N);
+                    lb = a.norm_inf ? fmax(lb, fabs(g)) : lb + g * g;
+                }
+                lb = a.norm_inf ? block_max(lb, tot, tid, T) : block_sum(lb, tot, tid, T);
+                __syncthreads();
+                if (lb > early_thr) { n_att = at + 1; continue; }
+            }
             const double sminus = canon_sum([&](int i) {
                 double p = sqrt((double)cnt_i[i] / N), x = vin(i);
                 P[i] = p;
@@ -352,6 +399,16 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
             build_tree(mass, L, a.logL, tid, T);
             if (tid == 0) cnt[1] = N;
             split_tree(mass, cnt, a.logL, tid, T, a.seed, vec, (unsigned)(2 * at), 0u, sc);
+            if (may_skip) {
+                double lb = 0.0;
+                for (int i = tid; i < L; i += T) {
+                    const double g = fabs(vin(i)) - sqrt(cnt[L + i] / N);
+                    lb = a.norm_inf ? fmax(lb, fabs(g)) : lb + g * g;
+                }
+                lb = a.norm_inf ? block_max(lb, tot, tid, T) : block_sum(lb, tot, tid, T);
+                __syncthreads();
+                if (lb > early_thr) { n_att = at + 1; continue; }
+            }
             // ---- stage 2 ----
             const double sminus = canon_sum([&](int i) {
                 double p = sqrt(cnt[L + i] / N), x = vin(i);
@@ -411,8 +468,11 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
 // an attempt uses - never the law of the result.
 static double g_direct_factor = 64.0;
 static int g_many_div = 4, g_many_cap = 128;
+static int g_cache_max_L = 256;       // the fused kernel keeps input + stage-1 CDF in shared memory up to this L
+static int g_early = 1;               // skip stage 2 of attempts that cannot succeed
 static int g_group_on = 1;            // single attempts of many vectors go to the group kernel (tomo_group.cu)
 static long long g_group_min_B = 296; // ... from this many vectors on
+static int g_group_threads = 256;     // threads per CTA of the group kernel (1024 / threads CTAs per SM)
 
 static int tomo_launch(TomoArgs a, long long B, int lanes, cudaStream_t stream) {
     const int L = a.L;
@@ -421,7 +481,9 @@ static int tomo_launch(TomoArgs a, long long B, int lanes, cudaStream_t stream) 
     int threads = many ? (L / g_many_div > g_many_cap ? g_many_cap : L / g_many_div) : L;   // (128 = the widest launch of the 64-register build)
     threads = (threads + 31) & ~31;
     threads = threads < 32 ? 32 : (threads > 512 ? 512 : threads);
-    const size_t smem = tomo_smem_doubles(L) * sizeof(double);
+    a.cache = (L <= g_cache_max_L && a.sched_len > 1) ? 1 : 0;
+    a.early = g_early;
+    const size_t smem = tomo_smem_doubles(L, a.cache) * sizeof(double);
     // up to 128 threads per vector: capped at 64 registers (a few spilled words), 8+ CTAs per SM - the kernel is
     // bound by dependent FP64 latency, and 64 registers measured best against 48, 80, 96 and 126
     if (threads <= 128) {
@@ -627,6 +689,10 @@ extern "C" int sq_tomography_tune(int what, double value) {
         case 1: SQ_REQUIRE(value >= 1.0 && value <= 64.0, "sq_tomography_tune: divisor in [1, 64]"); g_many_div = (int)value; break;
         case 2: SQ_REQUIRE(value >= 32.0 && value <= 128.0, "sq_tomography_tune: cap in [32, 128]"); g_many_cap = (int)value; break;
         case 3: g_group_on = value != 0.0; break;
+        case 6: g_cache_max_L = (int)value; break;
+        case 7: g_early = value != 0.0; break;
+        case 5: SQ_REQUIRE(value == 256.0 || value == 512.0 || value == 1024.0, "sq_tomography_tune: 256, 512 or 1024 threads");
+                g_group_threads = (int)value; break;
         case 4: SQ_REQUIRE(value >= 1.0, "sq_tomography_tune: minimum batch >= 1"); g_group_min_B = (long long)value; break;
         default: SQ_REQUIRE(false, "sq_tomography_tune: unknown tunable %d", what);
     }
@@ -698,9 +764,9 @@ static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, 
 // group kernel (d <= the fused limit): geometry for a batch of B vectors of L leaves
 static void tomo_group_geometry(long long B, int L, int* G, int* ctas) {
     const int sms = device_sm_count();
-    *G = tomo_group_size(B, L, sms);
-    long long groups = (B + *G - 1) / *G;
-    *ctas = (int)(groups < sms ? groups : sms);
+    *G = tomo_group_size(B, L, sms, g_group_threads);
+    const long long groups = (B + *G - 1) / *G, most = (long long)sms * (1024 / g_group_threads);
+    *ctas = (int)(groups < most ? groups : most);
 }
 static void tomo_leaves(int d, int* L, int* logL) {
     int l = 2, lg = 1;
@@ -793,7 +859,7 @@ extern "C" int sq_tomography_batched_ws(const double* V, long long B, int d, dou
                 g.V = V; g.est = est; g.n_used = n_used; g.err = err; g.ws = (double*)ws; g.B = B; g.d = d; g.L = L;
                 g.logL = logL; g.G = G; g.norm_inf = norm_inf; g.attempt = sched_len - 1; g.N = N; g.seed = seed;
                 g.vec_offset = vec_offset;
-                return tomo_group_launch(g, ctas, stream);
+                return tomo_group_launch(g, ctas, g_group_threads, stream);
             }
         }
         return sq_tomography_batched(V, B, d, delta, norm_inf, stop, sched_host, sched_len, seed, vec_offset, est,

@@ -377,3 +377,68 @@ def test_speculative_lanes_equal_the_in_order_search(cuda):
             assert np.array_equal(est.cpu().numpy(), want[0])
             assert np.array_equal(n_used.cpu().numpy(), want[1])
             assert np.array_equal(err.cpu().numpy(), want[2])
+
+
+@pytest.mark.parametrize("B,d,delta,norm_inf", [(700, 1000, 0.1, 0), (5000, 128, 0.25, 0), (400, 4096, 0.2, 0),
+                                                (3000, 61, 0.1, 0), (900, 300, 0.02, 1), (600, 2, 0.05, 0),
+                                                (5000, 3, 0.02, 0), (1200, 33, 0.1, 1)])
+def test_group_kernel_equals_the_fused_kernel(cuda, B, d, delta, norm_inf):
+    """a single attempt of many vectors runs in the group kernel (sq_tomography_batched_ws with a workspace):
+    same draws, same order of additions, so estimate / N / error equal the per-vector kernel's bit for bit -
+    with vectors that are renormalised, a zero vector, a ragged last group and a non-zero stream offset"""
+    import gpu_util as G
+    from oracle import quantum_utility as qu
+    from sqlearn import _cabi
+    rs = np.random.RandomState(B + d)
+    V = rs.uniform(-1, 1, (B, d))
+    V /= np.linalg.norm(V, axis=1, keepdims=True)
+    V[1] *= 3.0
+    V[2] = 0.0
+    V[B - 1] *= 0.2
+    N = qu.tomography_N(d, delta, "inf" if norm_inf else "L2")
+    assert _cabi.lib.sq_tomography_workspace_bytes(B, d) > 0            # the group path is taken
+    got = _big(V, delta, [float(N)], norm_inf=norm_inf, seed=91, vec_offset=12345)
+    want = G.tomography(V, delta, [float(N)], norm_inf=norm_inf, seed=91, vec_offset=12345)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    assert (got[0][2] == 0).all() and got[1][2] == 0
+    # a schedule without the stop rule returns its last attempt, keyed by that attempt's index
+    sched = qu.schedule(N).astype(float)[-3:]
+    got = _big(V, delta, sched, norm_inf=norm_inf, stop=0, seed=92)
+    want = G.tomography(V, delta, sched, norm_inf=norm_inf, stop=0, seed=92)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("d,delta,norm_inf", [(128, 0.25, 0), (61, 0.1, 0), (1000, 0.3, 0), (300, 0.1, 1), (16, 0.3, 0)])
+def test_skipping_hopeless_attempts_changes_nothing(cuda, d, delta, norm_inf):
+    """incremental mode gives up an attempt after stage 1 when no choice of signs could meet delta, and does not
+    start attempts whose N leaves too many components at zero; switched off (sq_tomography_tune 7), every
+    attempt runs both stages - the returned attempt, its N and its error must be the same bits"""
+    import gpu_util as G
+    from oracle import quantum_utility as qu
+    from sqlearn import _cabi
+    rs = np.random.RandomState(d)
+    B = 300
+    V = rs.uniform(-1, 1, (B, d)) * rs.uniform(0.3, 3.0, (B, 1))
+    V[7] = 0.0
+    sched = qu.schedule(max(qu.tomography_N(d, delta, "inf" if norm_inf else "L2"), 50)).astype(float)
+    try:
+        _cabi.check(_cabi.lib.sq_tomography_tune(7, 0.0), "tune")
+        _cabi.check(_cabi.lib.sq_tomography_tune(6, 0.0), "tune")
+        plain = G.tomography(V, delta, sched, norm_inf=norm_inf, stop=1, seed=55, vec_offset=9)
+    finally:
+        _cabi.check(_cabi.lib.sq_tomography_tune(7, 1.0), "tune")
+        _cabi.check(_cabi.lib.sq_tomography_tune(6, 256.0), "tune")
+    fast = G.tomography(V, delta, sched, norm_inf=norm_inf, stop=1, seed=55, vec_offset=9)
+    for a, b in zip(fast, plain):
+        assert np.array_equal(a, b)
+    assert (fast[2] <= delta).all()
+    # the trace of every attempt is still complete (nothing is skipped when it is asked for)
+    est, n_used, err, tr, att = G.tomography(V[:5], delta, sched, norm_inf=norm_inf, stop=1, seed=55, vec_offset=9,
+                                             trace=True)
+    assert np.array_equal(est, fast[0][:5])
+    for b in range(5):
+        a = int(att[b])
+        errs = np.linalg.norm(V[b] / np.linalg.norm(V[b]) - tr[b, :a], ord=np.inf if norm_inf else 2, axis=1)
+        assert (errs[:-1] > delta).all() and errs[-1] <= delta
