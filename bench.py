@@ -1,14 +1,16 @@
 #!/usr/bin/env python
-"""Benchmark of the q-means hot path (BASELINE.json config 4: 10M x 128, k = 256).
+"""Benchmark of the q-means hot path (BASELINE.json config 4: 10M x 128, k = 256) and of batched
+vector-state tomography (config 5).
 
   python bench.py --gpus N --steps K --warmup W          # this repo (CUDA, sm_100a)
   python bench.py --impl reference --steps K --warmup W  # CPU arm: oracle port of the reference
 
-A step = one Lloyd iteration of qMeans_ (E-step with the delta-window noise
-model, M-step, all-reduce of centroid sums, default-mode centroid tomography
-at delta/2, centre shift, read-back of inertia and shift).  The 10M rows are
-sharded over the N ranks (strong scaling); inputs are resident in HBM for
-`value`; `e2e` goes through the public API (qMeans_.fit on host arrays).
+A step = one Lloyd iteration of qMeans_ (E-step with the delta-window noise model, M-step, all-reduce of the
+centroid sums, default-mode centroid tomography at delta/2, centre shift, read-back of inertia and shift).
+The 10M rows are ONE fixed dataset, rank r of G holding rows [r n/G, (r+1) n/G) of it (strong scaling);
+inputs are resident in HBM for `value`; `e2e` goes through the public API (qMeans_.fit on a pageable host
+array, what an sklearn caller holds).  The tomography half of BASELINE.json's metric is under
+`roofline.kernels` (the config-5 grid, every N) with its CPU figure under `cpu_baseline.tomography`.
 Prints ONE JSON line on rank 0.
 """
 import argparse
@@ -28,6 +30,7 @@ for p in (ROOT, os.path.join(ROOT, "sq-learn_b200")):
 
 N_ROWS, DIM, K_CLUSTERS, DELTA = 10_000_000, 128, 256, 0.5
 METRIC, UNIT = "qmeans_lloyd_iterations_per_s_10Mx128_k256", "iter/s"
+BLOCK_ROWS = 1 << 20          # the dataset is generated in blocks of this many rows, keyed by block id
 
 
 def parse():
@@ -40,7 +43,11 @@ def parse():
     ap.add_argument("--rows", type=int, default=N_ROWS, help="total rows (default: the BASELINE config)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--no-extra", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the tomography grid, the other E-step modes and qPCA")
+    ap.add_argument("--tomo-budget", type=float, default=75.0, help="seconds of wall clock for the tomography grid")
+    ap.add_argument("--tomo-full", action="store_true", help="also the grid points left out by default (B*d > 1e8)")
+    ap.add_argument("--fit300", action="store_true", help="also time a fit of 300 iterations (the reference's max_iter)")
+    ap.add_argument("--csv", default=None, help="config 3: q-means k=15 on this CSV (standardised), delta 0.1..1.0")
     ap.add_argument("--cpu-rows", type=int, default=20000)
     return ap.parse_args()
 
@@ -87,43 +94,55 @@ class ClockSampler:
 
 # ----------------------------------------------------------------------------- data
 def make_shard(rows, rank, world, device):
-    """Blobs: 256 centres ~ N(0, 4^2 I), unit noise, seed 1234.  Generated
-    on the device in chunks; rank r holds the contiguous rows [r*n/G, (r+1)*n/G)."""
+    """Blobs: 256 centres ~ N(0, 4^2 I), unit noise, generated on the device.  The data
+    set is a function of the ROW INDEX alone: block b = rows [b 2^20, (b+1) 2^20) comes from a generator
+    seeded with (1234, b), and rank r holds the contiguous rows [r n/G, (r+1) n/G) - so 1, 2, 4 and 8 GPUs
+    cluster the same 10M rows."""
     import torch
     g = torch.Generator(device=device)
     g.manual_seed(1234)
     centres = torch.randn((K_CLUSTERS, DIM), generator=g, device=device, dtype=torch.float64) * 4.0
     lo = rows * rank // world
     hi = rows * (rank + 1) // world
-    n = hi - lo
-    X = torch.empty((n, DIM), dtype=torch.float64, device=device)
-    g.manual_seed(1234 + 7919 * (rank + 1))
-    step = 1 << 20
-    for a in range(0, n, step):
-        b = min(n, a + step)
-        lab = torch.randint(0, K_CLUSTERS, (b - a,), generator=g, device=device)
-        X[a:b] = centres[lab]
-        X[a:b] += torch.randn((b - a, DIM), generator=g, device=device, dtype=torch.float64)
+    X = torch.empty((hi - lo, DIM), dtype=torch.float64, device=device)
+    for blk in range(lo // BLOCK_ROWS, (hi + BLOCK_ROWS - 1) // BLOCK_ROWS):
+        b0, b1 = blk * BLOCK_ROWS, min(rows, (blk + 1) * BLOCK_ROWS)
+        g.manual_seed(1234 + 7919 * (blk + 1))
+        lab = torch.randint(0, K_CLUSTERS, (b1 - b0,), generator=g, device=device)
+        Xb = centres[lab]
+        Xb += torch.randn((b1 - b0, DIM), generator=g, device=device, dtype=torch.float64)
+        a, b = max(lo, b0), min(hi, b1)
+        X[a - lo:b - lo] = Xb[a - b0:b - b0]
+        del Xb, lab
     return X
 
 
 def measure_dgemm_peak(device):
-    """fp64 tensor-core denominator: cuBLAS DGEMM 8192^3, best of 5 (MEASURED_PEAKS.json has no
-    fp64 entry; same protocol as its bf16 line)."""
+    """fp64 tensor-core denominators: cuBLAS DGEMM 8192^3, best of 10 (burst) and back to back for 4 s
+    (sustained) - MEASURED_PEAKS.json has no fp64 entry; same protocol as its bf16 lines."""
     import torch
     n = 8192
     a = torch.randn((n, n), dtype=torch.float64, device=device)
     b = torch.randn((n, n), dtype=torch.float64, device=device)
+    flop = 2.0 * n ** 3
     best = 0.0
-    for _ in range(6):
+    for _ in range(10):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         torch.matmul(a, b)
         e1.record()
         torch.cuda.synchronize()
-        best = max(best, 2.0 * n ** 3 / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+        best = max(best, flop / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    reps = max(8, int(4.0 / (flop / (best * 1e12))))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        torch.matmul(a, b)
+    e1.record()
+    torch.cuda.synchronize()
+    sustained = reps * flop / (e0.elapsed_time(e1) * 1e-3) / 1e12
     del a, b
-    return best
+    return best, sustained
 
 
 # ----------------------------------------------------------------------------- CPU arm
@@ -162,6 +181,32 @@ def cpu_iteration_rate(cpu_rows, steps, warmup, mode, total_rows=N_ROWS):
             "host_cpus": os.cpu_count()}
 
 
+def cpu_tomography(budget_s=12.0):
+    """The oracle's tomography (oracle/quantum_utility.py: the reference's algorithm with the O(N) sampling
+    of RandomState.choice replaced by numpy's multinomial, so it flatters the CPU) on a few grid shapes, one
+    core, timed per vector."""
+    from oracle import quantum_utility as oqu
+    rng = np.random.default_rng(7)
+    out = []
+    t_all = time.perf_counter()
+    for d, delta, norm, inc in [(128, 0.25, "L2", True), (1000, 0.1, "L2", False), (1000, 0.1, "L2", True),
+                                (1000, 0.1, "inf", True), (10000, 0.1, "L2", False), (100000, 0.5, "L2", False)]:
+        v = rng.uniform(-1, 1, d)
+        v /= np.linalg.norm(v)
+        n, t0 = 0, time.perf_counter()
+        while n < 200 and time.perf_counter() - t0 < budget_s / 6:
+            oqu.real_tomography(v, delta=delta, norm=norm, incremental_measure=inc, rng=rng)
+            n += 1
+        dt = (time.perf_counter() - t0) / n
+        out.append({"d": d, "delta": delta, "norm": norm, "mode": "incremental+stop" if inc else "single-shot",
+                    "s_per_vector": dt, "vectors_per_s": 1.0 / dt, "vectors_timed": n})
+        if time.perf_counter() - t_all > budget_s:
+            break
+    return {"kind": "port", "cores": 1, "points": out,
+            "sample": "oracle port, one core, up to 200 vectors or %.0f s per shape; the reference itself "
+                      "(O(N) RandomState.choice + Counter) measured in the build container: BASELINE.md" % (budget_s / 6)}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -184,6 +229,30 @@ def run_reference_arm(args):
 
 
 # ----------------------------------------------------------------------------- GPU arm
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)
+    except Exception:
+        return {"hbm_gbs": 6650.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def _timed(torch, fn, reps):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+class Ctx:
+    pass
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -205,11 +274,21 @@ def run_b200(args):
             os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=device)
     assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
+    c = Ctx()
+    c.torch, c.dist, c.Q, c.cabi, c.D, c.world, c.rank, c.device, c.args = torch, dist, Q, _cabi, D, world, rank, device, args
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+    c.barrier = barrier
+
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], dtype=torch.float64, device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+    c.max_over_ranks = max_over_ranks
 
     mode = args.mode
     delta = 0.0 if mode == "exact" else DELTA
@@ -222,7 +301,8 @@ def run_b200(args):
     if world > 1:
         Q._sync_state()
     eng = QMeansEngine(X, K_CLUSTERS)
-    # centre the data as fit() does, then take the initial centres from rank 0's rows
+    c.eng = eng
+    # centre the data as fit() does, then take the initial centres from the first rows of the data set
     csum = eng.col_sums()
     if world > 1:
         dist.all_reduce(csum)
@@ -231,15 +311,17 @@ def run_b200(args):
     eng.refresh_norms()
     g = torch.Generator(device="cpu")
     g.manual_seed(1234)
-    idx = torch.randperm(min(n_local, 1 << 22), generator=g)[:K_CLUSTERS].to(device)
-    centers = X[idx].clone()
+    idx = torch.randperm(min(args.rows // 8, 1 << 20), generator=g)[:K_CLUSTERS].to(device)   # rows rank 0 holds at any N <= 8
+    centers0 = X[idx].clone() if rank == 0 else torch.empty((K_CLUSTERS, DIM), dtype=torch.float64, device=device)
     if world > 1:
-        dist.broadcast(centers, src=0)
+        dist.broadcast(centers0, src=0)
+    centers = centers0.clone()
     c_old, c_new = torch.empty_like(centers), torch.empty_like(centers)
     host = torch.empty((2,), dtype=torch.float64).pin_memory()
 
-    def step():
-        return D._lloyd_iteration(eng, centers, c_old, c_new, host, delta, inter, True, True, None, tde)
+    def make_step(d_, inter_, tde_):
+        return lambda: D._lloyd_iteration(eng, centers, c_old, c_new, host, d_, inter_, True, True, None, tde_)
+    step = make_step(delta, inter, tde)
 
     for _ in range(args.warmup):
         step()
@@ -252,13 +334,9 @@ def run_b200(args):
             inertia, shift = step()
         e1.record()
         barrier()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms.item())
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
     launches = eng.launches - l0
-    # tomography launches are made outside the engine
-    launches += args.steps if inter else 0
+    launches += D.TOMO_LAUNCHES_PER_ITER * args.steps if inter else 0    # tomography launches are made outside the engine
     value = args.steps / (ms_total * 1e-3)
 
     # ---- roofline leg: the E-step kernel alone, CUDA events inside the C ABI ----
@@ -270,7 +348,7 @@ def run_b200(args):
     _cabi.lib.sq_profile_assign(0, _cabi.ctypes.byref(tot), _cabi.ctypes.byref(cnt))
     k_ms = tot.value / max(cnt.value, 1)
     flops = 2.0 * n_local * K_CLUSTERS * DIM
-    peak = measure_dgemm_peak(device) if rank == 0 else 0.0
+    peak, peak_sustained = measure_dgemm_peak(device) if rank == 0 else (0.0, 0.0)
     achieved = flops / (k_ms * 1e-3) / 1e12
     traffic, traffic_src = None, None
     try:
@@ -280,13 +358,22 @@ def run_b200(args):
         traffic_src = tj["source"]
     except Exception:
         pass
+    peaks = load_peaks()
+    step_tflops = flops * world / (ms_total / args.steps * 1e-3) / 1e12 / world
     roofline = {"bound": "tensor", "kernel": "qmeans_assign_kernel (fp64 DMMA.8x8x4)", "achieved": achieved,
                 "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                 "traffic_source": traffic_src,
                 "kernel_ms": k_ms, "algorithmic_flops_per_launch": flops,
                 "algorithmic_bytes_per_launch": 8.0 * n_local * DIM + 4.0 * n_local,
-                "peak_source": "cuBLAS DGEMM 8192^3 fp64 measured in this run (MEASURED_PEAKS.json has no fp64 entry)",
-                "hbm_fraction": (8.0 * n_local * DIM + 4.0 * n_local) / (k_ms * 1e-3) / 1e9 / load_peaks()["hbm_gbs"]}
+                "peak_source": "cuBLAS DGEMM 8192^3 fp64 measured in this run, best of 10 (MEASURED_PEAKS.json has no "
+                               "fp64 entry); the kernel is timed alone, so the burst figure is its denominator",
+                "peak_sustained": peak_sustained,
+                "whole_step": {"tflops_per_gpu": step_tflops,
+                               "frac_of_sustained_peak": step_tflops / peak_sustained if peak_sustained else None,
+                               "note": "2 n k d flop of the E-step over the whole Lloyd step (M-step, tomography, "
+                                       "collectives included), against DGEMM back to back for 4 s"},
+                "hbm_fraction": (8.0 * n_local * DIM + 4.0 * n_local) / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                "kernels": []}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
@@ -295,86 +382,205 @@ def run_b200(args):
                                    "%s E-step, M-step, centroid tomography (incremental+stop, delta/2)"
                                    % (args.rows, DIM, world, K_CLUSTERS, DELTA, mode),
                        "rows_per_gpu": n_local, "mode": mode,
+                       "dataset": "one fixed data set of %d rows, generated per 2^20-row block from the block id; "
+                                  "rank r holds rows [r n/G, (r+1) n/G)" % args.rows,
                        "l2": "inputs (%.2f GB per GPU) exceed the 126 MB L2; no flush needed" % (n_local * DIM * 8 / 1e9),
                        "last_inertia": inertia, "last_shift": shift},
             "clocks": clk.summary(), "gpu_launches": launches, "roofline": roofline}
 
-    # ---- extra, rank 0 at N=1: other E-step modes and the tomography sweep ----
-    if not args.no_extra and world == 1:
-        line["extra"] = extra_measurements(eng, centers, D, Q, _cabi, torch)
-    # ---- e2e through the public API: qMeans_.fit on pinned host arrays ----
+    # ---- the same data at every N: a short noiseless run whose result must not depend on N ----
+    line["config"]["invariance"] = invariance_check(c, centers0)
+    # ---- the other E-step modes as real timed steps, the tomography grid (config 5), qPCA (config 2) ----
+    if not args.no_extra:
+        roofline["kernels"] += other_mode_steps(c, make_step, centers, centers0, flops, peak_sustained)
+        roofline["kernels"] += tomography_grid(c, peaks)
+        if world == 1:
+            line["extra"] = extra_measurements(c, centers)
+    # ---- e2e through the public API: qMeans_.fit on host arrays ----
     if not args.no_e2e:
         try:
-            line["e2e"] = e2e_fit(args, X, mean, centers, eng, qMeans_, Q, torch, dist, world, device)
-        except Exception as exc:      # e.g. the host cannot pin a copy of the shard
+            line["e2e"] = e2e_fit(c, X, mean, centers0, qMeans_)
+        except Exception as exc:      # e.g. the host cannot hold a copy of the shard
             line["e2e"] = {"value": None, "unit": UNIT, "error": "%s: %s" % (type(exc).__name__, exc)}
+    if args.csv and rank == 0 and world == 1:
+        line["config3_csv"] = config3_csv(c, args.csv, qMeans_)
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_iteration_rate(args.cpu_rows, 2, 1, mode, args.rows)
+        line["cpu_baseline"]["tomography"] = cpu_tomography()
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
 
 
-def load_peaks():
-    try:
-        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return json.load(f)
-    except Exception:
-        return {"hbm_gbs": 6650.0, "source": "fallback"}
+def invariance_check(c, centers0):
+    """Three noiseless Lloyd iterations from the common initial centres: inertia and a position-weighted
+    checksum of all labels.  Identical at N = 1, 2, 4, 8 (labels bit for bit; the inertia up to the order of
+    the cross-rank sums)."""
+    torch, D, eng = c.torch, c.D, c.eng
+    cen = centers0.clone()
+    c_old, c_new = torch.empty_like(cen), torch.empty_like(cen)
+    host = torch.empty((2,), dtype=torch.float64).pin_memory()
+    for _ in range(3):
+        inertia, _ = D._lloyd_iteration(eng, cen, c_old, c_new, host, 0.0, False, True, True, None, True)
+    D._labels_inertia(eng, cen, delta=0.0, pool=None, true_distance_estimate=True)
+    idx = torch.arange(eng.row0, eng.row0 + eng.n, device=c.device, dtype=torch.int64)
+    w = (idx * 2654435761 + 12345) & 0x7FFFFFFF
+    crc = ((eng.labels.to(torch.int64) + 1) * w).sum().reshape(1)
+    red = eng.inertia.clone()
+    if c.world > 1:
+        c.dist.all_reduce(crc)
+        c.dist.all_reduce(red)
+    return {"inertia_noiseless_3iter": inertia, "inertia_final_estep": float(red.item()),
+            "labels_crc": int(crc.item()) & 0xFFFFFFFFFFFFFFFF,
+            "what": "sum_i (label_i + 1) * ((i * 2654435761 + 12345) mod 2^31) over all rows i, mod 2^64"}
 
 
-def _timed(torch, fn, reps):
-    fn()
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(reps):
-        fn()
-    e1.record()
-    torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / reps
+def other_mode_steps(c, make_step, centers, centers0, flops, peak_sustained):
+    """One Lloyd step in each of the E-step modes the headline does not use, timed as real steps
+    (E-step + M-step + all-reduce + centroid tomography + read-back), max over ranks."""
+    torch, args = c.torch, c.args
+    out = []
+    for name, (delta, inter, tde, reps) in {"ipe": (DELTA, True, True, 3), "exact": (0.0, False, True, 3),
+                                             "window": (DELTA, True, False, 3)}.items():
+        if name == args.mode:
+            continue
+        centers.copy_(centers0)
+        st = make_step(delta, inter, tde)
+        st()
+        st()
+        c.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            st()
+        e1.record()
+        c.barrier()
+        ms = c.max_over_ranks(e0.elapsed_time(e1)) / reps
+        rec = {"kernel": "Lloyd step, %s E-step%s" % (name, " (the reference's default, true_distance_estimate=True)"
+                                                      if name == "ipe" else ""),
+               "shape": {"rows": args.rows, "d": DIM, "k": K_CLUSTERS, "gpus": c.world}, "ms": ms,
+               "lloyd_iterations_per_s": 1e3 / ms, "steps_timed": reps}
+        if name == "ipe":
+            pairs = float(args.rows) * K_CLUSTERS
+            rec["ipe_pairs_per_s"] = pairs / (ms * 1e-3)
+            rec["reference_draws_per_s"] = 13.0 * pairs / (ms * 1e-3)
+            rec["bound"] = "fp64 ALU / special functions (13 amplitude-estimation draws per pair, sampled as one median)"
+        else:
+            rec["bound"] = "tensor"
+            tf = flops / (ms * 1e-3) / 1e12
+            rec["achieved_TFLOPs_per_gpu"] = tf
+            rec["frac_of_sustained_peak"] = tf / peak_sustained if peak_sustained else None
+        out.append(rec)
+    centers.copy_(centers0)
+    return out
 
 
-def extra_measurements(eng, centers, D, Q, _cabi, torch):
-    """Per-phase device times of one Lloyd iteration and the batched-tomography sweep
-    (BASELINE.json config 5); explanatory numbers, not the headline."""
-    from sqlearn.QuantumUtility import Utility as U
+def tomography_grid(c, peaks):
+    """BASELINE.json config 5: d in {1e3, 1e4, 1e5, 1e6} x delta in {0.01, 0.05, 0.1, 0.5} x B in {1, 64, 4096}
+    x {L2, inf} x {single-shot, incremental+stop}; vectors uniform(-1, 1) normalised, seed 1234.
+    With several GPUs the vectors of a batch are dealt to the ranks (B >= G) and a single long vector goes
+    through tomography_sharded; the time is the max over ranks.  Roofline: 16 B d algorithmic bytes (read the
+    input once, write the estimate once) against the measured HBM copy bandwidth."""
+    torch, U, args = c.torch, c.Q, c.args
+    world, rank = c.world, c.rank
+    hbm = peaks["hbm_gbs"]
+    out, t_start = [], time.perf_counter()
+    g = torch.Generator(device=c.device)
+    fused = c.cabi.lib.sq_tomography_max_fused_dim()
+    budget_hit = False
+    order = [(d, B) for d in (1000, 10000, 100000, 1000000) for B in (4096, 64, 1)]
+    for d, B in order:
+        if B * d > 1e8 and not args.tomo_full:
+            out.append({"kernel": "tomography", "shape": {"B": B, "d": d}, "skipped":
+                        "16 B d = %.1f GB fits, but the point takes seconds; run with --tomo-full" % (16.0 * B * d / 1e9)})
+            continue
+        share = B >= world                                  # vectors dealt by vector
+        b_loc = (B * (rank + 1)) // world - (B * rank) // world if share else B
+        g.manual_seed(1234 + d + B)
+        V = torch.rand((max(b_loc, 1), d), generator=g, device=c.device, dtype=torch.float64) * 2 - 1
+        V /= V.norm(dim=1, keepdim=True)
+        for norm in ("L2", "inf"):
+            for inc in (False, True):
+                for delta in (0.01, 0.05, 0.1, 0.5):
+                    elapsed = time.perf_counter() - t_start
+                    flag = torch.tensor([1.0 if elapsed > args.tomo_budget else 0.0], device=c.device)
+                    if world > 1:
+                        c.dist.all_reduce(flag, op=c.dist.ReduceOp.MAX)
+                    if flag.item() > 0:
+                        budget_hit = True
+                        break
+                    res = {}
+
+                    def run():
+                        if not share and world > 1 and d > fused:
+                            res["est"] = U.tomography_sharded(V, delta, None, norm, True, inc, 0)
+                            res["n"] = None
+                        elif not share and world > 1 and rank != 0:
+                            res["n"] = None             # one short vector: rank 0 alone
+                        else:
+                            r = U._tomography_device(V, delta, None, norm, True, inc, 0)
+                            res["n"] = r[1]
+                    c.barrier()
+                    t0 = time.perf_counter()
+                    run()
+                    c.barrier()
+                    first = (time.perf_counter() - t0) * 1e3
+                    cold = first > 400.0                  # a point this slow is measured once, first run
+                    if cold:
+                        ms = c.max_over_ranks(first)
+                    else:
+                        reps = 3 if first < 50 else 1
+                        c.barrier()
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record()
+                        for _ in range(reps):
+                            run()
+                        e1.record()
+                        c.barrier()
+                        ms = c.max_over_ranks(e0.elapsed_time(e1) / reps)
+                    n_used = torch.zeros(1, dtype=torch.float64, device=c.device)
+                    if res.get("n") is not None:
+                        n_used += res["n"].sum()
+                    if world > 1 and share:
+                        c.dist.all_reduce(n_used)
+                    N_full = U.tomography_num_measurements(d, delta, norm)
+                    meas = float(n_used.item()) if float(n_used.item()) > 0 else None
+                    gbps = 16.0 * B * d / (ms * 1e-3) / 1e9
+                    kern = "tomo_group_kernel" if (not inc and d <= fused and b_loc >= 296) else \
+                        ("tomo_fused_kernel" if d <= fused else "tomo_big_* (block / top kernels)")
+                    out.append({"kernel": kern, "shape": {"B": B, "d": d, "delta": delta, "norm": norm,
+                                                          "mode": "incremental+stop" if inc else "single-shot",
+                                                          "gpus": world, "N_full": N_full},
+                                "ms": ms, "bound": "hbm (nominal): 16 B d bytes", "achieved_GBps": gbps,
+                                "frac_hbm": gbps / hbm / world, "vectors_per_s": B / (ms * 1e-3),
+                                "simulated_measurements_per_s": (2.0 * meas / (ms * 1e-3)) if meas else None,
+                                "timing": "first run, wall clock" if cold else "CUDA events after one warm-up"})
+                if budget_hit:
+                    break
+            if budget_hit:
+                break
+        del V
+        if budget_hit:
+            out.append({"kernel": "tomography", "note": "grid stopped after %.0f s (--tomo-budget); the points above "
+                                                       "are complete" % args.tomo_budget})
+            break
+    return out
+
+
+def extra_measurements(c, centers):
+    """Per-phase device times of one Lloyd iteration and the config-2 qPCA phases (N = 1 only)."""
+    torch, D, eng, U = c.torch, c.D, c.eng, c.Q
     out = {}
     for name, (delta, tde) in {"exact": (0.0, True), "window": (DELTA, False), "ipe": (DELTA, True)}.items():
         out["estep_%s_ms" % name] = _timed(
             torch, lambda: D._labels_inertia(eng, centers, delta=delta, pool=None, true_distance_estimate=tde),
             2 if name == "ipe" else 3)
-    # IPE mode samples, for every (row, centroid) pair, the median of 13 amplitude-estimation outcomes (SURVEY 8(d))
-    pairs = float(eng.n) * float(eng.k)
-    out["ipe_pairs_per_s"] = pairs / (out["estep_ipe_ms"] * 1e-3)
-    out["ipe_reference_draws_per_s"] = 13.0 * pairs / (out["estep_ipe_ms"] * 1e-3)
     D._labels_inertia(eng, centers, delta=0.0, pool=None, true_distance_estimate=True)
     out["mstep_accumulate_ms"] = _timed(torch, eng.accumulate, 3)
     c2 = torch.empty_like(centers)
     eng.finalize(centers, c2)
     out["centroid_tomography_ms"] = _timed(torch, lambda: U.tomography(c2, DELTA / 2), 3)
-    # the reference's default E-step (true_distance_estimate=True) in the same iteration, from the phases above
-    out["lloyd_iterations_per_s_ipe_estep_from_phases"] = 1e3 / (
-        out["estep_ipe_ms"] + out["mstep_accumulate_ms"] + out["centroid_tomography_ms"])
-    sweep = []
-    g = torch.Generator(device=centers.device)
-    g.manual_seed(1234)
-    for B, d, delta, incremental in [(4096, 1000, 0.1, False), (4096, 1000, 0.1, True), (65536, 128, 0.25, True),
-                                     (64, 4096, 0.05, False), (70000, 61, 0.1, True), (64, 100000, 0.1, False),
-                                     (1, 1000000, 0.01, False), (1, 1000000, 0.5, True)]:
-        V = torch.rand((B, d), generator=g, device=centers.device, dtype=torch.float64) * 2 - 1
-        V /= V.norm(dim=1, keepdim=True)
-        res = {}
-
-        def run():
-            res["r"] = U._tomography_device(V, delta, None, 'L2', True, incremental, 0)
-        ms = _timed(torch, run, 2)
-        n_used = float(res["r"][1].sum().item())
-        sweep.append({"B": B, "d": d, "delta": delta, "mode": "incremental+stop" if incremental else "single-shot",
-                      "ms": ms, "vectors_per_s": B / (ms * 1e-3), "simulated_measurements_per_s": 2 * n_used / (ms * 1e-3),
-                      "algorithmic_GBps": 16.0 * B * d / (ms * 1e-3) / 1e9})
-    out["tomography_sweep"] = sweep
     out["qpca_config2"] = qpca_config2(torch)
     return out
 
@@ -394,7 +600,6 @@ def qpca_config2(torch):
                                                                                 dtype=torch.float64)
     Xh = X.cpu().numpy()
     out = {"shape": [n, d], "n_components": k}
-    # kernels alone
     G = dv.empty((d, d))
     nb = _cabi.lib.sq_gram_workspace_bytes(n, d)
     ws = dv.workspace(nb)
@@ -432,54 +637,100 @@ def qpca_config2(torch):
     return out
 
 
-def e2e_fit(args, X, mean, centers_init, eng, qMeans_, Q, torch, dist, world, device):
-    """The same iterations through the public API on HOST arrays: qMeans_.fit(X_host) with an
-    explicit init and max_iter = steps.  Timed region: H2D of X from pinned memory, the fit
-    preamble (eta, mu, condition number, centring), the Lloyd iterations, the final E-step and
-    the D2H of labels / centres."""
+def _fit_once(c, qMeans_, Xnp, init, steps, seed):
+    """One timed qMeans_.fit on a host array; returns (seconds = max over ranks of max(wall, device), estimator)."""
     import warnings
+    torch, args = c.torch, c.args
     mode = args.mode
-    X.add_(mean)                                   # back to the uncentred data the user would hold
-    Xh = torch.empty(X.shape, dtype=torch.float64, pin_memory=True)
-    Xh.copy_(X)
-    init = (centers_init + mean).cpu().numpy()
-    n_local = X.shape[0]
-    del eng
-    est = qMeans_(n_clusters=K_CLUSTERS, init=init, n_init=1, max_iter=args.steps, tol=0,
+    est = qMeans_(n_clusters=K_CLUSTERS, init=init, n_init=1, max_iter=steps, tol=0,
                   delta=0 if mode == "exact" else DELTA, algorithm='full', intermediate_error=mode != "exact",
                   true_distance_estimate=mode == "ipe", copy_x=False)
-    # one small untimed fit first: library start-up (cuSOLVER handle, module load) is not the workload
-    with warnings.catch_warnings():
-        warnings.simplefilter("ignore")
-        qMeans_(n_clusters=K_CLUSTERS, init=init, n_init=1, max_iter=1, tol=0, delta=0, algorithm='full',
-                copy_x=False).fit(Xh[:min(n_local, 200000)].numpy())
-    Q.seed(99)
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
+    c.Q.seed(seed)
+    c.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     e0.record()
     with warnings.catch_warnings():
         warnings.simplefilter("ignore")
-        est.fit(Xh.numpy())
+        est.fit(Xnp)
     e1.record()
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
-    if world > 1:
-        dist.barrier()
-    ms = torch.tensor([max(e0.elapsed_time(e1), wall * 1e3)], dtype=torch.float64, device=device)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    secs = float(ms.item()) * 1e-3
-    return {"value": est.n_iter_ / secs, "unit": UNIT,
-            "h2d_bytes_per_step": (n_local * DIM * 8 + K_CLUSTERS * DIM * 8) / est.n_iter_,
-            "d2h_bytes_per_step": (n_local * 4 + K_CLUSTERS * DIM * 8 + 16 * est.n_iter_) / est.n_iter_,
-            "api": "qMeans_(n_clusters=256, init=<array>, n_init=1, max_iter=%d, tol=0, algorithm='full', ...)"
-                   ".fit(X_host)" % args.steps,
-            "fit_seconds": secs, "n_iter": est.n_iter_, "inertia": est.inertia_,
-            "note": "one fit = H2D of the shard + preamble + n_iter Lloyd iterations + final E-step; "
-                    "bytes are totals divided by n_iter"}
+    c.barrier()
+    return c.max_over_ranks(max(e0.elapsed_time(e1), wall * 1e3)) * 1e-3, est
+
+
+def e2e_fit(c, X, mean, centers_init, qMeans_):
+    """The same iterations through the public API on HOST arrays: qMeans_.fit(X_host) with an explicit init and
+    max_iter = steps.  Timed region: H2D of X, the fit preamble (eta, mu, condition number, centring), the Lloyd
+    iterations, the final E-step and the D2H of labels / centres.  `value` is the PAGEABLE case (a NumPy array
+    as an sklearn caller holds it: staged through two pinned 256 MB buffers); the pinned case is beside it."""
+    import warnings
+    torch, args = c.torch, c.args
+    X.add_(mean)                                   # back to the uncentred data the user would hold
+    Xh = torch.empty(X.shape, dtype=torch.float64)           # pageable
+    Xh.copy_(X)
+    init = (centers_init + mean).cpu().numpy()
+    n_local = X.shape[0]
+    c.eng = None
+    # one small untimed fit first: library start-up (cuSOLVER handle, module load) is not the workload
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        qMeans_(n_clusters=K_CLUSTERS, init=init, n_init=1, max_iter=1, tol=0, delta=0, algorithm='full',
+                copy_x=False).fit(Xh[:min(n_local, 200000)].numpy())
+    secs, est = _fit_once(c, qMeans_, Xh.numpy(), init, args.steps, 99)
+    out = {"value": est.n_iter_ / secs, "unit": UNIT,
+           "h2d_bytes_per_step": (n_local * DIM * 8 + K_CLUSTERS * DIM * 8) / est.n_iter_,
+           "d2h_bytes_per_step": (n_local * 4 + K_CLUSTERS * DIM * 8 + 16 * est.n_iter_) / est.n_iter_,
+           "api": "qMeans_(n_clusters=256, init=<array>, n_init=1, max_iter=%d, tol=0, algorithm='full', ...)"
+                  ".fit(X_host)" % args.steps,
+           "host_memory": "pageable", "fit_seconds": secs, "n_iter": est.n_iter_, "inertia": est.inertia_,
+           "note": "one fit = H2D of the shard + preamble + n_iter Lloyd iterations + final E-step; "
+                   "bytes are totals divided by n_iter; the upload is paid once per fit, so the figure "
+                   "grows with max_iter (see fits)"}
+    fits = [{"max_iter": args.steps, "host_memory": "pageable", "fit_seconds": secs, "iter_per_s": est.n_iter_ / secs}]
+    if args.steps != 20:
+        s20, e20 = _fit_once(c, qMeans_, Xh.numpy(), init, 20, 99)
+        fits.append({"max_iter": 20, "host_memory": "pageable", "fit_seconds": s20, "iter_per_s": e20.n_iter_ / s20})
+    if args.fit300 or (c.world == 1 and n_local * args.steps <= 2e8):
+        s300, e300 = _fit_once(c, qMeans_, Xh.numpy(), init, 300, 99)
+        fits.append({"max_iter": 300, "host_memory": "pageable", "fit_seconds": s300, "iter_per_s": e300.n_iter_ / s300,
+                     "note": "the reference's default max_iter"})
+    try:
+        Xp = Xh.pin_memory()
+        sp, ep = _fit_once(c, qMeans_, Xp.numpy(), init, args.steps, 99)
+        fits.append({"max_iter": args.steps, "host_memory": "pinned", "fit_seconds": sp, "iter_per_s": ep.n_iter_ / sp})
+        out["pinned"] = {"value": ep.n_iter_ / sp, "fit_seconds": sp}
+        del Xp
+    except Exception as exc:
+        out["pinned"] = {"error": "%s: %s" % (type(exc).__name__, exc)}
+    out["fits"] = fits
+    return out
+
+
+def config3_csv(c, path, qMeans_):
+    """BASELINE.json config 3: q-means k = 15 on a CSV (numeric columns, standardised), delta 0.1 ... 1.0."""
+    import warnings
+    import pandas as pd
+    df = pd.read_csv(path)
+    Xc = df.select_dtypes(include=[np.number]).to_numpy(dtype=np.float64)
+    Xc = Xc[np.isfinite(Xc).all(axis=1)]
+    sd = Xc.std(axis=0)
+    Xc = (Xc - Xc.mean(axis=0)) / np.where(sd > 0, sd, 1.0)
+    rs = np.random.RandomState(0)
+    init = Xc[rs.permutation(len(Xc))[:15]].copy()
+    out = {"path": path, "shape": list(Xc.shape), "k": 15, "runs": []}
+    for delta in [round(0.1 * i, 1) for i in range(1, 11)]:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")
+            c.Q.seed(5)
+            t0 = time.perf_counter()
+            est = qMeans_(n_clusters=15, init=init, n_init=1, max_iter=10, tol=0, delta=delta, algorithm='full',
+                          intermediate_error=True, true_distance_estimate=False).fit(Xc)
+            c.torch.cuda.synchronize()
+            out["runs"].append({"delta": delta, "fit_seconds": time.perf_counter() - t0, "n_iter": est.n_iter_,
+                                "inertia": est.inertia_})
+    return out
 
 
 def main():

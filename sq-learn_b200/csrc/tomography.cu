@@ -518,6 +518,11 @@ struct TomoBigArgs {
     double* bcnt;          // [B, nblk] measurements that fall in the block
     double* errp;          // [B, nblk] per-block error partial
     int* done;             // [B]
+    double* nhop;          // [B] attempts with fewer measurements than this cannot meet delta (0: no such bound)
+    double* lbp;           // [B, nblk] per block: sum (or max) of (|x_i| - P_i)^2 after stage 1
+    int* skip2;            // [B] stage 2 of the current attempt is skipped
+    int may_skip;          // the current attempt may be given up early (stop rule on, not the last attempt)
+    int early;             // early give-up enabled for this call (phase 0 then computes nhop)
     long long B;
     int d, nblk, NB, logNB;
     int blk_lo;            // first block of this launch (leaf blocks can be sharded over GPUs)
@@ -534,13 +539,36 @@ __device__ __forceinline__ double big_scale(double sumsq, bool& zero) {
     return keep ? 1.0 : nrm;   // divisor
 }
 
-__global__ void tomo_big_init_kernel(TomoBigArgs a) {
-    long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= a.B) return;
-    a.done[b] = (a.sumsq[b] > 0.0) ? 0 : 1;
-    a.n_used[b] = 0.0;
-    a.err[b] = 0.0;
+// one CTA per vector: done flags, and the number of measurements below which an attempt cannot succeed: N
+// measurements leave at least d - N components at zero, so the squared L2 error is at least
+// ||x||^2 - N max_i x_i^2 (x the normalised input); an attempt with that above delta^2 draws nothing.
+__global__ void tomo_big_init_kernel(TomoBigArgs a, int early) {
+    __shared__ double red[32];
+    const long long b = blockIdx.x;
+    const int tid = threadIdx.x;
+    double m = 0.0;
+    if (early) {
+        const double* v = a.V + b * (long long)a.d;
+        for (int i = tid; i < a.d; i += blockDim.x) m = fmax(m, fabs(v[i]));
+        m = block_max(m, red, tid, blockDim.x);
+    }
+    if (tid == 0) {
+        const double ss = a.sumsq[b];
+        a.done[b] = (ss > 0.0) ? 0 : 1;
+        a.n_used[b] = 0.0;
+        a.err[b] = 0.0;
+        a.skip2[b] = 0;
+        double nh = 0.0;
+        if (early && ss > 0.0 && m > 0.0) {
+            bool zero;
+            const double div = big_scale(ss, zero);
+            const double S = ss / (div * div), x2 = (m / div) * (m / div);
+            nh = (S - a.delta * a.delta * (1.0 + 1e-9)) / x2 * (1.0 - 1e-9);
+        }
+        a.nhop[b] = nh;
+    }
 }
+#define TOMO_BIG_IDLE(a, b) ((a).done[b] || ((a).may_skip && (a).N < (a).nhop[b]))
 
 // block masses of stage 1 (and zero output for zero vectors)
 __global__ void tomo_big_mass_kernel(TomoBigArgs a) {
@@ -553,7 +581,7 @@ __global__ void tomo_big_mass_kernel(TomoBigArgs a) {
         for (int i = tid; i < TB; i += blockDim.x) { int g = blk * TB + i; if (g < a.d) a.est[b * (long long)a.d + g] = 0.0; }
         return;
     }
-    if (a.done[b]) return;
+    if (TOMO_BIG_IDLE(a, b)) return;
     double s = 0.0;
     for (int i = tid; i < TB; i += blockDim.x) {
         int g = blk * TB + i;
@@ -568,13 +596,27 @@ __global__ void tomo_big_mass_kernel(TomoBigArgs a) {
 __global__ void tomo_big_top_kernel(TomoBigArgs a, int stage) {
     extern __shared__ double sm[];
     const long long b = blockIdx.x;
-    if (a.done[b]) return;
+    if (TOMO_BIG_IDLE(a, b)) return;
     const int tid = threadIdx.x, T = blockDim.x, NB = a.NB;
     double* mass = sm;            // [2 NB]
     double* cnt = mass + 2 * NB;  // [2 NB]
     double* red = cnt + 2 * NB;   // [32]
     const SplitScratch sc = split_scratch_at(red + 32, NB);
     const unsigned long long vec = a.vec_offset + (unsigned long long)b;
+    if (stage == 1 && tid == 0) a.skip2[b] = 0;
+    if (stage == 2 && a.may_skip) {
+        // stage 1 left P; if no choice of signs can bring ||x - est|| under delta, stage 2 is not drawn
+        double lb = 0.0;
+        for (int i = tid; i < a.nblk; i += T) {
+            const double p = a.lbp[b * a.nblk + i];
+            lb = a.norm_inf ? fmax(lb, p) : lb + p;
+        }
+        lb = a.norm_inf ? block_max(lb, red, tid, T) : block_sum(lb, red, tid, T);
+        const bool hopeless = lb > (a.norm_inf ? a.delta : a.delta * a.delta) * (1.0 + 1e-9);
+        if (tid == 0) a.skip2[b] = hopeless ? 1 : 0;
+        if (hopeless) return;
+        __syncthreads();
+    }
     double sminus = 0.0;
     for (int i = tid; i < NB; i += T) {
         mass[NB + i] = (i < a.nblk) ? a.bm_a[b * a.nblk + i] : 0.0;
@@ -597,7 +639,7 @@ __global__ void tomo_big_top_kernel(TomoBigArgs a, int stage) {
 __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
     extern __shared__ double sm[];
     const long long b = blockIdx.y;
-    if (a.done[b]) return;
+    if (TOMO_BIG_IDLE(a, b) || (stage == 2 && a.skip2[b])) return;
     const int blk = blockIdx.x + a.blk_lo, tid = threadIdx.x, T = blockDim.x;
     double* v = sm;               // [TB]
     double* P = v + TB;           // [TB]
@@ -627,7 +669,7 @@ __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
     split_tree(mass, cnt, TB_LOG, tid, T, a.seed, vec, (unsigned)(4 * a.at + (stage == 1 ? 1 : 3)),
                (unsigned)(blk * (2 * TB)), sc);
     if (stage == 1) {
-        double sp = 0.0, smn = 0.0;
+        double sp = 0.0, smn = 0.0, lb = 0.0;
         for (int i = tid; i < TB; i += T) {
             int g = blk * TB + i;
             double p = sqrt(cnt[TB + i] / a.N);
@@ -635,10 +677,16 @@ __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
             double ap = 0.5 * (v[i] + p), am = 0.5 * (v[i] - p);
             sp += ap * ap;
             smn += am * am;
+            const double gap = fabs(v[i]) - p;
+            lb = a.norm_inf ? fmax(lb, fabs(gap)) : lb + gap * gap;
         }
         sp = block_sum(sp, red, tid, T);
         smn = block_sum(smn, red, tid, T);
-        if (tid == 0) { a.bm_a[b * a.nblk + blk] = sp; a.bm_b[b * a.nblk + blk] = smn; }
+        if (a.may_skip) lb = a.norm_inf ? block_max(lb, red, tid, T) : block_sum(lb, red, tid, T);
+        if (tid == 0) {
+            a.bm_a[b * a.nblk + blk] = sp; a.bm_b[b * a.nblk + blk] = smn;
+            if (a.may_skip) a.lbp[b * a.nblk + blk] = lb;
+        }
     } else {
         double e = 0.0;
         for (int i = tid; i < TB; i += T) {
@@ -659,7 +707,7 @@ __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
 __global__ void tomo_big_finish_kernel(TomoBigArgs a) {
     __shared__ double red[32];
     const long long b = blockIdx.x;
-    if (a.done[b]) return;
+    if (TOMO_BIG_IDLE(a, b) || a.skip2[b]) return;
     const int tid = threadIdx.x;
     double e = 0.0;
     for (int i = tid; i < a.nblk; i += blockDim.x) {
@@ -745,7 +793,7 @@ extern "C" int sq_tomography_batched(const double* V, long long B, int d, double
 // ---- long vectors ------------------------------------------------------------
 extern "C" int sq_row_sqnorms(const double* X, long long n, int d, double* out, void* stream);
 
-static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, size_t off[6], size_t* total) {
+static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, size_t off[9], size_t* total) {
     int nb = (d + TB - 1) / TB;
     int p2 = 2, lg = 1;
     while (p2 < nb) { p2 <<= 1; ++lg; }
@@ -758,6 +806,9 @@ static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, 
     off[3] = o; o += per;                                         // bcnt
     off[4] = o; o += per;                                         // errp
     off[5] = o; o += align_up((size_t)B * sizeof(int), 256);      // done
+    off[6] = o; o += align_up((size_t)B * sizeof(double), 256);   // nhop
+    off[7] = o; o += per;                                         // lbp
+    off[8] = o; o += align_up((size_t)B * sizeof(int), 256);      // skip2
     *total = o;
 }
 
@@ -784,7 +835,7 @@ extern "C" size_t sq_tomography_workspace_bytes(long long B, int d) {
         return tomo_group_ws_bytes(L, G, ctas);
     }
     int nblk, NB, logNB;
-    size_t off[6], total;
+    size_t off[9], total;
     tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
     return total;
 }
@@ -794,7 +845,7 @@ static int tomo_big_prepare(TomoBigArgs& a, const double* V, long long B, int d,
                             unsigned long long seed, unsigned long long vec_offset, double* est, double* n_used,
                             double* err, void* ws, size_t ws_bytes, const char* who) {
     int nblk, NB, logNB;
-    size_t off[6], total;
+    size_t off[9], total;
     tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
     if (NB > 4096) { set_error("%s: d=%d exceeds the supported %d", who, d, 4096 * TB); return SQ_ERR_UNSUPPORTED; }
     if (!ws || ws_bytes < total) { set_error("%s: workspace needs %zu bytes, got %zu", who, total, ws_bytes); return SQ_ERR_WORKSPACE; }
@@ -802,6 +853,7 @@ static int tomo_big_prepare(TomoBigArgs& a, const double* V, long long B, int d,
     a.V = V; a.est = est; a.n_used = n_used; a.err = err;
     a.sumsq = (double*)(w + off[0]); a.bm_a = (double*)(w + off[1]); a.bm_b = (double*)(w + off[2]);
     a.bcnt = (double*)(w + off[3]); a.errp = (double*)(w + off[4]); a.done = (int*)(w + off[5]);
+    a.nhop = (double*)(w + off[6]); a.lbp = (double*)(w + off[7]); a.skip2 = (int*)(w + off[8]); a.may_skip = 0; a.early = 0;
     a.B = B; a.d = d; a.nblk = nblk; a.NB = NB; a.logNB = logNB; a.norm_inf = norm_inf; a.stop = stop; a.delta = delta;
     a.seed = seed; a.vec_offset = vec_offset; a.blk_lo = 0; a.at = 0; a.N = 1.0;
     return SQ_OK;
@@ -816,7 +868,7 @@ static int tomo_big_phase(TomoBigArgs a, int phase, int blk_lo, int blk_hi, cuda
     if (phase == 0) {
         int rc = sq_row_sqnorms(a.V, a.B, a.d, (double*)a.sumsq, stream);
         if (rc) return rc;
-        tomo_big_init_kernel<<<(unsigned)((a.B + 255) / 256), 256, 0, stream>>>(a);
+        tomo_big_init_kernel<<<(unsigned)a.B, 256, 0, stream>>>(a, a.early && !a.norm_inf);
         SQ_CUDA(cudaFuncSetAttribute(tomo_big_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_top));
         SQ_CUDA(cudaFuncSetAttribute(tomo_big_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_blk));
     } else if (phase == 1) {
@@ -875,11 +927,13 @@ extern "C" int sq_tomography_batched_ws(const double* V, long long B, int d, dou
     int rc = tomo_big_prepare(a, V, B, d, delta, norm_inf, stop, seed, vec_offset, est, n_used, err, ws, ws_bytes,
                               "sq_tomography_batched_ws");
     if (rc) return rc;
+    a.early = (g_early && stop && sched_len > 1) ? 1 : 0;
     rc = tomo_big_phase(a, 0, 0, a.nblk, stream);
     if (rc) return rc;
     for (int at = 0; at < sched_len; ++at) {
         SQ_REQUIRE(sched_host[at] >= 1.0 && sched_host[at] < 9.0e15, "sq_tomography_batched_ws: schedule entry out of range");
         a.at = at; a.N = sched_host[at];
+        a.may_skip = (a.early && at + 1 < sched_len) ? 1 : 0;
         for (int phase = 1; phase <= 3; ++phase) {
             rc = tomo_big_phase(a, phase, 0, a.nblk, stream);
             if (rc) return rc;
@@ -892,7 +946,7 @@ extern "C" int sq_tomography_workspace_layout(long long B, int d, long long out[
     SQ_REQUIRE(out && B >= 1 && d > sq_tomography_max_fused_dim(), "sq_tomography_workspace_layout: needs B >= 1 and d > %d",
                sq_tomography_max_fused_dim());
     int nblk, NB, logNB;
-    size_t off[6], total;
+    size_t off[9], total;
     tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
     out[0] = nblk;
     out[1] = TB;

@@ -172,6 +172,10 @@ def _kmeans_plusplus_device(engine, n_clusters, random_state, n_local_trials=Non
     return centers
 
 
+# kernel launches of the centroid tomography per Lloyd iteration (stop-index fill, attempt-lane search, replay)
+TOMO_LAUNCHES_PER_ITER = 3
+
+
 def _mode_of(delta, true_distance_estimate):
     if not delta or delta <= 0:
         return MODE_EXACT

@@ -442,3 +442,23 @@ def test_skipping_hopeless_attempts_changes_nothing(cuda, d, delta, norm_inf):
         a = int(att[b])
         errs = np.linalg.norm(V[b] / np.linalg.norm(V[b]) - tr[b, :a], ord=np.inf if norm_inf else 2, axis=1)
         assert (errs[:-1] > delta).all() and errs[-1] <= delta
+
+
+@pytest.mark.parametrize("d,delta,norm_inf", [(5000, 0.3, 0), (20000, 0.2, 0), (9000, 0.05, 1)])
+def test_skipping_hopeless_attempts_changes_nothing_long_vectors(cuda, d, delta, norm_inf):
+    """the same for vectors beyond the fused path (block / top kernels)"""
+    from oracle import quantum_utility as qu
+    from sqlearn import _cabi
+    rs = np.random.RandomState(d)
+    V = rs.uniform(-1, 1, (3, d))
+    V[1] *= 4.0
+    sched = qu.schedule(qu.tomography_N(d, delta, "inf" if norm_inf else "L2")).astype(float)
+    try:
+        _cabi.check(_cabi.lib.sq_tomography_tune(7, 0.0), "tune")
+        plain = _big(V, delta, sched, norm_inf=norm_inf, stop=1, seed=66, vec_offset=3)
+    finally:
+        _cabi.check(_cabi.lib.sq_tomography_tune(7, 1.0), "tune")
+    fast = _big(V, delta, sched, norm_inf=norm_inf, stop=1, seed=66, vec_offset=3)
+    for a, b in zip(fast, plain):
+        assert np.array_equal(a, b)
+    assert (fast[2] <= delta).all() and (fast[1] < sched[-1]).all()
