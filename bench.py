@@ -315,12 +315,11 @@ def run_b200(args):
     centers0 = X[idx].clone() if rank == 0 else torch.empty((K_CLUSTERS, DIM), dtype=torch.float64, device=device)
     if world > 1:
         dist.broadcast(centers0, src=0)
-    centers = centers0.clone()
-    c_old, c_new = torch.empty_like(centers), torch.empty_like(centers)
+    state = D.LloydState(centers0)
     host = torch.empty((2,), dtype=torch.float64).pin_memory()
 
     def make_step(d_, inter_, tde_):
-        return lambda: D._lloyd_iteration(eng, centers, c_old, c_new, host, d_, inter_, True, True, None, tde_)
+        return lambda: D._lloyd_iteration(eng, state, host, d_, inter_, True, True, None, tde_)
     step = make_step(delta, inter, tde)
 
     for _ in range(args.warmup):
@@ -343,7 +342,7 @@ def run_b200(args):
     tot, cnt = (_cabi.ctypes.c_double)(), (_cabi.ctypes.c_longlong)()
     _cabi.lib.sq_profile_assign(2, None, None)
     for _ in range(max(3, min(args.steps, 10))):
-        D._labels_inertia(eng, centers, delta=delta, pool=None, true_distance_estimate=tde)
+        D._labels_inertia(eng, state.centers, delta=delta, pool=None, true_distance_estimate=tde)
     torch.cuda.synchronize()
     _cabi.lib.sq_profile_assign(0, _cabi.ctypes.byref(tot), _cabi.ctypes.byref(cnt))
     k_ms = tot.value / max(cnt.value, 1)
@@ -392,10 +391,10 @@ def run_b200(args):
     line["config"]["invariance"] = invariance_check(c, centers0)
     # ---- the other E-step modes as real timed steps, the tomography grid (config 5), qPCA (config 2) ----
     if not args.no_extra:
-        roofline["kernels"] += other_mode_steps(c, make_step, centers, centers0, flops, peak_sustained)
+        roofline["kernels"] += other_mode_steps(c, make_step, state, centers0, flops, peak_sustained)
         roofline["kernels"] += tomography_grid(c, peaks)
         if world == 1:
-            line["extra"] = extra_measurements(c, centers)
+            line["extra"] = extra_measurements(c, state.centers)
     # ---- e2e through the public API: qMeans_.fit on host arrays ----
     if not args.no_e2e:
         try:
@@ -418,12 +417,11 @@ def invariance_check(c, centers0):
     checksum of all labels.  Identical at N = 1, 2, 4, 8 (labels bit for bit; the inertia up to the order of
     the cross-rank sums)."""
     torch, D, eng = c.torch, c.D, c.eng
-    cen = centers0.clone()
-    c_old, c_new = torch.empty_like(cen), torch.empty_like(cen)
+    st = D.LloydState(centers0)
     host = torch.empty((2,), dtype=torch.float64).pin_memory()
     for _ in range(3):
-        inertia, _ = D._lloyd_iteration(eng, cen, c_old, c_new, host, 0.0, False, True, True, None, True)
-    D._labels_inertia(eng, cen, delta=0.0, pool=None, true_distance_estimate=True)
+        inertia, _ = D._lloyd_iteration(eng, st, host, 0.0, False, True, True, None, True)
+    D._labels_inertia(eng, st.centers, delta=0.0, pool=None, true_distance_estimate=True)
     idx = torch.arange(eng.row0, eng.row0 + eng.n, device=c.device, dtype=torch.int64)
     w = (idx * 2654435761 + 12345) & 0x7FFFFFFF
     crc = ((eng.labels.to(torch.int64) + 1) * w).sum().reshape(1)
@@ -436,7 +434,7 @@ def invariance_check(c, centers0):
             "what": "sum_i (label_i + 1) * ((i * 2654435761 + 12345) mod 2^31) over all rows i, mod 2^64"}
 
 
-def other_mode_steps(c, make_step, centers, centers0, flops, peak_sustained):
+def other_mode_steps(c, make_step, state, centers0, flops, peak_sustained):
     """One Lloyd step in each of the E-step modes the headline does not use, timed as real steps
     (E-step + M-step + all-reduce + centroid tomography + read-back), max over ranks."""
     torch, args = c.torch, c.args
@@ -445,7 +443,7 @@ def other_mode_steps(c, make_step, centers, centers0, flops, peak_sustained):
                                              "window": (DELTA, True, False, 3)}.items():
         if name == args.mode:
             continue
-        centers.copy_(centers0)
+        state.centers = centers0.clone()
         st = make_step(delta, inter, tde)
         st()
         st()
@@ -472,7 +470,7 @@ def other_mode_steps(c, make_step, centers, centers0, flops, peak_sustained):
             rec["achieved_TFLOPs_per_gpu"] = tf
             rec["frac_of_sustained_peak"] = tf / peak_sustained if peak_sustained else None
         out.append(rec)
-    centers.copy_(centers0)
+    state.centers = centers0.clone()
     return out
 
 

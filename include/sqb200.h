@@ -97,6 +97,17 @@ int sq_tomography_batched_spec(const double* V, long long B, int d, double delta
                                unsigned long long vec_offset, double* est, double* n_used, double* err,
                                int* attempts, int* stop_idx, void* stream);
 
+/* The same in ONE launch: the attempt lane of a vector that finishes last replays the recorded attempt itself.
+ * state[2 B] ints carry the search from lane to lane; prepare them once with sq_tomography_spec_state_init -
+ * every call leaves them prepared for the next one (calls that share a state must not overlap on the GPU).
+ * Results are those of sq_tomography_batched_spec / sq_tomography_batched with stop = 1, bit for bit.
+ * (The q-means loop calls this once per Lloyd iteration for the centroid tomography, _dmeans.py:825-828.)   */
+int sq_tomography_spec_state_init(int* state, long long B, void* stream);
+int sq_tomography_batched_spec_fused(const double* V, long long B, int d, double delta, int norm_inf,
+                                     const double* sched_host, int sched_len, int lanes, unsigned long long seed,
+                                     unsigned long long vec_offset, double* est, double* n_used, double* err,
+                                     int* attempts, int* state, void* stream);
+
 /* Measurement hook (no reference counterpart; process-wide and NOT thread-safe - meant for tools/, not for
  * callers): what = 0 sets the factor f of the rule "an attempt with N <= f * clamp(L, 32, 512) measurements
  * draws them one by one instead of splitting counts down the tree" (L = d rounded up to a power of two;
@@ -115,8 +126,9 @@ int sq_tomography_tune(int what, double value);
  * xnorm[n] = ||x_i||^2 (sq_row_sqnorms).  Outputs: labels[n] int32,
  * mindist[n] (may be NULL), inertia[1] = sum_i min_j D_ij, n_fixed[1] (may be
  * NULL) = rows re-evaluated with the reference's exact arithmetic.          */
-/* workspace_bytes = the fixed part + 40 MiB for the ipe tiles (64 KB per resident CTA); sq_qmeans_assign accepts
- * less in modes 0 and 1 (fixed part only) and runs mode 2 on a smaller grid when fewer tiles fit. */
+/* workspace_bytes = the fixed part + 60 MiB for the ipe tiles (640 tiles of 96 KB, one per resident CTA);
+ * sq_qmeans_assign accepts less in modes 0 and 1 (fixed part only) and runs mode 2 on a smaller grid when fewer
+ * tiles fit. */
 size_t sq_qmeans_assign_workspace_bytes(long long n, int d, int k);
 int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, const double* C, int k, int mode,
                      double delta, unsigned long long seed, unsigned long long offset, int* labels,
@@ -142,10 +154,13 @@ int sq_ipe_debug_tail_sample(double M, double x, long long B, unsigned long long
  * stream capture.  All calls share the one array and it keeps the previous call's contents:
  * two calls whose kernels can run at the same time on one GPU (different streams, no
  * dependency) race on it; serialise them.  Inputs, outputs and results are those of
- * sq_qmeans_assign.  In mode 2 every resident CTA parks a tile of dot products (<= 64 KB) in
- * the scratch, so what the fixed part leaves of the 2 MiB bounds the grid (about ten CTAs at
- * the largest n): same results, a fraction of the speed - give sq_qmeans_assign a workspace
- * if you can.                                                                              */
+ * sq_qmeans_assign.  In mode 2 every resident CTA parks a tile of dot products (96 KB) in
+ * the scratch, so what the fixed part leaves of the 2 MiB bounds the grid (7 CTAs at the
+ * largest shape, 65536 x 1024, whose fixed part is 1.33 MB; 21 for a small batch): same
+ * results, a fraction of the speed - give sq_qmeans_assign a workspace if you can.  The
+ * per-device address of the array is looked up once and cached without a lock (two first
+ * calls racing on one device both store the same value); the cache does not survive
+ * cudaDeviceReset.                                                                          */
 int sq_qmeans_assign_noalloc(const double* X, const double* xnorm, long long n, int d, const double* C, int k,
                              int mode, double delta, unsigned long long seed, unsigned long long offset, int* labels,
                              double* mindist, double* inertia, int* n_fixed, void* stream);
@@ -153,7 +168,10 @@ int sq_qmeans_assign_noalloc(const double* X, const double* xnorm, long long n, 
 /* Timing hook for the roofline measurement (no reference counterpart): enable = 2 resets
  * the counters and turns per-launch CUDA-event timing of the main E-step kernel on (each
  * sq_qmeans_assign then blocks until its kernel ends); 1 = on, 0 = off.  The totals seen
- * before the call are returned through total_ms / launches (either may be NULL).        */
+ * before the call are returned through total_ms / launches (either may be NULL).
+ * Like sq_ipe_debug_force_replay and sq_tomography_tune this is a process-wide switch read
+ * without synchronisation: NOT thread-safe, and while it is on the "calls never
+ * synchronise" convention above does not hold.  Tools and tests only.                    */
 int sq_profile_assign(int enable, double* total_ms, long long* launches);
 
 /* row_norms(X, squared=True) (sklearn/utils/extmath.py:49-78) */
@@ -165,7 +183,8 @@ int sq_sum_f64(const double* v, long long n, double* out, void* ws, size_t ws_by
  * _centers_update (sklearn/cluster/_dmeans.py:814-823): sums[k,d] and
  * counts[k] of the rows carrying each label (this rank's rows only; the
  * caller all-reduces sums and counts before sq_centroid_finalize).
- * bad_label_flag[1] (may be NULL) is set to 1 if a label is outside [0,k).  */
+ * bad_label_flag[1] (may be NULL) is set to 1 if a label is outside [0,k); it is only ever set, never
+ * cleared: zero it once and look at it when you like.                        */
 size_t sq_centroid_workspace_bytes(long long n, int d, int k);
 int sq_centroid_accumulate(const double* X, const int* labels, long long n, int d, int k, double* sums,
                            double* counts, int* bad_label_flag, void* ws, size_t ws_bytes, void* stream);

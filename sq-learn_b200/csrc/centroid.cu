@@ -27,6 +27,7 @@ struct CentroidWs {
     int* perm;        // [n]   row indices grouped by label
     int* base;        // [k+1] first slot of each label in perm
     int* item_off;    // [k+1] first item of each label
+    int* scan_done;   // [1]   blocks of label_scan_kernel that have finished (reset by the last one)
     double* partial;  // [max_items][d]
 };
 
@@ -66,15 +67,17 @@ static size_t centroid_ws_layout(long long n, int d, int k, CentroidWs* w, char*
     p = take((size_t)n * sizeof(int));                if (w) w->perm = (int*)p;
     p = take((size_t)(k + 1) * sizeof(int));          if (w) w->base = (int*)p;
     p = take((size_t)(k + 1) * sizeof(int));          if (w) w->item_off = (int*)p;
+    p = take(256);                                    if (w) w->scan_done = (int*)p;
     p = take((size_t)g.max_items * d * sizeof(double)); if (w) w->partial = (double*)p;
     return off;
 }
 
 // ---- 1. per-warp label histogram -------------------------------------------
 __global__ void label_hist_kernel(const int* __restrict__ labels, long long n, int k, long long rows_per_warp, int W,
-                                  int* __restrict__ hist, int* __restrict__ bad) {
+                                  int* __restrict__ hist, int* __restrict__ bad, int* __restrict__ scan_done) {
     extern __shared__ int sh[];
     const int lane = threadIdx.x & 31, wl = threadIdx.x >> 5;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *scan_done = 0;     // counter of the next kernel (workspace is uninitialised)
     const int w = blockIdx.x * CW_WARPS_PER_BLOCK + wl;
     int* h = sh + wl * k;
     for (int j = lane; j < k; j += 32) h[j] = 0;
@@ -91,10 +94,46 @@ __global__ void label_hist_kernel(const int* __restrict__ labels, long long n, i
     for (int j = lane; j < k; j += 32) hist[(long long)j * W + w] = h[j];
 }
 
-// ---- 2. exclusive scan of every label's row over the W slices ----------------
-__global__ void label_scan_kernel(int* __restrict__ hist, int W, int* __restrict__ totals) {
+// ---- 2. + 3. exclusive scan of every label's row over the W slices; the block that finishes last then
+// turns the k totals into label bases and item offsets (two exclusive scans over k) ----------------
+__device__ __forceinline__ void label_base_scan(const int* totals, int k, int* base, int* item_off, double* counts,
+                                                int ITEM_ROWS) {
+    __shared__ int wsum_c[32], wsum_i[32];
+    __shared__ int carry_c, carry_i;
+    const int tid = threadIdx.x, lane = tid & 31, wl = tid >> 5;
+    if (tid == 0) { carry_c = 0; carry_i = 0; }
+    __syncthreads();
+    for (int j0 = 0; j0 < k; j0 += blockDim.x) {
+        const int j = j0 + tid;
+        const int c = (j < k) ? totals[j] : 0;          // read before base[j] is overwritten (totals may alias base)
+        const int it = (c + ITEM_ROWS - 1) / ITEM_ROWS;
+        int xc = c, xi = it;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int yc = __shfl_up_sync(0xffffffffu, xc, o), yi = __shfl_up_sync(0xffffffffu, xi, o);
+            if (lane >= o) { xc += yc; xi += yi; }
+        }
+        if (lane == 31) { wsum_c[wl] = xc; wsum_i[wl] = xi; }
+        __syncthreads();
+        int oc = carry_c, oi = carry_i;
+        for (int w = 0; w < wl; ++w) { oc += wsum_c[w]; oi += wsum_i[w]; }
+        if (j < k) {
+            base[j] = oc + xc - c;
+            item_off[j] = oi + xi - it;
+            if (counts) counts[j] = (double)c;
+        }
+        __syncthreads();
+        if (tid == blockDim.x - 1) { carry_c = oc + xc; carry_i = oi + xi; }
+        __syncthreads();
+    }
+    if (tid == 0) { base[k] = carry_c; item_off[k] = carry_i; }
+}
+
+__global__ void label_scan_kernel(int* __restrict__ hist, int W, int* totals, int k, int* item_off, double* counts,
+                                  int ITEM_ROWS, int* done) {
     __shared__ int wsum[32];
     __shared__ int carry_s;
+    __shared__ int s_last;
     const int j = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wl = tid >> 5;
     int* row = hist + (long long)j * W;
     if (tid == 0) carry_s = 0;
@@ -121,41 +160,17 @@ __global__ void label_scan_kernel(int* __restrict__ hist, int W, int* __restrict
         if (tid == 0) carry_s = carry + wsum[(blockDim.x >> 5) - 1];
         __syncthreads();
     }
-    if (tid == 0) totals[j] = carry_s;
-}
-
-// ---- 3. label bases and item offsets: two exclusive scans over k in one block ----------------
-__global__ void label_base_kernel(const int* totals, int k, int* base, int* item_off, double* counts, int ITEM_ROWS) {
-    __shared__ int wsum_c[32], wsum_i[32];
-    __shared__ int carry_c, carry_i;
-    const int tid = threadIdx.x, lane = tid & 31, wl = tid >> 5, nw = blockDim.x >> 5;
-    if (tid == 0) { carry_c = 0; carry_i = 0; }
-    __syncthreads();
-    for (int j0 = 0; j0 < k; j0 += blockDim.x) {
-        const int j = j0 + tid;
-        const int c = (j < k) ? totals[j] : 0;          // read before base[j] is overwritten (totals may alias base)
-        const int it = (c + ITEM_ROWS - 1) / ITEM_ROWS;
-        int xc = c, xi = it;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            int yc = __shfl_up_sync(0xffffffffu, xc, o), yi = __shfl_up_sync(0xffffffffu, xi, o);
-            if (lane >= o) { xc += yc; xi += yi; }
-        }
-        if (lane == 31) { wsum_c[wl] = xc; wsum_i[wl] = xi; }
-        __syncthreads();
-        int oc = carry_c, oi = carry_i;
-        for (int w = 0; w < wl; ++w) { oc += wsum_c[w]; oi += wsum_i[w]; }
-        if (j < k) {
-            base[j] = oc + xc - c;
-            item_off[j] = oi + xi - it;
-            if (counts) counts[j] = (double)c;
-        }
-        __syncthreads();
-        if (tid == blockDim.x - 1) { carry_c = oc + xc; carry_i = oi + xi; }
-        __syncthreads();
-        (void)nw;
+    if (tid == 0) {
+        totals[j] = carry_s;
+        __threadfence();                                   // the total is visible before the block counts as done
+        s_last = (atomicAdd(done, 1) == (int)gridDim.x - 1);
     }
-    if (tid == 0) { base[k] = carry_c; item_off[k] = carry_i; }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (tid == 0) *done = 0;                               // ready for the next call
+    // totals[] aliases base[]: label_base_scan reads totals[j] before it writes base[j]
+    label_base_scan(totals, k, totals, item_off, counts, ITEM_ROWS);
 }
 
 // ---- 4. stable scatter of row indices into label buckets ---------------------
@@ -329,14 +344,11 @@ extern "C" int sq_centroid_accumulate(const double* X, const int* labels, long l
         SQ_CUDA(cudaFuncSetAttribute(label_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
     }
     int* bad = bad_label_flag ? bad_label_flag : w.item_off;  // scratch int when the caller does not care
-    if (bad_label_flag) SQ_CUDA(cudaMemsetAsync(bad_label_flag, 0, sizeof(int), stream));
-    label_hist_kernel<<<g.blocks, 32 * CW_WARPS_PER_BLOCK, sh, stream>>>(labels, n, k, g.rows_per_warp, g.W, w.hist, bad);
+    label_hist_kernel<<<g.blocks, 32 * CW_WARPS_PER_BLOCK, sh, stream>>>(labels, n, k, g.rows_per_warp, g.W, w.hist, bad,
+                                                                         w.scan_done);
     SQ_LAUNCH_CHECK("label_hist_kernel");
-    label_scan_kernel<<<k, 256, 0, stream>>>(w.hist, g.W, w.base);
+    label_scan_kernel<<<k, 256, 0, stream>>>(w.hist, g.W, w.base, k, w.item_off, counts, g.item_rows, w.scan_done);
     SQ_LAUNCH_CHECK("label_scan_kernel");
-    // base[] holds the totals on entry; the kernel reads totals[j] before it writes base[j]
-    label_base_kernel<<<1, 256, 0, stream>>>(w.base, k, w.base, w.item_off, counts, g.item_rows);
-    SQ_LAUNCH_CHECK("label_base_kernel");
     label_scatter_kernel<<<g.blocks, 32 * CW_WARPS_PER_BLOCK, sh, stream>>>(labels, n, k, g.rows_per_warp, g.W, w.hist, w.base, w.perm);
     SQ_LAUNCH_CHECK("label_scatter_kernel");
     int items_grid = (int)(g.max_items < 65535LL * 16 ? g.max_items : 65535LL * 16);

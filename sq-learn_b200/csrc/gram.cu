@@ -319,6 +319,7 @@ extern "C" int sq_gram_centered(const double* X, long long n, int d, const doubl
                                 size_t ws_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     SQ_REQUIRE(X && out_gram && n >= 1 && d >= 1, "sq_gram_centered: bad arguments");
+    SQ_REQUIRE(n < 2147483647LL, "sq_gram_centered: n=%lld rows exceed the 2^31 - 1 the row coordinates hold", n);
     size_t need = sq_gram_workspace_bytes(n, d);
     if (!ws || ws_bytes < need) { set_error("sq_gram_centered: workspace needs %zu bytes, got %zu", need, ws_bytes); return SQ_ERR_WORKSPACE; }
     GramGeom g = gram_geom(n, d);
@@ -329,7 +330,8 @@ extern "C" int sq_gram_centered(const double* X, long long n, int d, const doubl
     SQ_CUDA(cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int vec16 = ((d & 1) == 0 && ((uintptr_t)X & 15) == 0) ? 1 : 0;
     CUtensorMap tm;
-    bool use_tma = vec16 && !mean && !getenv("SQ_GRAM_NO_TMA") &&
+    static const bool no_tma = getenv("SQ_GRAM_NO_TMA") != nullptr;   // A/B timing switch, read once
+    bool use_tma = vec16 && !mean && !no_tma &&
                    make_tensor_map_2d(&tm, X, (unsigned long long)d, (unsigned long long)n, 4, GT_R) == 0;
     if (use_tma) {
         size_t sm2 = (size_t)GT_STAGES * 2 * GB * GT_R * sizeof(double) + GT_STAGES * sizeof(unsigned long long);
@@ -351,6 +353,7 @@ extern "C" size_t sq_col_sums_workspace_bytes(long long n, int d) { return (size
 extern "C" int sq_col_sums(const double* X, long long n, int d, double* out, void* ws, size_t ws_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     SQ_REQUIRE(X && out && n >= 1 && d >= 1, "sq_col_sums: bad arguments");
+    SQ_REQUIRE(n < 2147483647LL, "sq_col_sums: n=%lld rows exceed 2^31 - 1", n);
     size_t need = sq_col_sums_workspace_bytes(n, d);
     if (!ws || ws_bytes < need) { set_error("sq_col_sums: workspace needs %zu bytes, got %zu", need, ws_bytes); return SQ_ERR_WORKSPACE; }
     int blocks = colsum_blocks(n, d);

@@ -143,7 +143,7 @@ extern "C" int sq_mu_norms(const double* X, long long n, int d, const double* ex
                            size_t ws_bytes, void* stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     SQ_REQUIRE(X && exp_row_host && exp_col_host && out_rowmax && out_colsum && out_frob2, "sq_mu_norms: null pointer");
-    SQ_REQUIRE(n >= 1 && d >= 1, "sq_mu_norms: bad shape");
+    SQ_REQUIRE(n >= 1 && n < 2147483647LL && d >= 1, "sq_mu_norms: bad shape (n=%lld rows must be below 2^31 - 1)", n);
     SQ_REQUIRE(n_p >= 1 && n_p <= MU_MAXP, "sq_mu_norms: n_p=%d outside [1,%d]", n_p, MU_MAXP);
     size_t need = sq_mu_norms_workspace_bytes(n, d, n_p);
     if (!ws || ws_bytes < need) { set_error("sq_mu_norms: workspace needs %zu bytes, got %zu", need, ws_bytes); return SQ_ERR_WORKSPACE; }

@@ -679,7 +679,9 @@ __global__ void qmeans_window_fixup_kernel(AssignArgs a) {
 }
 
 // ---- ||row||^2 of a row-major matrix (row_norms(X, squared=True), extmath.py:49-78)
-__global__ void row_sqnorm_kernel(const double* __restrict__ X, long long n, int d, double* __restrict__ out) {
+__global__ void row_sqnorm_kernel(const double* __restrict__ X, long long n, int d, double* __restrict__ out,
+                                  int* __restrict__ clear) {
+    if (clear && blockIdx.x == 0 && threadIdx.x == 0) *clear = 0;   // (the E-step's near-tie counter rides along)
     const int lane = threadIdx.x & 31;
     long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nw = ((long long)gridDim.x * blockDim.x) >> 5;
@@ -711,8 +713,10 @@ __global__ void sum_partial_kernel(const double* __restrict__ v, long long n, do
         part[blockIdx.x] = t;
     }
 }
-__global__ void sum_final_kernel(const double* __restrict__ part, int np, double* __restrict__ out) {
+__global__ void sum_final_kernel(const double* __restrict__ part, int np, double* __restrict__ out,
+                                 const int* __restrict__ copy_src, int* __restrict__ copy_dst) {
     __shared__ double red[32];
+    if (copy_dst && threadIdx.x == 0) *copy_dst = *copy_src;      // (the E-step's count of re-evaluated rows rides along)
     double s = 0.0;
     for (int i = threadIdx.x; i < np; i += blockDim.x) s += part[i];
     s = warp_sum(s);
@@ -773,6 +777,12 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
     a.num_tiles = (int)((a.n + Cfg::BM - 1) / Cfg::BM);
     a.NT = (a.k + Cfg::BN - 1) / Cfg::BN;
     a.KC = (a.d + Cfg::BK - 1) / Cfg::BK;
+    // a CTA counts its (tile, centroid block, k chunk) steps in an int: even one CTA owning every tile must fit
+    if ((long long)a.num_tiles * a.NT * a.KC >= 2147483647LL) {
+        set_error("sq_qmeans_assign: n=%lld d=%d k=%d is %lld tile steps, beyond 2^31 - 1; split the rows", a.n, a.d, a.k,
+                  (long long)a.num_tiles * a.NT * a.KC);
+        return SQ_ERR_UNSUPPORTED;
+    }
     size_t smem = assign_smem_bytes<Cfg>() + (size_t)a.NT * Cfg::BN * sizeof(double);
     if (smem > 227 * 1024) { set_error("sq_qmeans_assign: k=%d needs %zu bytes of shared memory", a.k, smem); return SQ_ERR_UNSUPPORTED; }
     bool vec16 = (a.d & 1) == 0 && ((uintptr_t)a.X & 15) == 0 && ((uintptr_t)a.C & 15) == 0;
@@ -784,7 +794,9 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
     CUtensorMap tmA, tmB;
     memset(&tmA, 0, sizeof(tmA));
     memset(&tmB, 0, sizeof(tmB));
-    bool use_tma = vec16 && !getenv("SQ_ASSIGN_NO_TMA");   // (the variable forces the cp.async path, for A/B timing)
+    // (SQ_ASSIGN_NO_TMA forces the cp.async path, for A/B timing; read once, when the library is loaded)
+    static const bool no_tma = getenv("SQ_ASSIGN_NO_TMA") != nullptr;
+    bool use_tma = vec16 && !no_tma;
     if (use_tma) {
         int r1 = make_tensor_map_2d(&tmA, a.X, (unsigned long long)a.d, (unsigned long long)a.n, 4, Cfg::BM);
         int r2 = make_tensor_map_2d(&tmB, a.C, (unsigned long long)a.d, (unsigned long long)a.k, 4, Cfg::BN);
@@ -869,7 +881,7 @@ extern "C" int sq_row_sqnorms(const double* X, long long n, int d, double* out, 
     long long blocks = (n + 7) / 8;
     int cap = device_sm_count() * 16;
     if (blocks > cap) blocks = cap;
-    row_sqnorm_kernel<<<(int)blocks, 256, 0, stream>>>(X, n, d, out);
+    row_sqnorm_kernel<<<(int)blocks, 256, 0, stream>>>(X, n, d, out, nullptr);
     SQ_LAUNCH_CHECK("row_sqnorm_kernel");
     return SQ_OK;
 }
@@ -880,7 +892,7 @@ extern "C" int sq_sum_f64(const double* v, long long n, double* out, void* ws, s
     if (ws_bytes < SUM_BLOCKS * sizeof(double) || !ws) { set_error("sq_sum_f64: workspace needs %d bytes", (int)(SUM_BLOCKS * sizeof(double))); return SQ_ERR_WORKSPACE; }
     sum_partial_kernel<<<SUM_BLOCKS, 256, 0, stream>>>(v, n, (double*)ws);
     SQ_LAUNCH_CHECK("sum_partial_kernel");
-    sum_final_kernel<<<1, 1024, 0, stream>>>((double*)ws, SUM_BLOCKS, out);
+    sum_final_kernel<<<1, 1024, 0, stream>>>((double*)ws, SUM_BLOCKS, out, nullptr, nullptr);
     SQ_LAUNCH_CHECK("sum_final_kernel");
     return SQ_OK;
 }
@@ -904,9 +916,15 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     AssignWs w;
     assign_ws_layout(n, k, &w, (char*)ws);
 
-    SQ_CUDA(cudaMemsetAsync(w.flag_count, 0, sizeof(int), stream));
-    int rc = sq_row_sqnorms(C, k, d, w.cnorm, stream);
-    if (rc) return rc;
+    // centre norms; the same launch clears the near-tie counter
+    {
+        long long blocks = ((long long)k + 7) / 8;
+        int cap = device_sm_count() * 16;
+        if (blocks > cap) blocks = cap;
+        row_sqnorm_kernel<<<(int)blocks, 256, 0, stream>>>(C, k, d, w.cnorm, w.flag_count);
+        SQ_LAUNCH_CHECK("row_sqnorm_kernel");
+    }
+    int rc;
 
     AssignArgs a;
     a.X = X; a.xnorm = xnorm; a.C = C; a.cnorm = w.cnorm; a.rowmin_in = nullptr;
@@ -939,9 +957,11 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
         qmeans_window_fixup_kernel<<<fb, 256, 0, stream>>>(a);
         SQ_LAUNCH_CHECK("qmeans_window_fixup_kernel");
     }
-    rc = sq_sum_f64(a.mindist, n, inertia, w.partial, SUM_BLOCKS * sizeof(double), stream);
-    if (rc) return rc;
-    if (n_fixed) SQ_CUDA(cudaMemcpyAsync(n_fixed, w.flag_count, sizeof(int), cudaMemcpyDeviceToDevice, stream));
+    // inertia = sum of the row minima (fixed order); the last launch also hands out the count of re-evaluated rows
+    sum_partial_kernel<<<SUM_BLOCKS, 256, 0, stream>>>(a.mindist, n, w.partial);
+    SQ_LAUNCH_CHECK("sum_partial_kernel");
+    sum_final_kernel<<<1, 1024, 0, stream>>>(w.partial, SUM_BLOCKS, inertia, w.flag_count, n_fixed);
+    SQ_LAUNCH_CHECK("sum_final_kernel");
     return SQ_OK;
 }
 

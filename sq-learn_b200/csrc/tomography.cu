@@ -31,7 +31,9 @@ struct TomoArgs {
     double* trace;        // optional [B, sched_len, d]: the estimate of every attempt made
     int* attempts;        // optional [B]: number of attempts made
     int* stop_idx;        // [B] speculative modes: index of the first attempt that met the accuracy
-    int spec;             // 0: attempts in order; 1: attempt lanes searching for stop_idx; 2: replay stop_idx
+    int* lane_done;       // [B] spec = 3: attempt lanes of the vector that have finished their search
+    int spec;             // 0: attempts in order; 1: attempt lanes searching for stop_idx; 2: replay stop_idx;
+                          // 3: search, then the lane that finishes last replays (one launch)
     double sched[128];    // attempt sizes N (integers stored as doubles), by value
     long long B;
     int d;
@@ -321,12 +323,12 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
     // delta^2 (or max_i ||x_i| - P_i| > delta), fails whatever stage 2 draws; its stage 2 is skipped.  Attempts
     // are independent fresh draws, so this does not touch the law of the attempt that is returned - nor a bit of
     // it.  Not for the last attempt (returned even when it fails), nor when every attempt's estimate is wanted.
-    const bool early = a.early && a.stop && a.spec != 2 && a.trace == nullptr;
+    const bool early_on = a.early && a.stop && a.trace == nullptr;
     const double early_thr = (a.norm_inf ? a.delta : a.delta * a.delta) * (1.0 + 1e-9);
     // The same before any draw: N measurements leave at least d - N components at zero, so the squared error
     // is at least ||x||^2 - N max_i x_i^2.
     double n_hopeless = 0.0;
-    if (early && cache && !a.norm_inf) {
+    if (early_on && a.spec != 2 && cache && !a.norm_inf) {
         xmax2 = block_max(xmax2, tot, tid, T);
         n_hopeless = (C1[L - 1] - early_thr) / xmax2 * (1.0 - 1e-9);   // attempts with N < n_hopeless cannot succeed
         __syncthreads();
@@ -338,11 +340,23 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
     // records the smallest successful index.  Attempts are independent fresh draws keyed by their index, so
     // replaying the recorded attempt (spec = 2) returns exactly what the in-order loop would have returned.
     __shared__ int s_cut;
-    int at0 = 0, step = 1, at_end = a.sched_len;
-    if (a.spec == 1) { at0 = blockIdx.y; step = gridDim.y; }
-    if (a.spec == 2) { at0 = min(a.stop_idx[b], a.sched_len - 1); at_end = at0 + 1; }
+    int at0 = 0;
+  for (int pass = 0; pass < (a.spec == 3 ? 2 : 1); ++pass) {
+    const int mode = a.spec == 3 ? pass + 1 : a.spec;          // 0 in order, 1 search, 2 replay
+    const bool early = early_on && mode != 2;
+    int step = 1, at_end = a.sched_len;
+    at0 = 0;
+    if (mode == 1) { at0 = blockIdx.y; step = gridDim.y; }
+    if (mode == 2) {
+        __syncthreads();
+        if (tid == 0) s_cut = *((volatile int*)&a.stop_idx[b]);
+        __syncthreads();
+        at0 = min(s_cut, a.sched_len - 1); at_end = at0 + 1;
+        __syncthreads();
+        if (a.spec == 3 && tid == 0) a.stop_idx[b] = 0x7fffffff;      // as the next call expects it
+    }
     for (int at = at0; at < at_end; at += step) {
-        if (a.spec == 1) {
+        if (mode == 1) {
             __syncthreads();
             if (tid == 0) s_cut = *((volatile int*)&a.stop_idx[b]);
             __syncthreads();
@@ -447,14 +461,27 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
             double* tr = a.trace + (b * a.sched_len + at) * (long long)d;
             for (int i = tid; i < d; i += T) tr[i] = P[i];
         }
-        if (a.spec == 1) {
+        if (mode == 1) {
             if (e <= a.delta) { if (tid == 0) atomicMin(&a.stop_idx[b], at); break; }
             continue;
         }
         if (a.stop && e <= a.delta) break;  // e is identical in every thread
     }
-    if (a.spec == 1) return;
-    if (a.spec == 2) n_att = at0 + 1;
+    if (mode == 1) {
+        if (a.spec != 3) return;
+        // the lane that finishes last knows the first successful attempt of all lanes and replays it
+        __shared__ int s_last;
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            s_last = (atomicAdd(&a.lane_done[b], 1) == (int)gridDim.y - 1);
+        }
+        __syncthreads();
+        if (!s_last) return;
+        if (tid == 0) { a.lane_done[b] = 0; __threadfence(); }
+    }
+  }
+    if (a.spec >= 2) n_att = at0 + 1;
     __syncthreads();
     for (int i = tid; i < d; i += T) a.est[b * (long long)d + i] = P[i];
     if (tid == 0) { a.n_used[b] = n_last; a.err[b] = err_last; if (a.attempts) a.attempts[b] = n_att; }
@@ -763,7 +790,7 @@ extern "C" int sq_tomography_batched(const double* V, long long B, int d, double
     if (B == 0) return SQ_OK;
     TomoArgs a;
     a.V = V; a.est = est; a.n_used = n_used; a.err = err; a.trace = trace; a.attempts = attempts;
-    a.stop_idx = nullptr; a.spec = 0;
+    a.stop_idx = nullptr; a.lane_done = nullptr; a.spec = 0;
     for (int i = 0; i < sched_len; ++i) {
         SQ_REQUIRE(sched_host[i] >= 1.0 && sched_host[i] < 9.0e15, "sq_tomography_batched: schedule entry out of range");
         a.sched[i] = sched_host[i];
@@ -1000,7 +1027,7 @@ extern "C" int sq_tomography_batched_spec(const double* V, long long B, int d, d
     if (B == 0) return SQ_OK;
     TomoArgs a;
     a.V = V; a.est = est; a.n_used = n_used; a.err = err; a.trace = nullptr; a.attempts = attempts;
-    a.stop_idx = stop_idx;
+    a.stop_idx = stop_idx; a.lane_done = nullptr;
     for (int i = 0; i < sched_len; ++i) {
         SQ_REQUIRE(sched_host[i] >= 1.0 && sched_host[i] < 9.0e15, "sq_tomography_batched_spec: schedule entry out of range");
         a.sched[i] = sched_host[i];
@@ -1016,4 +1043,49 @@ extern "C" int sq_tomography_batched_spec(const double* V, long long B, int d, d
     if (rc) return rc;
     a.spec = 2;
     return tomo_launch(a, B, 1, stream);
+}
+
+// ---- the same in one launch ---------------------------------------------------------------------
+__global__ void tomo_spec_state_kernel(int* state, long long B) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < B) { state[i] = 0x7fffffff; state[B + i] = 0; }
+}
+
+extern "C" int sq_tomography_spec_state_init(int* state, long long B, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(state && B >= 1 && B <= 65535, "sq_tomography_spec_state_init: bad arguments");
+    tomo_spec_state_kernel<<<(unsigned)((B + 255) / 256), 256, 0, stream>>>(state, B);
+    SQ_LAUNCH_CHECK("tomo_spec_state_kernel");
+    return SQ_OK;
+}
+
+extern "C" int sq_tomography_batched_spec_fused(const double* V, long long B, int d, double delta, int norm_inf,
+                                                const double* sched_host, int sched_len, int lanes,
+                                                unsigned long long seed, unsigned long long vec_offset, double* est,
+                                                double* n_used, double* err, int* attempts, int* state, void* stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    SQ_REQUIRE(V && est && n_used && err && sched_host && state, "sq_tomography_batched_spec_fused: null pointer");
+    SQ_REQUIRE(B >= 0 && B <= 65535 && d >= 1, "sq_tomography_batched_spec_fused: bad shape B=%lld d=%d", B, d);
+    SQ_REQUIRE(sched_len >= 1 && sched_len <= 128, "sq_tomography_batched_spec_fused: sched_len=%d outside [1,128]", sched_len);
+    SQ_REQUIRE(lanes >= 1 && lanes <= 64, "sq_tomography_batched_spec_fused: lanes=%d outside [1,64]", lanes);
+    SQ_REQUIRE(delta > 0.0, "sq_tomography_batched_spec_fused: delta must be > 0");
+    if (d > sq_tomography_max_fused_dim()) {
+        set_error("sq_tomography_batched_spec_fused: d=%d exceeds the fused-path limit %d", d, sq_tomography_max_fused_dim());
+        return SQ_ERR_UNSUPPORTED;
+    }
+    if (B == 0) return SQ_OK;
+    TomoArgs a;
+    a.V = V; a.est = est; a.n_used = n_used; a.err = err; a.trace = nullptr; a.attempts = attempts;
+    a.stop_idx = state; a.lane_done = state + B;
+    for (int i = 0; i < sched_len; ++i) {
+        SQ_REQUIRE(sched_host[i] >= 1.0 && sched_host[i] < 9.0e15, "sq_tomography_batched_spec_fused: schedule entry out of range");
+        a.sched[i] = sched_host[i];
+    }
+    a.B = B; a.d = d;
+    int L = 2, logL = 1;
+    while (L < d) { L <<= 1; ++logL; }
+    a.L = L; a.logL = logL; a.sched_len = sched_len; a.norm_inf = norm_inf; a.stop = 1; a.delta = delta;
+    a.seed = seed; a.vec_offset = vec_offset;
+    a.spec = 3;
+    return tomo_launch(a, B, lanes, stream);
 }

@@ -225,6 +225,24 @@ def tomography_schedule(N, faster_measure_increment=0):
     return check_measure(idx, faster_measure_increment=faster_measure_increment)
 
 
+_spec_states = {}
+
+
+def _spec_state(B):
+    """Search state of sq_tomography_batched_spec_fused for batches of B vectors on the current device and
+    stream: prepared once, left prepared by every call."""
+    key = (torch.cuda.current_device(), torch.cuda.current_stream().cuda_stream, int(B))
+    st = _spec_states.get(key)
+    if st is None:
+        st = dv.empty((2 * int(B),), dtype=torch.int32)
+        _cabi.check(_cabi.lib.sq_tomography_spec_state_init(dv.ptr(st), int(B), dv.stream_ptr()),
+                    "sq_tomography_spec_state_init")
+        if len(_spec_states) > 64:
+            _spec_states.clear()
+        _spec_states[key] = st
+    return st
+
+
 def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, vec_offset=None, seed_=None):
     """Run K1 on a device tensor V [B, d]; returns (est, n_used, err, trace, attempts)."""
     B, d = V.shape
@@ -264,12 +282,12 @@ def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, v
                 "sq_tomography_batched_ws")
         return est, n_used, err, tr, att, sched
     if stop and incremental and len(sched) > 1 and not trace and B <= 2048:
-        # few vectors: the latency of the attempt-by-attempt search dominates; search 8 attempts at a time
-        scratch = dv.empty((B,), dtype=torch.int32)
-        _cabi.check(_cabi.lib.sq_tomography_batched_spec(
+        # few vectors: the latency of the attempt-by-attempt search dominates; 8 attempt lanes per vector search
+        # the schedule together and the lane that finishes last replays the first successful attempt (one launch)
+        _cabi.check(_cabi.lib.sq_tomography_batched_spec_fused(
             dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, sched.ctypes.data, len(sched), 8, seed_,
-            vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err), None, dv.ptr(scratch), dv.stream_ptr()),
-            "sq_tomography_batched_spec")
+            vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err), None, dv.ptr(_spec_state(B)), dv.stream_ptr()),
+            "sq_tomography_batched_spec_fused")
         return est, n_used, err, tr, att, sched
     if not trace:
         # a single attempt of many vectors runs in the group kernel, which keeps its trees in a workspace

@@ -33,6 +33,9 @@ SIGNATURES = {
                                             c_void_p]),
     "sq_tomography_batched_spec": (c_int, [c_void_p, c_ll, c_int, c_double, c_int, c_void_p, c_int, c_int, c_ull, c_ull,
                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "sq_tomography_spec_state_init": (c_int, [c_void_p, c_ll, c_void_p]),
+    "sq_tomography_batched_spec_fused": (c_int, [c_void_p, c_ll, c_int, c_double, c_int, c_void_p, c_int, c_int, c_ull,
+                                                 c_ull, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "sq_tomography_tune": (c_int, [c_int, c_double]),
     "sq_ipe_debug_force_replay": (c_int, [c_int]),
     "sq_ipe_debug_tail_sample": (c_int, [c_double, c_double, c_ll, c_ull, c_void_p, c_void_p]),

@@ -172,8 +172,8 @@ def _kmeans_plusplus_device(engine, n_clusters, random_state, n_local_trials=Non
     return centers
 
 
-# kernel launches of the centroid tomography per Lloyd iteration (stop-index fill, attempt-lane search, replay)
-TOMO_LAUNCHES_PER_ITER = 3
+# kernel launches of the centroid tomography per Lloyd iteration (attempt-lane search + replay in one kernel)
+TOMO_LAUNCHES_PER_ITER = 1
 
 
 def _mode_of(delta, true_distance_estimate):
@@ -236,20 +236,29 @@ def _centroid_tomography(engine, centers, error, true_tomography, stop_when_reac
     return out
 
 
-def _lloyd_iteration(engine, centers, centers_old, centers_new, host, delta, intermediate_err, true_tomography,
-                     stop_when_reached_accuracy, pool, true_distance_estimate):
-    """One pass of the loop body of _kmeans_single_lloyd (reference: _dmeans.py:619-651):
-    E-step, M-step (+ centroid tomography), centre shift; updates ``centers`` in place and
-    returns (inertia, shift) read back through the pinned 2-double buffer ``host``."""
-    centers_old.copy_(centers)
-    labels, _, _ = _labels_inertia(engine, centers, delta=delta, pool=pool,
-                                   true_distance_estimate=true_distance_estimate)
-    out = _centers_update(engine, labels, delta / 2, intermediate_error=intermediate_err,
-                          true_tomography=true_tomography,
-                          stop_when_reached_accuracy=stop_when_reached_accuracy,
-                          centers_old=centers_old, centers_out=centers_new)
-    centers.copy_(out)
-    shift_dev = engine.shift(centers_old, centers)
+class LloydState:
+    """The centres of a run on the device: ``centers`` is the current [k, d] tensor (a new object after every
+    iteration - nothing is copied), ``spare`` a buffer of the same shape for the means of the next M-step."""
+
+    def __init__(self, centers_init):
+        self.centers = centers_init.clone()
+        self.spare = torch.empty_like(self.centers)
+
+
+def _lloyd_iteration(engine, state, host, delta, intermediate_err, true_tomography, stop_when_reached_accuracy, pool,
+                     true_distance_estimate):
+    """One pass of the loop body of _kmeans_single_lloyd (reference: _dmeans.py:619-651): E-step, M-step
+    (+ centroid tomography), centre shift; ``state.centers`` becomes the new centres and (inertia, shift) come
+    back through the pinned 2-double buffer ``host``."""
+    old = state.centers
+    labels, _, _ = _labels_inertia(engine, old, delta=delta, pool=pool, true_distance_estimate=true_distance_estimate)
+    new = _centers_update(engine, labels, delta / 2, intermediate_error=intermediate_err,
+                          true_tomography=true_tomography, stop_when_reached_accuracy=stop_when_reached_accuracy,
+                          centers_old=old, centers_out=state.spare)
+    shift_dev = engine.shift(old, new)
+    if new is state.spare:                       # no tomography: the means are the centres; the old ones become spare
+        state.spare = old
+    state.centers = new
     host[0:1].copy_(engine.inertia, non_blocking=True)   # already summed over ranks by the M-step
     host[1:2].copy_(shift_dev, non_blocking=True)
     torch.cuda.current_stream().synchronize()
@@ -269,11 +278,9 @@ def _kmeans_single_lloyd(engine, sample_weight, centers_init, intermediate_err, 
     if delta == None:  # noqa: E711
         delta = 0
     k, d = engine.k, engine.d
-    centers = centers_init.clone()
-    centers_old = torch.empty_like(centers)
-    centers_new = torch.empty_like(centers)
+    state = LloydState(centers_init)
     best_labels = torch.empty_like(engine.labels)
-    best_centers = torch.empty_like(centers)
+    best_centers = torch.empty_like(state.centers)
     best_inertia = None
     host = torch.empty((2,), dtype=torch.float64).pin_memory()
     stats = {"fixed_rows": 0, "empty_clusters": 0}
@@ -282,13 +289,13 @@ def _kmeans_single_lloyd(engine, sample_weight, centers_init, intermediate_err, 
     for i in range(max_iter):
         labels = engine.labels
         inertia, center_shift_total = _lloyd_iteration(
-            engine, centers, centers_old, centers_new, host, delta, intermediate_err, true_tomography,
-            stop_when_reached_accuracy, pool, true_distance_estimate)
+            engine, state, host, delta, intermediate_err, true_tomography, stop_when_reached_accuracy, pool,
+            true_distance_estimate)
         if verbose:
             print("Iteration %2d, inertia %.3f" % (i, inertia))
         if best_inertia is None or inertia < best_inertia:
             best_labels.copy_(labels)
-            best_centers.copy_(centers)
+            best_centers.copy_(state.centers)
             best_inertia = inertia
         if center_shift_total <= tol:
             if verbose:
@@ -313,6 +320,7 @@ def _kmeans_single_lloyd(engine, sample_weight, centers_init, intermediate_err, 
 
 
 from .._base import BaseEstimator, check_is_fitted  # noqa: E402
+from .._spectral import refined_eigh  # noqa: E402
 
 
 def _validate_X(X, copy=True):
@@ -485,7 +493,9 @@ class qMeans_(BaseEstimator):
         self.eta = float(s1[-1])                                        # max_i ||x_i||^2
         mu = list(np.sqrt(s1[:-1] * s2[:-1]))
         self.muA = min(min(mu), float(np.sqrt(fr.item())))
-        lam = torch.linalg.eigvalsh(G)                                  # cuSOLVER, d x d
+        # cuSOLVER, d x d; eigenvalues below 1e-6 of the largest are re-solved in their own subspace
+        # (sqlearn/_spectral.py), so that min(S) is as accurate as the reference's LAPACK SVD
+        lam, _ = refined_eigh(engine.X, G)
         r = min(engine.n_total, d)
         smin = float(torch.sqrt(torch.clamp(lam[d - r], min=0.0)).item())
         self.condition_number = 1 / smin if smin > 0 else float('inf')

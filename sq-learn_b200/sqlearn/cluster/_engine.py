@@ -33,7 +33,7 @@ class QMeansEngine:
         self.inertia = self.red[k * d + k:]
         self.scal = dv.empty((4,))          # [shift, ...]
         self.n_fixed = dv.empty((1,), dtype=torch.int32)
-        self.bad = dv.empty((1,), dtype=torch.int32)
+        self.bad = torch.zeros((1,), dtype=torch.int32, device=X_dev.device)   # sticky flag: a label outside [0, k) was seen
         self.ws_a_bytes = _cabi.lib.sq_qmeans_assign_workspace_bytes(n, d, k)
         self.ws_a = dv.workspace(self.ws_a_bytes)
         self.ws_c_bytes = _cabi.lib.sq_centroid_workspace_bytes(n, d, k)
@@ -79,7 +79,7 @@ class QMeansEngine:
             dv.ptr(self.X), dv.ptr(self.xnorm), self.n, self.d, dv.ptr(centers), self.k, mode, float(delta),
             seed, offset, dv.ptr(self.labels), dv.ptr(self.mindist), dv.ptr(self.inertia), dv.ptr(self.n_fixed),
             dv.ptr(self.ws_a), self.ws_a_bytes, dv.stream_ptr()), "sq_qmeans_assign")
-        # memset, centre norms, assign, (fix-up), 2 x sum
+        # centre norms (+ counter reset), assign, (fix-up), 2 x sum
         self.launches += 4 if mode == MODE_IPE else 5
 
     # ---- M-step (K3) -------------------------------------------------------
@@ -87,7 +87,7 @@ class QMeansEngine:
         _cabi.check(_cabi.lib.sq_centroid_accumulate(
             dv.ptr(self.X), dv.ptr(self.labels), self.n, self.d, self.k, dv.ptr(self.sums), dv.ptr(self.counts),
             dv.ptr(self.bad), dv.ptr(self.ws_c), self.ws_c_bytes, dv.stream_ptr()), "sq_centroid_accumulate")
-        self.launches += 6
+        self.launches += 5          # histogram, scan (+ bases), scatter, segment sums, combine
 
     def finalize(self, centers_old, centers_new):
         _cabi.check(_cabi.lib.sq_centroid_finalize(dv.ptr(self.sums), dv.ptr(self.counts), dv.ptr(centers_old),

@@ -5,7 +5,10 @@ reference class ``qPCA``.  What runs where:
   * singular values / right singular vectors: the reference takes a LAPACK SVD of the
     centred data (_qPCA.py:578-583); here the centred Gram matrix is formed on the fp64
     tensor cores (K4) and only the d x d symmetric eigenproblem goes to cuSOLVER.  sigma =
-    sqrt(lambda); relative error of sigma_i ~ eps_mach * (sigma_1/sigma_i)^2.
+    sqrt(lambda); the eigenvalues below 1e-6 of the largest are re-solved in their own subspace
+    (sqlearn/_spectral.py), which brings the absolute error of every sigma_i to ~eps_mach * sigma_1,
+    the accuracy of the reference's LAPACK SVD (np.isclose(singular_values_, 0) and 1/min(S) then
+    behave as in the reference on rank-deficient data).
   * svd_flip's signs need arg-max |U[:, j]| over all rows: K5 streams X once more through
     the tensor cores without materialising U.
   * best_mu over the 11-point grid: K6; singular-value estimation (consistent phase
@@ -30,7 +33,43 @@ from .. import _device as dv
 from ..QuantumUtility import Utility as qu
 from ..QuantumUtility.Utility import (QuantumState, amplitude_estimation, estimate_wald, tomography,
                                       unwrap_phase_est_arguments, wrapper_phase_est_arguments)
+from .._spectral import refined_eigh
 from ._base import _BasePCA
+
+
+def _infer_dimension(spectrum, n_samples):
+    """Minka's choice of the PCA dimension ("Automatic choice of dimensionality for PCA", NIPS 2000), the rule
+    behind n_components='mle' (reference: _assess_dimension / _infer_dimension, _qPCA.py:30-110): the rank in
+    [1, n_features - 1] with the largest Laplace-approximated evidence
+
+        log p(rank k) = log p(U) - n/2 sum_{i<=k} log l_i - n (d - k)/2 log v + (m + k)/2 log 2 pi
+                        - 1/2 sum_{i<=k, j>i} [log((l_i - l_j)(1/l~_j - 1/l~_i)) + log n] - k/2 log n,
+
+    l the eigenvalues of the covariance, v the mean of the discarded ones, l~ = l with the tail replaced by v,
+    m = d k - k (k + 1)/2.  A rank whose last eigenvalue is below 1e-15 is never chosen.  Host-side and cold."""
+    from scipy.special import gammaln
+    spectrum = np.asarray(spectrum, dtype=np.float64)
+    d = spectrum.shape[0]
+    tiny = 1e-15
+    ll = np.full(d, -np.inf)
+    for k in range(1, d):
+        if spectrum[k - 1] < tiny:
+            continue
+        i = np.arange(1, k + 1)
+        log_pu = -k * log(2.) + np.sum(gammaln((d - i + 1) / 2.) - log(np.pi) * (d - i + 1) / 2.)
+        log_pl = -np.sum(np.log(spectrum[:k])) * n_samples / 2.
+        v = max(tiny, np.sum(spectrum[k:]) / (d - k))
+        log_pv = -np.log(v) * n_samples * (d - k) / 2.
+        m = d * k - k * (k + 1.) / 2.
+        log_pp = log(2. * np.pi) * (m + k) / 2.
+        lt = spectrum.copy()
+        lt[k:] = v
+        log_pa = 0.
+        for a in range(k):
+            gap = (spectrum[a] - spectrum[a + 1:]) * (1. / lt[a + 1:] - 1. / lt[a])
+            log_pa += np.sum(np.log(gap)) + (d - a - 1) * log(n_samples)
+        ll[k] = log_pu + log_pl + log_pv + log_pp - log_pa / 2. - k * log(n_samples) / 2.
+    return int(np.argmax(ll))
 
 
 def _cpe(thetas, epsilon, gamma):
@@ -171,7 +210,9 @@ class qPCA(_BasePCA):
         _cabi.check(_cabi.lib.sq_gram_centered(dv.ptr(Xd), n, d, None, dv.ptr(G), dv.ptr(ws), nb, dv.stream_ptr()),
                     "sq_gram_centered")
         dv.all_reduce_sum(G)
-        lam, V = torch.linalg.eigh(G)                      # ascending; cuSOLVER, d x d (off the hot path)
+        # ascending; cuSOLVER, d x d (off the hot path), with the small end of the spectrum re-solved in its own
+        # subspace so that sigma is accurate to ~eps * sigma_max like LAPACK's SVD, not to sqrt(eps) * sigma_max
+        lam, V = refined_eigh(Xd, G)
         r = min(n_glob, d)
         lam = torch.flip(lam, dims=[0])[:r]
         Vt = torch.flip(V, dims=[1]).T[:r].contiguous()    # rows = right singular vectors, descending sigma
@@ -197,7 +238,6 @@ class qPCA(_BasePCA):
         if n_components == 'mle':
             if n_samples < n_features:
                 raise ValueError("n_components='mle' is only supported if n_samples >= n_features")
-            raise NotImplementedError("n_components='mle' (Minka's dimension inference) is outside the quantum path")
         elif not 0 <= n_components <= min(n_samples, n_features):
             raise ValueError("n_components=%r must be between 0 and min(n_samples, n_features)=%r with "
                              "svd_solver='full'" % (n_components, min(n_samples, n_features)))
@@ -214,7 +254,9 @@ class qPCA(_BasePCA):
         total_var = explained_variance_.sum()
         explained_variance_ratio_ = explained_variance_ / total_var
         singular_values_ = S.copy()
-        if 0 < n_components < 1.0:
+        if n_components == 'mle':
+            n_components = _infer_dimension(explained_variance_, n_glob)
+        elif 0 < n_components < 1.0:
             ratio_cumsum = np.cumsum(explained_variance_ratio_, dtype=np.float64)
             n_components = np.searchsorted(ratio_cumsum, n_components, side='right') + 1
         if n_components < min(n_features, n_samples):
@@ -243,6 +285,8 @@ class qPCA(_BasePCA):
         U_rows = U_rows / torch.clamp(S_d, min=1e-300)[None, :]
         self.left_sv = U_rows.cpu().numpy()
         self.spectral_norm = self.singular_values_[0]
+        # (the reference sets this in _fit_truncated only, :749; q_ret_variance reads it)
+        self.scaled_singular_values = self.singular_values_ / self.spectral_norm
         self.frob_norm = frob
         self._frob_sq = frob ** 2
         self.norm_muA, self.muA = qu.best_mu(Xd, start=0, step=0.1)

@@ -377,6 +377,21 @@ def test_speculative_lanes_equal_the_in_order_search(cuda):
             assert np.array_equal(est.cpu().numpy(), want[0])
             assert np.array_equal(n_used.cpu().numpy(), want[1])
             assert np.array_equal(err.cpu().numpy(), want[2])
+        # the same in one launch (the lane that finishes last replays); the state is prepared once and every
+        # call leaves it prepared: three calls in a row, the second with another seed
+        state = torch.empty(2 * B, dtype=torch.int32, device="cuda")
+        _cabi.check(_cabi.lib.sq_tomography_spec_state_init(state.data_ptr(), B, dv.stream_ptr()), "state")
+        other = G.tomography(V, delta, sched, stop=1, seed=78, vec_offset=5)
+        for seed, ref in ((77, want), (78, other), (77, want)):
+            est.zero_(); n_used.zero_(); err.zero_()
+            _cabi.check(_cabi.lib.sq_tomography_batched_spec_fused(
+                Vd.data_ptr(), B, d, delta, 0, sched.ctypes.data, len(sched), 8, seed, 5, est.data_ptr(),
+                n_used.data_ptr(), err.data_ptr(), att.data_ptr(), state.data_ptr(), dv.stream_ptr()), "spec_fused")
+            torch.cuda.synchronize()
+            assert np.array_equal(est.cpu().numpy(), ref[0])
+            assert np.array_equal(n_used.cpu().numpy(), ref[1])
+            assert np.array_equal(err.cpu().numpy(), ref[2])
+        assert (state[:B] == 0x7fffffff).all() and (state[B:] == 0).all()
 
 
 @pytest.mark.parametrize("B,d,delta,norm_inf", [(700, 1000, 0.1, 0), (5000, 128, 0.25, 0), (400, 4096, 0.2, 0),

@@ -55,6 +55,35 @@ def test_noalloc_matches_workspace_entry_point_twice_in_a_row(cuda):
         assert nfix == want_fix
 
 
+def test_noalloc_ipe_mode_and_wide_window(cuda):
+    """mode 2 (the IPE tiles live in what the fixed part leaves of the 2 MiB: a smaller grid, same draws) and the
+    delta-window mode with more than 256 centroids (row-minimum pre-pass), twice in a row each, plus the largest
+    shape the entry point takes"""
+    import gpu_util as G
+    rs = np.random.RandomState(321)
+    C3 = rs.randn(40, 16)
+    X3 = C3[rs.randint(0, 40, 2500)] + 0.3 * rs.randn(2500, 16)
+    C4 = rs.randn(300, 24) * 1.5
+    X4 = C4[rs.randint(0, 300, 4000)] + rs.randn(4000, 24)
+    for X, C, mode, delta, seed in [(X3, C3, 2, 0.5, 5), (X4, C4, 1, 5.0, 6), (X3, C3, 2, 0.5, 7), (X4, C4, 1, 5.0, 8),
+                                    (X4, C4, 2, 1.0, 9)]:
+        rc, lab, mind, inertia, nfix = _call_noalloc(X, C, mode, delta, seed=seed)
+        assert rc == 0
+        want_lab, want_mind, want_inertia, want_fix = G.assign(X, C, mode=mode, delta=delta, seed=seed)
+        assert np.array_equal(lab, want_lab)                      # same seed, same draws, whatever the grid
+        np.testing.assert_allclose(mind, want_mind, rtol=1e-10, atol=1e-12)
+        assert inertia == pytest.approx(want_inertia, rel=1e-10)
+    # 65536 x 1024: the fixed part of the scratch is 1.33 MB, seven IPE tiles fit beside it
+    C5 = rs.randn(1024, 8)
+    X5 = C5[rs.randint(0, 1024, 65536)] + 0.2 * rs.randn(65536, 8)
+    for mode, delta in [(0, 0.0), (1, 0.3), (2, 0.3)]:
+        rc, lab, mind, inertia, nfix = _call_noalloc(X5, C5, mode, delta, seed=11)
+        assert rc == 0
+        want_lab, want_mind, want_inertia, _ = G.assign(X5, C5, mode=mode, delta=delta, seed=11)
+        assert np.array_equal(lab, want_lab)
+        assert inertia == pytest.approx(want_inertia, rel=1e-10)
+
+
 def test_noalloc_rejects_sizes_beyond_its_scratch(cuda, lib):
     rc, *_ = _call_noalloc(np.zeros((65537, 2)), np.ones((3, 2)), 0, 0.0, seed=1)
     assert rc == 4
