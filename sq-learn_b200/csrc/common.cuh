@@ -127,6 +127,17 @@ struct Philox {
 };
 
 #ifdef __CUDACC__
+// The sign rule of real_tomography, `x > 0.4 * P_i[e] ** 2 * N` (Utility.py:350, :396), evaluated in the
+// reference's own order of operations, ((0.4 * (P * P)) * N), each product rounded once.  It matters: P^2 = n/N, so
+// the threshold is 0.4 n up to rounding, and whenever 0.4 n is an integer (n a multiple of 5) the count x can hit it
+// exactly - the comparison is then decided by the last bit of the threshold.  With a few hundred components of
+// 5..30 counts each that happens several times per vector, on components whose flipped sign IS the L-infinity
+// error; another association of the products (or a fused multiply-add) changes the law of that error by ~1 %
+// (seen against 10^4 reference draws at d = 784).
+__device__ __forceinline__ double tomo_sign_threshold(double p, double N) {
+    return __dmul_rn(__dmul_rn(0.4, __dmul_rn(p, p)), N);
+}
+
 // ---------------------------------------------------------------------------
 // Warp helpers
 // ---------------------------------------------------------------------------

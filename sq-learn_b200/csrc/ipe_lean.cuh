@@ -1,0 +1,276 @@
+// Inner-product estimation for one (sample, centroid) pair: the median of the 13 amplitude-estimation outcomes
+// sampled by ONE inversion.
+//
+// Reference: ipe -> median_evaluation(amplitude_estimation, gamma = 0.1 => Q = 13)
+// (sklearn/QuantumUtility/Utility.py:697-737, :534-572, :442-531).  One outcome j has the law
+//     p(j) = sin^2(pi t) f(|j - x|),   f(d) = 1 / (M sin(pi d / M))^2,   x = M theta_a / pi,  t = frac(x),
+// and the estimate a~ = sin^2(pi j / M) depends on j through r = min(j, M - j) only, increasingly.  The median
+// of 13 independent outcomes therefore has the CDF  G(F(r)),  F the CDF of ONE outcome in r-order and
+// G(F) = P(Binomial(13, F) >= 7), so it can be drawn by inversion from a single uniform V: the smallest r with
+// V <= G(F(r)).  No tail draws, no sort.
+//
+// F at the 8 grid points around x ("window") is  F_i = B + cum_i,  cum_i the running sum of the window weights
+// (plus the weights of their mirror images M - r, negligible away from M/2) and B the mass of every r below the
+// window.  In distance from x, B is ONE contiguous run:  B = sin^2(pi t) sum_{k=0}^{K-1} f(a + k),  a = t + 4,
+// K = 2 floor(x) - 7 (the points left of the window down to 0, then their mirror images).  f is convex on (0, M),
+// so the run is bracketed by two integrals with a closed form (the antiderivative of csc^2 is -cot):
+//     int_a^{a+K-1} f + (f(a) + f(a+K-1))/2   <=   sum   <=   int_{a-1/2}^{a+K-1/2} f        (Hermite-Hadamard)
+// The gap is ~3e-4 of the mass.  V is compared with G at both ends of the bracket: if both agree the comparison
+// is certain; otherwise (0.3 % of the pairs) ipe_tighten peels exact terms off both ends of the run, which
+// shrinks the gap like 1/a^3, until every comparison is certain; a median outside the window (1e-6) is found by
+// plain summation (ipe_brute).  All three use the same V, so together they ARE the inversion - exact in law, not
+// an approximation.  ipe_lean declines (IPE_GENERAL) what it is not built for - small grids, windows touching 0
+// or M/2, sizeable mirror weights - before looking at V, so those pairs can go to the general estimator of
+// ipe.cuh with its own draws without touching the law.
+#pragma once
+#include "common.cuh"
+#include "fejer.cuh"
+
+namespace sq {
+
+enum { IPE_DONE = 0, IPE_GENERAL = 1, IPE_TIGHTEN = 2, IPE_BRUTE = 3 };
+
+struct IpeGrid {
+    double S;      // |x|^2 + |c|^2
+    double M;      // grid size of amplitude estimation (Utility.py:484)
+    double x;      // M theta_a / pi
+    double j0, t;  // floor and fraction of x
+    int kind;      // 0: S <= 0 (estimate 0), 1: x on a grid point (deterministic), 2: to be sampled
+};
+
+__host__ __device__ inline double sq_cospi(double y) {
+#ifdef __CUDA_ARCH__
+    return cospi(y);
+#else
+    return cos(3.14159265358979323846 * y);
+#endif
+}
+
+// a, epsilon_a, M, theta_a of ipe / amplitude_estimation (Utility.py:725-733, :484-493)
+__host__ __device__ inline void ipe_grid(double dot, double xn, double cn, double eps, IpeGrid& g) {
+    const double PI = 3.14159265358979323846;
+    g.S = xn + cn;
+    g.kind = 0;
+    g.M = 16.0; g.x = 0.0; g.j0 = 0.0; g.t = 0.0;
+    if (!(g.S > 0.0)) return;
+    double a = (g.S - 2.0 * dot) / (2.0 * g.S);
+    if (a < 1e-15) a = 0.0;  // math.isclose(a, 0, abs_tol=1e-15) (Utility.py:730); negatives are rounding noise
+    if (a > 1.0) a = 1.0;
+    const double eps_a = eps * fmax(1.0, fabs(dot)) / g.S;
+    g.M = ceil((PI / (2.0 * eps_a)) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
+    g.x = g.M * (asin(sqrt(a)) / PI);
+    g.j0 = floor(g.x);
+    g.t = g.x - g.j0;
+    g.kind = (g.t == 0.0) ? 1 : 2;
+}
+
+// P(Binomial(13, F) >= 7) = F^7 sum_{i=0}^{6} C(6 + i, i) (1 - F)^i
+__host__ __device__ inline double ipe_G(double F) {
+    F = fmin(fmax(F, 0.0), 1.0);
+    const double q = 1.0 - F;
+    double s = 924.0;
+    s = fma(s, q, 462.0);
+    s = fma(s, q, 210.0);
+    s = fma(s, q, 84.0);
+    s = fma(s, q, 28.0);
+    s = fma(s, q, 7.0);
+    s = fma(s, q, 1.0);
+    const double F2 = F * F, F4 = F2 * F2;
+    return F4 * F2 * F * s;
+}
+
+__host__ __device__ inline double ipe_f(double M, double d) {
+    const double ms = M * sq_sinpi(d / M);
+    return 1.0 / (ms * ms);
+}
+
+// window weights w_i = sin^2(pi t) f(|i - 3 - t|), i = 0..7 (grid points j0 - 3 .. j0 + 4), M >= 32
+__host__ __device__ inline void ipe_window(double M, double t, double s2, double w[8]) {
+    const double PI = 3.14159265358979323846;
+    const double piM = PI / M;
+    double pw[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        // |pi z / M| < pi/8: M sin(pi z/M) = pi z P(u), u = (pi z/M)^2, Taylor to u^7 (next term < 2e-18)
+        const double z = (double)(i - 3) - t, y = z * piM, u = y * y;
+        double P = -1.0 / 1307674368000.0;
+        P = fma(P, u, 1.0 / 6227020800.0);
+        P = fma(P, u, -1.0 / 39916800.0);
+        P = fma(P, u, 1.0 / 362880.0);
+        P = fma(P, u, -1.0 / 5040.0);
+        P = fma(P, u, 1.0 / 120.0);
+        P = fma(P, u, -1.0 / 6.0);
+        P = fma(P, u, 1.0);
+        const double ms = PI * z * P;
+        pw[i] = ms * ms;
+    }
+    // w_i = s2 / pw_i with one division: prefix and suffix products
+    const double a01 = pw[0] * pw[1], a23 = pw[2] * pw[3], a45 = pw[4] * pw[5], a67 = pw[6] * pw[7];
+    const double lo4 = a01 * a23, hi4 = a45 * a67;
+    const double r = s2 / (lo4 * hi4);
+    const double rl = r * hi4, rh = r * lo4;
+    const double r01 = rl * a23, r23 = rl * a01, r45 = rh * a67, r67 = rh * a45;
+    w[0] = r01 * pw[1]; w[1] = r01 * pw[0]; w[2] = r23 * pw[3]; w[3] = r23 * pw[2];
+    w[4] = r45 * pw[5]; w[5] = r45 * pw[4]; w[6] = r67 * pw[7]; w[7] = r67 * pw[6];
+}
+
+// sin and cos of a small angle (|y| <= 0.5), to full double precision
+__host__ __device__ inline void ipe_sincos_small(double y, double& s, double& c) {
+    const double u = y * y;
+    double P = -1.0 / 1307674368000.0;
+    P = fma(P, u, 1.0 / 6227020800.0);
+    P = fma(P, u, -1.0 / 39916800.0);
+    P = fma(P, u, 1.0 / 362880.0);
+    P = fma(P, u, -1.0 / 5040.0);
+    P = fma(P, u, 1.0 / 120.0);
+    P = fma(P, u, -1.0 / 6.0);
+    P = fma(P, u, 1.0);
+    s = y * P;
+    double Q = 1.0 / 20922789888000.0;
+    Q = fma(Q, u, -1.0 / 87178291200.0);
+    Q = fma(Q, u, 1.0 / 479001600.0);
+    Q = fma(Q, u, -1.0 / 3628800.0);
+    Q = fma(Q, u, 1.0 / 40320.0);
+    Q = fma(Q, u, -1.0 / 720.0);
+    Q = fma(Q, u, 1.0 / 24.0);
+    Q = fma(Q, u, -0.5);
+    c = fma(Q, u, 1.0);
+}
+
+// Bracket of  sum_{k=0}^{K-1} f(a + k)  for the convex f above (K >= 1, 1/2 < a, a + K - 1/2 < M).
+// near = true: the near end (a - 1/2, a) is within 0.5 rad of 0 and is done by Taylor series.
+__host__ __device__ inline void ipe_run_bracket(double M, double a, double K, bool near, double& lo, double& hi) {
+    const double PI = 3.14159265358979323846;
+    const double piM = PI / M;
+    double s1, c1, s3, c3;                                  // at d1 = a - 1/2 and d3 = a
+    if (near) {
+        ipe_sincos_small((a - 0.5) * piM, s1, c1);
+        ipe_sincos_small(a * piM, s3, c3);
+    } else {
+        s1 = sq_sinpi((a - 0.5) / M); c1 = sq_cospi((a - 0.5) / M);
+        s3 = sq_sinpi(a / M); c3 = sq_cospi(a / M);
+    }
+    const double d4 = a + K - 1.0;                          // last point; d2 = d4 + 1/2
+    const double s4 = sq_sinpi(d4 / M), c4 = sq_cospi(d4 / M);
+    double sh, ch;
+    ipe_sincos_small(0.5 * piM, sh, ch);
+    const double s2 = s4 * ch + c4 * sh, c2 = c4 * ch - s4 * sh;
+    const double inv = 1.0 / (PI * M);
+    const double f3 = 1.0 / ((M * s3) * (M * s3)), f4 = 1.0 / ((M * s4) * (M * s4));
+    hi = (c1 / s1 - c2 / s2) * inv;
+    lo = (c3 / s3 - c4 / s4) * inv + 0.5 * (f3 + f4);
+    // floating-point slack: the brackets are sums of O(10) correctly rounded operations on O(1) quantities
+    hi = hi * (1.0 + 1e-12) + 1e-300;
+    lo = lo * (1.0 - 1e-12);
+    if (lo < 0.0) lo = 0.0;
+}
+
+// The common case.  Returns IPE_DONE with the median's r in `med`, or who should take the pair.
+__host__ __device__ inline int ipe_lean(const IpeGrid& g, double V, double& med) {
+    const double M = g.M, t = g.t, j0 = g.j0;
+    if (!(M >= 32.0 && j0 >= 4.0 && 2.0 * (j0 + 4.0) < M)) return IPE_GENERAL;
+    // mirror images of the window points sit at distances t + 2 j0 - 3 .. t + 2 j0 + 4; sin(pi d/M) >= 2 min(d, M - d)/M
+    const double m = fmin(t + 2.0 * j0 - 3.0, M - (t + 2.0 * j0 + 4.0));
+    if (!(m >= 4.0)) return IPE_GENERAL;
+    const double st = sq_sinpi(t), s2 = st * st;
+    const double mu = 2.0 * s2 / (m * m);                   // >= the 8 mirror weights together
+    if (mu > 1e-4) return IPE_GENERAL;
+    double w[8];
+    ipe_window(M, t, s2, w);
+    double blo, bhi;
+    ipe_run_bracket(M, t + 4.0, 2.0 * j0 - 7.0, true, blo, bhi);
+    blo *= s2; bhi *= s2;
+    const double c0 = w[0], c1 = c0 + w[1], c2 = c1 + w[2], c3 = c2 + w[3], c4 = c3 + w[4], c5 = c4 + w[5],
+                 c6 = c5 + w[6], c7 = c6 + w[7];
+    const double up = bhi + mu * (1.0 + 1e-12) + 1e-15;     // added to cum_i for the upper end of F_i
+    const double dn = blo - 1e-15;
+    // a median below or above the window: plain summation
+    if (V <= ipe_G(up - mu) || V > ipe_G(dn + c7)) return IPE_BRUTE;
+    // smallest i in 0..7 with V <= G(F_i)  (V <= G(F_7) holds)
+    int i = 0;
+    {
+        const bool a3 = V <= ipe_G(dn + c3), b3 = V > ipe_G(up + c3);
+        if (a3 == b3) return IPE_TIGHTEN;
+        const double cq = a3 ? c1 : c5;
+        const bool a2 = V <= ipe_G(dn + cq), b2 = V > ipe_G(up + cq);
+        if (a2 == b2) return IPE_TIGHTEN;
+        const double cr = a3 ? (a2 ? c0 : c2) : (a2 ? c4 : c6);
+        const bool a1 = V <= ipe_G(dn + cr), b1 = V > ipe_G(up + cr);
+        if (a1 == b1) return IPE_TIGHTEN;
+        i = (a3 ? 0 : 4) + (a2 ? 0 : 2) + (a1 ? 0 : 1);
+    }
+    med = j0 - 3.0 + (double)i;
+    return IPE_DONE;
+}
+
+// The inversion by plain summation: smallest r with V <= G(F(r)).  O(r) - for the rare pairs only.
+__host__ __device__ inline double ipe_brute(const IpeGrid& g, double V) {
+    const double M = g.M, x = g.x;
+    const double st = sq_sinpi(g.t), s2 = st * st;
+    const double rmax = floor(M * 0.5);
+    double F = 0.0;
+    for (double r = 0.0; r <= rmax; r += 1.0) {
+        double P = ipe_f(M, fabs(r - x));
+        if (r > 0.0 && 2.0 * r < M) P += ipe_f(M, r + x);   // the mirror image M - r, at distance r + x going left
+        F += s2 * P;
+        if (V <= ipe_G(F)) return r;
+    }
+    return rmax;
+}
+
+// Same decisions as ipe_lean with the mirror weights exact and the bracket of B tightened by peeling exact terms
+// off both ends of its run (term k and term K-1-k together are the weight of r = j0 - 4 - k).  Returns IPE_DONE
+// or IPE_BRUTE (the median left the window).
+__host__ __device__ inline int ipe_tighten(const IpeGrid& g, double V, double& med) {
+    const double M = g.M, t = g.t, j0 = g.j0;
+    const double st = sq_sinpi(t), s2 = st * st;
+    double w[8], c[8];
+    ipe_window(M, t, s2, w);
+    double acc = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        acc += w[i] + s2 * ipe_f(M, t + 2.0 * j0 - 3.0 + (double)i);      // + the mirror image of the point
+        c[i] = acc;
+    }
+    const double a = t + 4.0, K = 2.0 * j0 - 7.0;
+    double peeled = 0.0, n = 0.0;                          // terms 0..n-1 and K-n..K-1 are in `peeled`
+    double target = 8.0;
+    while (true) {
+        while (n < target && 2.0 * n < K) {
+            const double lo_d = a + n, hi_d = a + K - 1.0 - n;
+            peeled += ipe_f(M, lo_d);
+            if (hi_d > lo_d) peeled += ipe_f(M, hi_d);
+            n += 1.0;
+        }
+        const double rest = K - 2.0 * n;                   // terms n .. K-1-n are still bracketed
+        double blo = 0.0, bhi = 0.0;
+        if (rest >= 1.0) ipe_run_bracket(M, a + n, rest, false, blo, bhi);
+        const double dn = (peeled + blo) * s2 * (1.0 - 1e-12) - 1e-16;
+        const double up = (peeled + bhi) * s2 * (1.0 + 1e-12) + 1e-16;
+        const bool exact = !(rest >= 1.0);
+        if (V <= ipe_G(up) || V > ipe_G(dn + c[7])) {
+            // possibly outside the window; certain once the bracket has closed
+            if (exact || (V <= ipe_G(dn)) || (V > ipe_G(up + c[7]))) return IPE_BRUTE;
+        } else {
+            int i = 0;
+            bool sure = true;
+#pragma unroll
+            for (int p = 0; p < 7; ++p) {                  // first i with V <= G(F_i); F_7 holds
+                const bool le_lo = V <= ipe_G(dn + c[p]), le_hi = V <= ipe_G(up + c[p]);
+                if (le_lo != le_hi) sure = false;
+                if (!le_hi && i == p) i = p + 1;
+            }
+            if (sure || exact) { med = j0 - 3.0 + (double)i; return IPE_DONE; }
+        }
+        if (exact) { med = j0 - 3.0; return IPE_DONE; }    // not reached
+        target *= 8.0;
+    }
+}
+
+// the estimate |x|^2 + |c|^2 - 2 ipe(x, c) from the median's r (Utility.py:733-734, :520-531)
+__host__ __device__ inline double ipe_value(const IpeGrid& g, double med) {
+    const double sn = sq_sinpi(med / g.M);
+    return 2.0 * g.S * sn * sn;
+}
+
+}  // namespace sq

@@ -30,6 +30,7 @@
 #include "sqb200.h"
 #include "fejer.cuh"
 #include "ipe.cuh"
+#include "ipe_lean.cuh"
 #include "binomial.cuh"
 #include <cstdlib>
 #include <cmath>
@@ -335,10 +336,12 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 const int pairs = rows * kk;
                 const int rounds = (pairs + Cfg::THREADS - 1) / Cfg::THREADS;
                 // (the dot product of the next round is fetched while this round's estimate is computed)
-                // Pass 1 runs the lean estimator; the few pairs it cannot take (tiny grid, window wrapping around
-                // 0 or M/2, a tail draw inside the window's range) are listed and done by the general one in
-                // pass 2, all together: the common path stays small and uniform.
+                // Pass 1, one pair per lane: the median of the 13 amplitude-estimation outcomes by one inversion
+                // (ipe_lean.cuh).  Pairs it declines before looking at its uniform (tiny grid, window touching 0 or
+                // M/2) are listed for the general estimator of ipe.cuh; pairs whose uniform falls inside the
+                // bracket of a threshold (0.3 %) are listed for the same inversion with the bracket tightened.
                 int* list = reinterpret_cast<int*>(sc + BM * BN);
+                constexpr int IPE_RESOLVE = 1 << 30;               // list flag: finish the inversion (same uniform)
                 if (tid == 0) *ipe_cnt = 0;
                 __syncthreads();
                 int row = 0, cl = 0;
@@ -351,24 +354,55 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     const bool ok2 = idx2 < pairs;
                     const int row2 = ok2 ? idx2 / kk : 0, cl2 = ok2 ? idx2 - row2 * kk : 0;
                     const double dot2 = sc[row2 * BN + cl2];
-                    const double xn = xn_s[row];
-                    bool defer;
-                    const double v = ipe_estimate_warp<true>(dot, xn, ok ? cn_s[n0 + cl] : 0.0, 0.5 * a.delta, ok,
-                                                             a.seed, a.offset + (unsigned long long)(r0 + row),
-                                                             (unsigned)(n0 + cl), a.ipe_force_replay != 0, defer);
                     if (ok) {
-                        if (defer) list[atomicAdd(ipe_cnt, 1)] = row * BN + cl;
-                        else sc[row * BN + cl] = v - xn;
+                        const double xn = xn_s[row];
+                        IpeGrid g;
+                        ipe_grid(dot, xn, cn_s[n0 + cl], 0.5 * a.delta, g);
+                        double v = 0.0;
+                        int st = IPE_DONE;
+                        if (g.kind == 1) v = ipe_value(g, fmin(g.j0, g.M - g.j0));      // weight 1 at distance 0 (Utility.py:500-501)
+                        else if (g.kind == 2) {
+                            if (a.ipe_force_replay) st = IPE_GENERAL;
+                            else {
+                                Philox rng(a.seed, a.offset + (unsigned long long)(r0 + row), IPE_TAG_MAIN, (unsigned)(n0 + cl));
+                                double u0, V, med = 0.0;
+                                rng.uniform2(u0, V);
+                                st = ipe_lean(g, V, med);
+                                if (st == IPE_DONE) v = ipe_value(g, med);
+                            }
+                        }
+                        if (st == IPE_DONE) sc[row * BN + cl] = v - xn;
+                        else list[atomicAdd(ipe_cnt, 1)] = (row * BN + cl) | (st == IPE_GENERAL ? 0 : IPE_RESOLVE);
                     }
                     row = row2; cl = cl2; ok = ok2; dot = dot2;
                 }
                 __syncthreads();
                 const int ndef = *ipe_cnt;
+                // Pass 2a: finish the inversions (per lane; tens of pairs per tile, dealt to the warps first so that
+                // they run side by side instead of one after the other in the lanes of one warp)
+#pragma unroll 1
+                for (int li = lane * (Cfg::THREADS / 32) + warp; li < ndef; li += Cfg::THREADS) {
+                    const int e = list[li];
+                    if (!(e & IPE_RESOLVE)) continue;
+                    const int pos = e & (IPE_RESOLVE - 1), rowd = pos / BN, cld = pos - rowd * BN;
+                    const double xn = xn_s[rowd];
+                    IpeGrid g;
+                    ipe_grid(sc[pos], xn, cn_s[n0 + cld], 0.5 * a.delta, g);
+                    Philox rng(a.seed, a.offset + (unsigned long long)(r0 + rowd), IPE_TAG_MAIN, (unsigned)(n0 + cld));
+                    double u0, V, med = 0.0;
+                    rng.uniform2(u0, V);
+                    int st = ipe_lean(g, V, med);
+                    if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
+                    if (st == IPE_BRUTE) med = ipe_brute(g, V);
+                    sc[pos] = ipe_value(g, med) - xn;
+                }
+                // Pass 2b: the general estimator (warp-cooperative: every lane of a warp calls it together)
 #pragma unroll 1
                 for (int it = 0; it * Cfg::THREADS < ndef; ++it) {
                     const int li = it * Cfg::THREADS + tid;
-                    const bool okd = li < ndef;
-                    const int pos = okd ? list[li] : 0;
+                    const int e = li < ndef ? list[li] : IPE_RESOLVE;
+                    const bool okd = !(e & IPE_RESOLVE);
+                    const int pos = okd ? e : 0;
                     const int rowd = pos / BN, cld = pos - rowd * BN;
                     const double xn = xn_s[rowd];
                     bool defer;

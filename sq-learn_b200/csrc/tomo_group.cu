@@ -213,7 +213,7 @@ __global__ void __launch_bounds__(GT, 1024 / GT) tomo_group_kernel(TomoGroupArgs
             if (i >= d) return 0.0;
             const double p = Eg[v * d + i];
             const double c2 = ws[v * wsv + L + i];
-            const double est = (s_div[v] == 0.0) ? 0.0 : ((c2 > 0.4 * p * p * N) ? p : -p);
+            const double est = (s_div[v] == 0.0) ? 0.0 : ((c2 > tomo_sign_threshold(p, N)) ? p : -p);
             Eg[v * d + i] = est;
             return vin(v, i) - est;
         };

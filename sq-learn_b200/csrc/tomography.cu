@@ -442,7 +442,7 @@ __global__ void __launch_bounds__(MAXT, MINB) tomo_fused_kernel(TomoArgs a) {
         auto sign_and_diff = [&](int i) {
             double p = P[i];
             double c2 = direct ? (double)cnt_i[i] : cnt[L + i];
-            double est = (c2 > 0.4 * p * p * N) ? p : -p;
+            double est = (c2 > tomo_sign_threshold(p, N)) ? p : -p;
             P[i] = est;
             return (i < d) ? vin(i) - est : 0.0;
         };
@@ -719,7 +719,7 @@ __global__ void tomo_big_block_kernel(TomoBigArgs a, int stage) {
         for (int i = tid; i < TB; i += T) {
             int g = blk * TB + i;
             double p = P[i];
-            double est = (cnt[TB + i] > 0.4 * p * p * a.N) ? p : -p;
+            double est = (cnt[TB + i] > tomo_sign_threshold(p, a.N)) ? p : -p;
             if (g < a.d) {
                 a.est[base + i] = est;
                 double df = v[i] - est;

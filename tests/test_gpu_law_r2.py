@@ -26,6 +26,12 @@ def prob():
     return np.load(os.path.join(GOLDEN, "r2_problems.npz"))
 
 
+def _ks(a, b):
+    """two-sample KS on values rounded to 8 decimals: with few measurements the errors live on atoms, and the same
+    atom summed in two different orders differs in the last bit - unrounded, its whole mass would show up as a gap"""
+    return stats.ks_2samp(np.round(np.asarray(a, dtype=float), 8), np.round(np.asarray(b, dtype=float), 8)).pvalue
+
+
 def _same_discrete_law(a, b):
     """chi-square test of homogeneity for two samples of a discrete variable (cells with few counts merged)"""
     vals = np.unique(np.concatenate([a, b]))
@@ -72,7 +78,7 @@ def test_tomography_law_against_reference_draws(cuda, ref, prob, name):
                                     stop=int(inc), seed=2026 + d, vec_offset=7)
     r_err, r_N = ref[name + "__err"], ref[name + "__N"]
     assert len(r_err) >= 400
-    assert stats.ks_2samp(err, r_err).pvalue > P_MIN
+    assert _ks(err, r_err) > P_MIN
     if inc:
         assert (err <= delta).all()                       # the stop rule: the returned attempt met the accuracy
         assert _same_discrete_law(n_used, r_N.astype(float)) > P_MIN
@@ -81,8 +87,8 @@ def test_tomography_law_against_reference_draws(cuda, ref, prob, name):
         if N is None:
             # theorem 4.1's guarantee, failure probability far inside 1/poly(d)
             assert (err > delta).mean() < 1e-3 and (r_err > delta).mean() < 1e-2
-    assert stats.ks_2samp(est[:, 0], ref[name + "__c0"]).pvalue > P_MIN
-    assert stats.ks_2samp(est[:, 3], ref[name + "__c3"]).pvalue > P_MIN
+    assert _ks(est[:, 0], ref[name + "__c0"]) > P_MIN
+    assert _ks(est[:, 3], ref[name + "__c3"]) > P_MIN
     wrong = (np.sign(est) != np.sign(v)[None]).sum(axis=1)
     r_wrong = ref[name + "__signerr"]
     # mean number of wrong signs per trial (z-test on the means; the counts are small integers)
@@ -150,9 +156,9 @@ def test_error_injection_and_window_pick(cuda, ref, golden_stoch):
     from sqlearn import QuantumUtility as Q
     Q.seed(33)
     g = np.concatenate([Q.make_gaussian_est(np.zeros(8), 0.5) for _ in range(1250)])
-    assert stats.ks_2samp(g, ref["gauss__x"]).pvalue > P_MIN
+    assert _ks(g, ref["gauss__x"]) > P_MIN
     e = np.array([float(Q.introduce_error(1.5, 0.3)[0]) for _ in range(5000)])
-    assert stats.ks_2samp(e, ref["intro__x"]).pvalue > P_MIN
+    assert _ks(e, ref["intro__x"]) > P_MIN
     Xw, Cw = golden_stoch["window_X"], golden_stoch["window_C"]
     labels, _, _, _ = G.assign(np.repeat(Xw, 10000, axis=0), Cw, mode=1, delta=0.5, seed=34)
     mine, want = np.bincount(labels, minlength=4), np.bincount(ref["window__label"], minlength=4)
@@ -204,7 +210,7 @@ def test_quantum_state_api(cuda, ref):
         assert _same_discrete_law(np.round(w50[:, i] * 50), np.round(ref["qstate__wald50"][:, i] * 50)) > P_MIN
     cc = np.array([Q.coupon_collect(q) for _ in range(300)])
     assert cc.min() >= 6
-    assert stats.ks_2samp(cc, ref["qstate__coupon"]).pvalue > P_MIN
+    assert _ks(cc, ref["qstate__coupon"]) > P_MIN
 
 
 # ------------------------------------------------------------------ the noisy Lloyd loop
@@ -266,13 +272,13 @@ def test_noisy_lloyd_loop_follows_the_reference_law(cuda, lloyd_ref, prob, which
         np.testing.assert_allclose(its[:, 0], r_it[0, 0], atol=2e-3)
         assert np.allclose(r_it[:, 0], r_it[0, 0])
     if len(r_it) >= 100:
-        assert stats.ks_2samp(fin, g[key + "inertia"]).pvalue > P_MIN
+        assert _ks(fin, g[key + "inertia"]) > P_MIN
         for it in ((1, 2, max_iter - 1) if which == "w" else (0, 1, 2, max_iter - 1)):
-            assert stats.ks_2samp(its[:, it], r_it[:, it]).pvalue > P_MIN
+            assert _ks(its[:, it], r_it[:, it]) > P_MIN
         for it in (0, 1, max_iter - 1):
-            assert stats.ks_2samp(shifts[:, it], r_sh[:, it]).pvalue > P_MIN
+            assert _ks(shifts[:, it], r_sh[:, it]) > P_MIN
         r_sizes = np.sort(g[key + "label_counts"], axis=1)
-        assert stats.ks_2samp(np.array(sizes)[:, 0], r_sizes[:, 0]).pvalue > P_MIN
-        assert stats.ks_2samp(np.array(sizes)[:, -1], r_sizes[:, -1]).pvalue > P_MIN
+        assert _ks(np.array(sizes)[:, 0], r_sizes[:, 0]) > P_MIN
+        assert _ks(np.array(sizes)[:, -1], r_sizes[:, -1]) > P_MIN
     # the inflated inertia of SURVEY D5 reproduces: after the first update the inertia is far above iteration 0's
     assert np.median(its[:, 1]) > 1.5 * its[0, 0] and np.median(r_it[:, 1]) > 1.5 * r_it[0, 0]
