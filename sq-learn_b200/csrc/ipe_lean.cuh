@@ -46,6 +46,15 @@ __host__ __device__ inline double sq_cospi(double y) {
 #endif
 }
 
+__host__ __device__ inline void sq_sincospi(double y, double& sn, double& cs) {
+#ifdef __CUDA_ARCH__
+    sincospi(y, &sn, &cs);
+#else
+    sn = sin(3.14159265358979323846 * y);
+    cs = cos(3.14159265358979323846 * y);
+#endif
+}
+
 // a, epsilon_a, M, theta_a of ipe / amplitude_estimation (Utility.py:725-733, :484-493)
 __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, double eps, IpeGrid& g) {
     const double PI = 3.14159265358979323846;
@@ -58,7 +67,34 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
     if (a > 1.0) a = 1.0;
     const double eps_a = eps * fmax(1.0, fabs(dot)) / g.S;
     g.M = ceil((PI / (2.0 * eps_a)) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
-    g.x = g.M * (asin(sqrt(a)) / PI);
+    // theta_a = asin(sqrt(a)) (Utility.py:493).  With c = 1 - 2a = cos(2 theta_a), theta_a = pi/4 - asin(c)/2; for the
+    // usual pair (|x.c| a small fraction of |x|^2 + |c|^2) c is small and asin(c) is a short odd series - same
+    // accuracy as the library call (both are within an ulp or two of the true angle) at a fifth of the instructions.
+    double theta;
+    const double c = 1.0 - 2.0 * a;
+    if (fabs(c) < 0.25) {
+        const double u = c * c;
+        // asin(c) = c * sum_k  (2k)! / (4^k (k!)^2 (2k+1))  c^(2k); 14 terms: next one < 0.25^28 * 0.02 = 3e-19
+        // exact rational coefficients (2k)!/(4^k k!^2 (2k+1)), highest first
+        double Q = 10400600.0 / (67108864.0 * 27.0);
+        Q = fma(Q, u, 2704156.0 / (16777216.0 * 25.0));
+        Q = fma(Q, u, 705432.0 / (4194304.0 * 23.0));
+        Q = fma(Q, u, 184756.0 / (1048576.0 * 21.0));
+        Q = fma(Q, u, 48620.0 / (262144.0 * 19.0));
+        Q = fma(Q, u, 12870.0 / (65536.0 * 17.0));
+        Q = fma(Q, u, 3432.0 / (16384.0 * 15.0));
+        Q = fma(Q, u, 924.0 / (4096.0 * 13.0));
+        Q = fma(Q, u, 252.0 / (1024.0 * 11.0));
+        Q = fma(Q, u, 70.0 / (256.0 * 9.0));
+        Q = fma(Q, u, 20.0 / (64.0 * 7.0));
+        Q = fma(Q, u, 6.0 / (16.0 * 5.0));
+        Q = fma(Q, u, 2.0 / (4.0 * 3.0));
+        Q = fma(Q, u, 1.0);
+        theta = 0.25 * PI - 0.5 * (c * Q);
+    } else {
+        theta = asin(sqrt(a));
+    }
+    g.x = g.M * (theta / PI);
     g.j0 = floor(g.x);
     g.t = g.x - g.j0;
     g.kind = (g.t == 0.0) ? 1 : 2;
@@ -67,6 +103,20 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
 // P(Binomial(13, F) >= 7) = F^7 sum_{i=0}^{6} C(6 + i, i) (1 - F)^i
 __host__ __device__ inline double ipe_G(double F) {
     F = fmin(fmax(F, 0.0), 1.0);
+    const double q = 1.0 - F;
+    double s = 924.0;
+    s = fma(s, q, 462.0);
+    s = fma(s, q, 210.0);
+    s = fma(s, q, 84.0);
+    s = fma(s, q, 28.0);
+    s = fma(s, q, 7.0);
+    s = fma(s, q, 1.0);
+    const double F2 = F * F, F4 = F2 * F2;
+    return F4 * F2 * F * s;
+}
+
+// the same without the clamp, for arguments already within rounding of [0, 1]
+__host__ __device__ inline double ipe_G_raw(double F) {
     const double q = 1.0 - F;
     double s = 924.0;
     s = fma(s, q, 462.0);
@@ -139,7 +189,8 @@ __host__ __device__ inline void ipe_sincos_small(double y, double& s, double& c)
 
 // Bracket of  sum_{k=0}^{K-1} f(a + k)  for the convex f above (K >= 1, 1/2 < a, a + K - 1/2 < M).
 // near = true: the near end (a - 1/2, a) is within 0.5 rad of 0 and is done by Taylor series.
-__host__ __device__ inline void ipe_run_bracket(double M, double a, double K, bool near, double& lo, double& hi) {
+__host__ __device__ inline void ipe_run_bracket(double M, double a, double K, bool near, double& lo, double& hi,
+                                                double& s4, double& c4) {
     const double PI = 3.14159265358979323846;
     const double piM = PI / M;
     double s1, c1, s3, c3;                                  // at d1 = a - 1/2 and d3 = a
@@ -151,14 +202,16 @@ __host__ __device__ inline void ipe_run_bracket(double M, double a, double K, bo
         s3 = sq_sinpi(a / M); c3 = sq_cospi(a / M);
     }
     const double d4 = a + K - 1.0;                          // last point; d2 = d4 + 1/2
-    const double s4 = sq_sinpi(d4 / M), c4 = sq_cospi(d4 / M);
+    const double invM = 1.0 / M;
+    sq_sincospi(d4 * invM, s4, c4);                         // (handed back: the mirror weights start from here)
     double sh, ch;
     ipe_sincos_small(0.5 * piM, sh, ch);
     const double s2 = s4 * ch + c4 * sh, c2 = c4 * ch - s4 * sh;
-    const double inv = 1.0 / (PI * M);
-    const double f3 = 1.0 / ((M * s3) * (M * s3)), f4 = 1.0 / ((M * s4) * (M * s4));
-    hi = (c1 / s1 - c2 / s2) * inv;
-    lo = (c3 / s3 - c4 / s4) * inv + 0.5 * (f3 + f4);
+    // cot(y1) - cot(y2) = sin(y2 - y1) / (sin y1 sin y2): one division per bracket end
+    const double inv = invM * (1.0 / PI);
+    const double p34 = s3 * s4;
+    hi = (s2 * c1 - c2 * s1) / (s1 * s2) * inv;
+    lo = ((s4 * c3 - c4 * s3) * p34 * (M * (1.0 / PI)) + 0.5 * (s3 * s3 + s4 * s4)) / (p34 * p34) * (invM * invM);
     // floating-point slack: the brackets are sums of O(10) correctly rounded operations on O(1) quantities
     hi = hi * (1.0 + 1e-12) + 1e-300;
     lo = lo * (1.0 - 1e-12);
@@ -174,28 +227,56 @@ __host__ __device__ inline int ipe_lean(const IpeGrid& g, double V, double& med)
     if (!(m >= 4.0)) return IPE_GENERAL;
     const double st = sq_sinpi(t), s2 = st * st;
     const double mu = 2.0 * s2 / (m * m);                   // >= the 8 mirror weights together
-    if (mu > 1e-4) return IPE_GENERAL;
     double w[8];
     ipe_window(M, t, s2, w);
-    double blo, bhi;
-    ipe_run_bracket(M, t + 4.0, 2.0 * j0 - 7.0, true, blo, bhi);
+    double blo, bhi, s4, c4;
+    ipe_run_bracket(M, t + 4.0, 2.0 * j0 - 7.0, true, blo, bhi, s4, c4);
     blo *= s2; bhi *= s2;
-    const double c0 = w[0], c1 = c0 + w[1], c2 = c1 + w[2], c3 = c2 + w[3], c4 = c3 + w[4], c5 = c4 + w[5],
-                 c6 = c5 + w[6], c7 = c6 + w[7];
-    const double up = bhi + mu * (1.0 + 1e-12) + 1e-15;     // added to cum_i for the upper end of F_i
+    double c0 = w[0], c1 = c0 + w[1], c2 = c1 + w[2], c3 = c2 + w[3], c4_ = c3 + w[4], c5 = c4_ + w[5],
+           c6 = c5 + w[6], c7 = c6 + w[7];
+    double up = bhi + 1e-15;                                // added to cum_i for the upper end of F_i
     const double dn = blo - 1e-15;
+    if (mu > 1e-6) {
+        // sizeable mirror images (small grid, or x near 0 / M/2): their weights exactly.  They sit at the distances
+        // d4 + 1 + i (d4 = t + 2 j0 - 4 is the far end of the run below the window): rotate (sin, cos) of pi d4 / M
+        // by pi / M eight times; one division for the eight reciprocals.
+        double sh, ch;
+        ipe_sincos_small(3.14159265358979323846 / M, sh, ch);
+        double sn = s4, cs = c4, pm[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const double s_ = sn * ch + cs * sh, c_ = cs * ch - sn * sh;
+            sn = s_; cs = c_;
+            const double ms = M * sn;
+            pm[i] = ms * ms;
+        }
+        const double a01 = pm[0] * pm[1], a23 = pm[2] * pm[3], a45 = pm[4] * pm[5], a67 = pm[6] * pm[7];
+        const double lo4 = a01 * a23, hi4 = a45 * a67;
+        const double r = s2 / (lo4 * hi4);
+        const double rl = r * hi4, rh = r * lo4;
+        const double r01 = rl * a23, r23 = rl * a01, r45 = rh * a67, r67 = rh * a45;
+        const double m0 = r01 * pm[1], m1 = r01 * pm[0], m2 = r23 * pm[3], m3 = r23 * pm[2];
+        const double m4 = r45 * pm[5], m5 = r45 * pm[4], m6 = r67 * pm[7], m7 = r67 * pm[6];
+        double acc = m0;
+        c0 += acc; acc += m1; c1 += acc; acc += m2; c2 += acc; acc += m3; c3 += acc;
+        acc += m4; c4_ += acc; acc += m5; c5 += acc; acc += m6; c6 += acc; acc += m7; c7 += acc;
+        up += 1e-14;                                        // rounding of the rotations
+    } else {
+        up += mu * (1.0 + 1e-12);
+    }
+    const double umu = (mu > 1e-6) ? 0.0 : mu;              // what `up` carries on top of B's upper end
     // a median below or above the window: plain summation
-    if (V <= ipe_G(up - mu) || V > ipe_G(dn + c7)) return IPE_BRUTE;
+    if (V <= ipe_G_raw(up - umu) || V > ipe_G_raw(dn + c7)) return IPE_BRUTE;
     // smallest i in 0..7 with V <= G(F_i)  (V <= G(F_7) holds)
     int i = 0;
     {
-        const bool a3 = V <= ipe_G(dn + c3), b3 = V > ipe_G(up + c3);
+        const bool a3 = V <= ipe_G_raw(dn + c3), b3 = V > ipe_G_raw(up + c3);
         if (a3 == b3) return IPE_TIGHTEN;
         const double cq = a3 ? c1 : c5;
-        const bool a2 = V <= ipe_G(dn + cq), b2 = V > ipe_G(up + cq);
+        const bool a2 = V <= ipe_G_raw(dn + cq), b2 = V > ipe_G_raw(up + cq);
         if (a2 == b2) return IPE_TIGHTEN;
-        const double cr = a3 ? (a2 ? c0 : c2) : (a2 ? c4 : c6);
-        const bool a1 = V <= ipe_G(dn + cr), b1 = V > ipe_G(up + cr);
+        const double cr = a3 ? (a2 ? c0 : c2) : (a2 ? c4_ : c6);
+        const bool a1 = V <= ipe_G_raw(dn + cr), b1 = V > ipe_G_raw(up + cr);
         if (a1 == b1) return IPE_TIGHTEN;
         i = (a3 ? 0 : 4) + (a2 ? 0 : 2) + (a1 ? 0 : 1);
     }
@@ -244,7 +325,8 @@ __host__ __device__ inline int ipe_tighten(const IpeGrid& g, double V, double& m
         }
         const double rest = K - 2.0 * n;                   // terms n .. K-1-n are still bracketed
         double blo = 0.0, bhi = 0.0;
-        if (rest >= 1.0) ipe_run_bracket(M, a + n, rest, false, blo, bhi);
+        double s4u, c4u;
+        if (rest >= 1.0) ipe_run_bracket(M, a + n, rest, false, blo, bhi, s4u, c4u);
         const double dn = (peeled + blo) * s2 * (1.0 - 1e-12) - 1e-16;
         const double up = (peeled + bhi) * s2 * (1.0 + 1e-12) + 1e-16;
         const bool exact = !(rest >= 1.0);
@@ -269,7 +351,7 @@ __host__ __device__ inline int ipe_tighten(const IpeGrid& g, double V, double& m
 
 // the estimate |x|^2 + |c|^2 - 2 ipe(x, c) from the median's r (Utility.py:733-734, :520-531)
 __host__ __device__ inline double ipe_value(const IpeGrid& g, double med) {
-    const double sn = sq_sinpi(med / g.M);
+    const double sn = sq_sinpi(med / g.M);   // (kept as a true division: the estimate is the reference's sin^2(pi j / M))
     return 2.0 * g.S * sn * sn;
 }
 

@@ -347,12 +347,15 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 int row = 0, cl = 0;
                 bool ok = tid < pairs;
                 if (ok) { row = tid / kk; cl = tid - row * kk; }
+                const int drow = Cfg::THREADS / kk, dcl = Cfg::THREADS - drow * kk;     // one round further on
                 double dot = sc[row * BN + cl];
 #pragma unroll 1
                 for (int it = 0; it < rounds; ++it) {
                     const int idx2 = (it + 1) * Cfg::THREADS + tid;
                     const bool ok2 = idx2 < pairs;
-                    const int row2 = ok2 ? idx2 / kk : 0, cl2 = ok2 ? idx2 - row2 * kk : 0;
+                    int row2 = row + drow, cl2 = cl + dcl;
+                    if (cl2 >= kk) { cl2 -= kk; ++row2; }
+                    if (!ok2) { row2 = 0; cl2 = 0; }
                     const double dot2 = sc[row2 * BN + cl2];
                     if (ok) {
                         const double xn = xn_s[row];
