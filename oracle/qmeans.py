@@ -21,9 +21,15 @@ def cdist_sq(X, C):
     return r * r
 
 
-def labels_estimation(X, centers, delta, true_distance_estimate, rng):
-    """_dmeans.py:732-777.  Returns (labels, distances, inertia)."""
-    D = cdist_sq(X, centers)
+def labels_estimation(X, centers, delta, true_distance_estimate, rng, scipy_cdist=False):
+    """_dmeans.py:732-777.  Returns (labels, distances, inertia).  ``scipy_cdist`` calls scipy's compiled cdist as
+    the reference does (:736) instead of the operation-order restatement above - same values (checked in the
+    tests), an order of magnitude faster; bench.py times this one."""
+    if scipy_cdist:
+        from scipy.spatial.distance import cdist
+        D = np.square(cdist(X, centers, "euclidean"))
+    else:
+        D = cdist_sq(X, centers)
     if delta > 0:
         if not true_distance_estimate:
             mins = D.min(axis=1)

@@ -284,8 +284,9 @@ def _tomography_device(V, delta, N, norm, stop, incremental, fmi, trace=False, v
     if stop and incremental and len(sched) > 1 and not trace and B <= 2048:
         # few vectors: the latency of the attempt-by-attempt search dominates; 8 attempt lanes per vector search
         # the schedule together and the lane that finishes last replays the first successful attempt (one launch)
+        lanes = 8        # (any number of lanes gives the same bits; 8 measured fastest from 16 to 256 vectors)
         _cabi.check(_cabi.lib.sq_tomography_batched_spec_fused(
-            dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, sched.ctypes.data, len(sched), 8, seed_,
+            dv.ptr(V), B, d, float(delta), 1 if norm == 'inf' else 0, sched.ctypes.data, len(sched), lanes, seed_,
             vec_offset, dv.ptr(est), dv.ptr(n_used), dv.ptr(err), None, dv.ptr(_spec_state(B)), dv.stream_ptr()),
             "sq_tomography_batched_spec_fused")
         return est, n_used, err, tr, att, sched

@@ -1,5 +1,7 @@
 """Device plumbing: torch owns memory, streams and the process group; the
 kernels are reached through :mod:`sqlearn._cabi` only."""
+import os
+
 import numpy as np
 import torch
 
@@ -34,11 +36,41 @@ def to_device(a, dtype=torch.float64, pin=False):
     return t.to(dev, non_blocking=pin)
 
 
+_STAGE_THREADS = max(1, int(os.environ.get("SQ_STAGE_THREADS", "4")))   # host threads per rank for the staging copy
+_stage_pool = None
+
+
+def _stage_threads():
+    """4 threads move 19 GB/s on the B200 box's host (one: 6 GB/s); with several ranks on one node the cores are
+    shared, so each rank takes its share."""
+    world = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")) or 1)
+    return max(1, min(_STAGE_THREADS, (os.cpu_count() or 1) // max(world, 1)))
+
+
+def _staged_copy(dst, src):
+    """pageable -> pinned copy of one chunk, cut into row slices copied by a few host threads (numpy's copy
+    releases the GIL and does not depend on the OpenMP thread count, which torchrun pins to one per rank)"""
+    global _stage_pool
+    rows = src.shape[0]
+    nthr = _stage_threads()
+    if nthr == 1 or rows < 4 * nthr or src.numel() < (8 << 20):
+        dst.copy_(src)
+        return
+    if _stage_pool is None:
+        from concurrent.futures import ThreadPoolExecutor
+        _stage_pool = ThreadPoolExecutor(max_workers=_STAGE_THREADS)
+    dn, sn = dst.numpy(), src.numpy()
+    step = (rows + nthr - 1) // nthr
+    futs = [_stage_pool.submit(np.copyto, dn[a:a + step], sn[a:a + step]) for a in range(0, rows, step)]
+    for f in futs:
+        f.result()
+
+
 def stream_to_device(a, on_chunk=None, chunk_bytes=256 << 20):
     """Host matrix [n, d] (float64) -> device tensor, copied in row chunks on a side stream; ``on_chunk(out, r0,
     r1)`` is called once per chunk with the current stream already waiting for that chunk, so the caller's
     kernels on rows [r0, r1) overlap the copy of the next chunk.  Pageable input is staged through two pinned
-    chunk buffers instead of pinning (and copying) the whole array."""
+    chunk buffers (filled by a few host threads) instead of pinning - and copying - the whole array."""
     dev = require_cuda()
     t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64))
     n, d = t.shape
@@ -63,7 +95,7 @@ def stream_to_device(a, on_chunk=None, chunk_bytes=256 << 20):
                 slot = c % len(ring)
                 if ring_ev[slot] is not None:
                     ring_ev[slot].synchronize()       # the buffer's previous upload has left the host
-                ring[slot][:r1 - r0].copy_(t[r0:r1])
+                _staged_copy(ring[slot][:r1 - r0], t[r0:r1])
                 out[r0:r1].copy_(ring[slot][:r1 - r0], non_blocking=True)
                 ring_ev[slot] = torch.cuda.Event()
                 ring_ev[slot].record(copy)
