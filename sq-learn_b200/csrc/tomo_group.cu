@@ -22,6 +22,7 @@ namespace sq {
 
 static const int GCH = 4;            // nodes per thread and chunk of a level
 static const int GMAXV = 1024;       // most vectors in a group
+static const int GBMAX = 32;         // most (vector, block) members in a group of the long-vector kernel
 
 // sum_{i<L} f(v, i) for every vector v of the group, in canon_sum's order (tomography.cu): partial[i] = f(i) +
 // f(i + L/2), then partial[i] += partial[i + s] for s = L/4, L/8, ..., 1.  Partials of vector v at scr + v * stride
@@ -70,9 +71,10 @@ __device__ __forceinline__ void group_build(double* ws, int wsv, int Gc, int L, 
 
 // top-down splitting of every tree of the group; tree[v][1] holds the count to split.  Counts overwrite the
 // masses in place (a node reads its two child masses right before it stores the two child counts).
-template <int GT>
+// vec_of(v) / key_of(v): the Philox stream identity of member v's tree (vector id; node-id offset)
+template <int GT, class VecOf, class KeyOf>
 __device__ __forceinline__ void group_split(double* ws, int wsv, int Gc, int logL, int tid, unsigned long long seed,
-                                            unsigned long long vec0, unsigned stream, int* list, int* ctr) {
+                                            VecOf vec_of, KeyOf key_of, unsigned stream, int* list, int* ctr) {
     const int lane = tid & 31;
     int flip = 0;                                  // two pairs of counters, used by alternate chunks
     if (tid == 0) { ctr[0] = 0; ctr[1] = 0; ctr[2] = 0; ctr[3] = 0; }
@@ -95,7 +97,7 @@ __device__ __forceinline__ void group_split(double* ws, int wsv, int Gc, int log
                     double left = 0.0;
                     if (n > 0.0) {
                         const double2 m = *reinterpret_cast<const double2*>(t + 2 * i);
-                        Philox rng(seed, vec0 + (unsigned long long)v, stream, (unsigned)i);
+                        Philox rng(seed, vec_of(v), stream, key_of(v) + (unsigned)i);
                         st = binomial_head(n, m.x, m.y, rng, left);
                     }
                     if (st == BINOM_DONE) *reinterpret_cast<double2*>(t + 2 * i) = make_double2(left, n - left);
@@ -123,7 +125,7 @@ __device__ __forceinline__ void group_split(double* ws, int wsv, int Gc, int log
                 double* t = ws + v * wsv;
                 const double n = t[i];
                 const double2 m = *reinterpret_cast<const double2*>(t + 2 * i);
-                Philox rng(seed, vec0 + (unsigned long long)v, stream, (unsigned)i);
+                Philox rng(seed, vec_of(v), stream, key_of(v) + (unsigned)i);
                 const double left = binomial_split(n, m.x, m.y, rng);
                 *reinterpret_cast<double2*>(t + 2 * i) = make_double2(left, n - left);
             }
@@ -206,7 +208,8 @@ __global__ void __launch_bounds__(GT, 1024 / GT) tomo_group_kernel(TomoGroupArgs
                     t[1] = c;
                 }
             }
-            group_split<GT>(ws, wsv, Gc, logL, tid, a.seed, vec0, stage == 0 ? st1 : st2, list, ctr);
+            group_split<GT>(ws, wsv, Gc, logL, tid, a.seed, [&](int v) { return vec0 + (unsigned long long)v; },
+                            [](int) { return 0u; }, stage == 0 ? st1 : st2, list, ctr);
         }
         // ---- sign rule, estimate, error ----
         auto sign_and_diff = [&](int v, int i) {
@@ -237,6 +240,124 @@ __global__ void __launch_bounds__(GT, 1024 / GT) tomo_group_kernel(TomoGroupArgs
             a.err[g0 + v] = zero ? 0.0 : (a.norm_inf ? s_aux[v] : sqrt(s_aux[v]));
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Long vectors (d > 4096): the leaf blocks of tomography.cu's block path, handled the same way.  A member of a
+// group is one (vector, block of 1024 leaves); its tree lives in the workspace, its root count comes from the top
+// kernel, its node streams are keyed (vector, 4*attempt + {1, 3}, block * 2048 + node) exactly as
+// tomo_big_block_kernel keys them.  Per-member sums (masses of stage 2, the sign-free lower bound, the error) are
+// taken by one warp per member in an order fixed by the block alone, so nothing depends on the grouping.
+template <int GT>
+__global__ void __launch_bounds__(GT, 1024 / GT) tomo_blockgroup_kernel(TomoBlockGroupArgs a) {
+    constexpr int TBL = 1024, TBLOG = 10;
+    __shared__ int list[GT * GCH];
+    __shared__ int ctr[4];
+    __shared__ long long s_b[GBMAX];
+    __shared__ int s_blk[GBMAX];
+    __shared__ double s_div[GBMAX];      // 0: member idle (vector done / hopeless attempt / stage 2 skipped / zero vector)
+    __shared__ double s_cnt[GBMAX];      // measurements that fall in the member's block
+    __shared__ int s_act[GBMAX];         // members with measurements to split: slot -> member
+    __shared__ int s_slot[GBMAX];        // member -> slot (-1: none; all its leaf counts are zero)
+    __shared__ int s_nact;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, G = a.G;
+    const int wsv = 2 * TBL;
+    double* ws = a.gws + (size_t)blockIdx.x * G * wsv;
+    const double N = a.N;
+    const long long total = a.B * (long long)a.nown;
+    const unsigned stream = (unsigned)(4 * a.at + (a.stage == 1 ? 1 : 3));
+    for (long long g0 = (long long)blockIdx.x * G; g0 < total; g0 += (long long)gridDim.x * G) {
+        const int Gc = (int)((total - g0 < G) ? (total - g0) : G);
+        __syncthreads();
+        if (tid == 0) {
+            // (G <= 32 members: one thread lists them in order, so the slots do not depend on timing)
+            int na = 0;
+            for (int v = 0; v < Gc; ++v) {
+                const long long m = g0 + v, b = m / a.nown;
+                const int blk = a.blk_lo + (int)(m - b * a.nown);
+                const double ss = a.sumsq[b], nrm = sqrt(ss);
+                const bool zero = !(nrm > 0.0), keep = fabs(nrm - 1.0) <= (1e-8 + 1e-2);
+                const bool idle = zero || a.done[b] || (a.may_skip && N < a.nhop[b]) || (a.stage == 2 && a.skip2[b]);
+                s_b[v] = b; s_blk[v] = blk;
+                s_div[v] = idle ? 0.0 : (keep ? 1.0 : nrm);
+                const double c = idle ? 0.0 : a.bcnt[b * a.nblk + blk];
+                s_cnt[v] = c;
+                s_slot[v] = -1;
+                if (c > 0.0) { s_slot[v] = na; s_act[na++] = v; }
+            }
+            s_nact = na;
+        }
+        __syncthreads();
+        const int nact = s_nact;
+        // ---- trees of the members that have measurements to split (slot s of the workspace) ----
+        for (int q = tid; q < nact << TBLOG; q += GT) {
+            const int sl = q >> TBLOG, i = q & (TBL - 1), v = s_act[sl];
+            const double dv = s_div[v];
+            double mass = 0.0;
+            const int gidx = s_blk[v] * TBL + i;
+            if (gidx < a.d) {
+                const long long at = s_b[v] * (long long)a.d + gidx;
+                const double x = a.V[at] / dv;
+                if (a.stage == 1) mass = x * x;
+                else { const double ap = 0.5 * (x + a.est[at]); mass = ap * ap; }
+            }
+            ws[sl * wsv + TBL + i] = mass;
+        }
+        if (nact > 0) {
+            group_build<GT>(ws, wsv, nact, TBL, TBLOG, tid);
+            for (int sl = tid; sl < nact; sl += GT) ws[sl * wsv + 1] = s_cnt[s_act[sl]];
+            group_split<GT>(ws, wsv, nact, TBLOG, tid, a.seed,
+                            [&](int sl) { return a.vec_offset + (unsigned long long)s_b[s_act[sl]]; },
+                            [&](int sl) { return (unsigned)(s_blk[s_act[sl]] * (2 * TBL)); }, stream, list, ctr);
+        }
+        // ---- per-member epilogue, one warp per member ----
+        for (int v = warp; v < Gc; v += GT / 32) {
+            const double dv = s_div[v];
+            if (dv == 0.0) continue;
+            const long long b = s_b[v];
+            const int blk = s_blk[v], sl = s_slot[v];
+            const long long base = b * (long long)a.d + (long long)blk * TBL;
+            const double* t = ws + (sl < 0 ? 0 : sl) * wsv + TBL;
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+            for (int i = lane; i < TBL; i += 32) {
+                const int gidx = blk * TBL + i;
+                const bool in = gidx < a.d;
+                const double x = in ? a.V[base + i] / dv : 0.0;
+                const double cnt = sl < 0 ? 0.0 : t[i];
+                if (a.stage == 1) {
+                    const double p = sqrt(cnt / N);
+                    if (in) a.est[base + i] = p;
+                    const double ap = 0.5 * (x + p), am = 0.5 * (x - p), gap = fabs(x) - p;
+                    s0 += ap * ap;
+                    s1 += am * am;
+                    s2 = a.norm_inf ? fmax(s2, fabs(gap)) : s2 + gap * gap;
+                } else if (in) {
+                    const double p = a.est[base + i];
+                    const double est = (cnt > tomo_sign_threshold(p, N)) ? p : -p;
+                    a.est[base + i] = est;
+                    const double df = x - est;
+                    s0 = a.norm_inf ? fmax(s0, fabs(df)) : s0 + df * df;
+                }
+            }
+            if (a.stage == 1) {
+                s0 = warp_sum(s0); s1 = warp_sum(s1);
+                s2 = a.norm_inf ? warp_max(s2) : warp_sum(s2);
+                if (lane == 0) {
+                    a.bm_a[b * a.nblk + blk] = s0; a.bm_b[b * a.nblk + blk] = s1;
+                    if (a.may_skip) a.lbp[b * a.nblk + blk] = s2;
+                }
+            } else {
+                s0 = a.norm_inf ? warp_max(s0) : warp_sum(s0);
+                if (lane == 0) a.errp[b * a.nblk + blk] = s0;
+            }
+        }
+    }
+}
+
+int tomo_blockgroup_launch(TomoBlockGroupArgs a, int ctas, cudaStream_t stream) {
+    tomo_blockgroup_kernel<256><<<ctas, 256, 0, stream>>>(a);
+    SQ_LAUNCH_CHECK("tomo_blockgroup_kernel");
+    return SQ_OK;
 }
 
 size_t tomo_group_ws_bytes(int L, int G, int ctas) { return (size_t)ctas * G * tomo_group_wsv(L) * sizeof(double); }

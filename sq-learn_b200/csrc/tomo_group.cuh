@@ -19,6 +19,28 @@ struct TomoGroupArgs {
     unsigned long long seed, vec_offset;
 };
 
+// the long-vector variant: members are (vector, leaf block) pairs of tomography.cu's block path
+struct TomoBlockGroupArgs {
+    const double* V;
+    double* est;
+    const double* sumsq;   // [B]
+    const double* bcnt;    // [B, nblk] measurements that fall in the block (from the top kernel)
+    double* bm_a;          // [B, nblk] out, stage 1: '+' mass of the block
+    double* bm_b;          // [B, nblk] out, stage 1: '-' mass
+    double* lbp;           // [B, nblk] out, stage 1: sum / max of (|x| - P)^2
+    double* errp;          // [B, nblk] out, stage 2: error partial
+    const int* done;       // [B]
+    const double* nhop;    // [B]
+    const int* skip2;      // [B]
+    double* gws;           // ctas * G * 2048 doubles
+    long long B;
+    int d, nblk, blk_lo, nown;   // blocks [blk_lo, blk_lo + nown) of every vector
+    int G, stage, at, norm_inf, may_skip;
+    double N;
+    unsigned long long seed, vec_offset;
+};
+int tomo_blockgroup_launch(TomoBlockGroupArgs a, int ctas, cudaStream_t stream);
+
 // doubles of workspace per vector: the sum tree / counts [2L] and the partial sums of the ordered reductions [L/2]
 __host__ __device__ inline size_t tomo_group_wsv(int L) { return (size_t)2 * L + (L / 2 < 2 ? 2 : L / 2); }
 size_t tomo_group_ws_bytes(int L, int G, int ctas);

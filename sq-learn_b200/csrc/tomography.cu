@@ -497,6 +497,7 @@ static double g_direct_factor = 64.0;
 static int g_many_div = 4, g_many_cap = 128;
 static int g_cache_max_L = 256;       // the fused kernel keeps input + stage-1 CDF in shared memory up to this L
 static int g_early = 1;               // skip stage 2 of attempts that cannot succeed
+static int g_blockgroup_on = 1;       // leaf blocks of long vectors go through the block-group kernel (tomo_group.cu)
 static int g_group_on = 1;            // single attempts of many vectors go to the group kernel (tomo_group.cu)
 static long long g_group_min_B = 296; // ... from this many vectors on
 static int g_group_threads = 256;     // threads per CTA of the group kernel (1024 / threads CTAs per SM)
@@ -540,7 +541,8 @@ struct TomoBigArgs {
     double* n_used;
     double* err;
     const double* sumsq;   // [B] ||V||^2
-    double* bm_a;          // [B, nblk] stage-1 mass, then stage-2 '+' mass of every block
+    double* bm_0;          // [B, nblk] stage-1 mass of every block (the same for every attempt: computed once)
+    double* bm_a;          // [B, nblk] stage-2 '+' mass of every block
     double* bm_b;          // [B, nblk] stage-2 '-' mass
     double* bcnt;          // [B, nblk] measurements that fall in the block
     double* errp;          // [B, nblk] per-block error partial
@@ -550,6 +552,7 @@ struct TomoBigArgs {
     int* skip2;            // [B] stage 2 of the current attempt is skipped
     int may_skip;          // the current attempt may be given up early (stop rule on, not the last attempt)
     int early;             // early give-up enabled for this call (phase 0 then computes nhop)
+    double* gws;           // trees of the block-group kernel (tomo_group.cu)
     long long B;
     int d, nblk, NB, logNB;
     int blk_lo;            // first block of this launch (leaf blocks can be sharded over GPUs)
@@ -616,7 +619,7 @@ __global__ void tomo_big_mass_kernel(TomoBigArgs a) {
         s += x * x;
     }
     s = block_sum(s, red, tid, blockDim.x);
-    if (tid == 0) a.bm_a[b * a.nblk + blk] = s;
+    if (tid == 0) a.bm_0[b * a.nblk + blk] = s;
 }
 
 // one CTA per vector: split the attempt's measurements over the blocks
@@ -646,7 +649,7 @@ __global__ void tomo_big_top_kernel(TomoBigArgs a, int stage) {
     }
     double sminus = 0.0;
     for (int i = tid; i < NB; i += T) {
-        mass[NB + i] = (i < a.nblk) ? a.bm_a[b * a.nblk + i] : 0.0;
+        mass[NB + i] = (i < a.nblk) ? (stage == 1 ? a.bm_0 : a.bm_a)[b * a.nblk + i] : 0.0;
         if (stage == 2 && i < a.nblk) sminus += a.bm_b[b * a.nblk + i];
     }
     if (stage == 2) sminus = block_sum(sminus, red, tid, T);
@@ -765,6 +768,7 @@ extern "C" int sq_tomography_tune(int what, double value) {
         case 2: SQ_REQUIRE(value >= 32.0 && value <= 128.0, "sq_tomography_tune: cap in [32, 128]"); g_many_cap = (int)value; break;
         case 3: g_group_on = value != 0.0; break;
         case 6: g_cache_max_L = (int)value; break;
+        case 8: g_blockgroup_on = value != 0.0; break;
         case 7: g_early = value != 0.0; break;
         case 5: SQ_REQUIRE(value == 256.0 || value == 512.0 || value == 1024.0, "sq_tomography_tune: 256, 512 or 1024 threads");
                 g_group_threads = (int)value; break;
@@ -820,7 +824,12 @@ extern "C" int sq_tomography_batched(const double* V, long long B, int d, double
 // ---- long vectors ------------------------------------------------------------
 extern "C" int sq_row_sqnorms(const double* X, long long n, int d, double* out, void* stream);
 
-static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, size_t off[9], size_t* total) {
+static size_t tomo_blockgroup_slots(long long members) {
+    const long long most = (long long)device_sm_count() * 4 * 8;     // 4 CTAs per SM, up to 8 members each
+    return (size_t)(members + 8 < most ? members + 8 : most);
+}
+
+static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, size_t off[11], size_t* total) {
     int nb = (d + TB - 1) / TB;
     int p2 = 2, lg = 1;
     while (p2 < nb) { p2 <<= 1; ++lg; }
@@ -836,6 +845,8 @@ static void tomo_big_layout(long long B, int d, int* nblk, int* NB, int* logNB, 
     off[6] = o; o += align_up((size_t)B * sizeof(double), 256);   // nhop
     off[7] = o; o += per;                                         // lbp
     off[8] = o; o += align_up((size_t)B * sizeof(int), 256);      // skip2
+    off[9] = o; o += tomo_blockgroup_slots(B * (long long)nb) * 2048 * sizeof(double);   // trees of the block-group kernel
+    off[10] = o; o += per;                                        // bm_0
     *total = o;
 }
 
@@ -862,7 +873,7 @@ extern "C" size_t sq_tomography_workspace_bytes(long long B, int d) {
         return tomo_group_ws_bytes(L, G, ctas);
     }
     int nblk, NB, logNB;
-    size_t off[9], total;
+    size_t off[11], total;
     tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
     return total;
 }
@@ -872,7 +883,7 @@ static int tomo_big_prepare(TomoBigArgs& a, const double* V, long long B, int d,
                             unsigned long long seed, unsigned long long vec_offset, double* est, double* n_used,
                             double* err, void* ws, size_t ws_bytes, const char* who) {
     int nblk, NB, logNB;
-    size_t off[9], total;
+    size_t off[11], total;
     tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
     if (NB > 4096) { set_error("%s: d=%d exceeds the supported %d", who, d, 4096 * TB); return SQ_ERR_UNSUPPORTED; }
     if (!ws || ws_bytes < total) { set_error("%s: workspace needs %zu bytes, got %zu", who, total, ws_bytes); return SQ_ERR_WORKSPACE; }
@@ -881,9 +892,29 @@ static int tomo_big_prepare(TomoBigArgs& a, const double* V, long long B, int d,
     a.sumsq = (double*)(w + off[0]); a.bm_a = (double*)(w + off[1]); a.bm_b = (double*)(w + off[2]);
     a.bcnt = (double*)(w + off[3]); a.errp = (double*)(w + off[4]); a.done = (int*)(w + off[5]);
     a.nhop = (double*)(w + off[6]); a.lbp = (double*)(w + off[7]); a.skip2 = (int*)(w + off[8]); a.may_skip = 0; a.early = 0;
+    a.gws = (double*)(w + off[9]); a.bm_0 = (double*)(w + off[10]);
     a.B = B; a.d = d; a.nblk = nblk; a.NB = NB; a.logNB = logNB; a.norm_inf = norm_inf; a.stop = stop; a.delta = delta;
     a.seed = seed; a.vec_offset = vec_offset; a.blk_lo = 0; a.at = 0; a.N = 1.0;
     return SQ_OK;
+}
+
+static int tomo_big_blocks(const TomoBigArgs& a, int stage, int blk_lo, int blk_hi, dim3 gown, size_t sm_blk, cudaStream_t stream) {
+    if (!g_blockgroup_on) {
+        tomo_big_block_kernel<<<gown, 256, sm_blk, stream>>>(a, stage);
+        return SQ_OK;
+    }
+    TomoBlockGroupArgs g;
+    g.V = a.V; g.est = a.est; g.sumsq = a.sumsq; g.bcnt = a.bcnt; g.bm_a = a.bm_a; g.bm_b = a.bm_b; g.lbp = a.lbp;
+    g.errp = a.errp; g.done = a.done; g.nhop = a.nhop; g.skip2 = a.skip2; g.gws = a.gws; g.B = a.B; g.d = a.d;
+    g.nblk = a.nblk; g.blk_lo = blk_lo; g.nown = blk_hi - blk_lo; g.stage = stage; g.at = a.at; g.norm_inf = a.norm_inf;
+    g.may_skip = a.may_skip; g.N = a.N; g.seed = a.seed; g.vec_offset = a.vec_offset;
+    const long long members = a.B * (long long)g.nown, most = (long long)device_sm_count() * 4;
+    long long G = (members + most - 1) / most;
+    G = G < 1 ? 1 : (G > 8 ? 8 : G);
+    long long ctas = (members + G - 1) / G;
+    if (ctas > most) ctas = most;
+    g.G = (int)G;
+    return tomo_blockgroup_launch(g, (int)ctas, stream);
 }
 
 static int tomo_big_phase(TomoBigArgs a, int phase, int blk_lo, int blk_hi, cudaStream_t stream) {
@@ -896,17 +927,17 @@ static int tomo_big_phase(TomoBigArgs a, int phase, int blk_lo, int blk_hi, cuda
         int rc = sq_row_sqnorms(a.V, a.B, a.d, (double*)a.sumsq, stream);
         if (rc) return rc;
         tomo_big_init_kernel<<<(unsigned)a.B, 256, 0, stream>>>(a, a.early && !a.norm_inf);
+        tomo_big_mass_kernel<<<gall, 256, 0, stream>>>(a);       // stage-1 block masses: once, every block
         SQ_CUDA(cudaFuncSetAttribute(tomo_big_top_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_top));
         SQ_CUDA(cudaFuncSetAttribute(tomo_big_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_blk));
     } else if (phase == 1) {
-        // stage 1: block masses (cheap, all blocks), top tree, leaves of the own blocks
-        tomo_big_mass_kernel<<<gall, 256, 0, stream>>>(a);
+        // stage 1: top tree over the block masses of phase 0, leaves of the own blocks
         tomo_big_top_kernel<<<(unsigned)a.B, ttop, sm_top, stream>>>(a, 1);
-        if (blk_hi > blk_lo) tomo_big_block_kernel<<<gown, 256, sm_blk, stream>>>(a, 1);
+        if (blk_hi > blk_lo) { int rc = tomo_big_blocks(a, 1, blk_lo, blk_hi, gown, sm_blk, stream); if (rc) return rc; }
     } else if (phase == 2) {
         // stage 2 (needs the '+' / '-' masses of every block)
         tomo_big_top_kernel<<<(unsigned)a.B, ttop, sm_top, stream>>>(a, 2);
-        if (blk_hi > blk_lo) tomo_big_block_kernel<<<gown, 256, sm_blk, stream>>>(a, 2);
+        if (blk_hi > blk_lo) { int rc = tomo_big_blocks(a, 2, blk_lo, blk_hi, gown, sm_blk, stream); if (rc) return rc; }
     } else {
         // error over all blocks, stop rule
         tomo_big_finish_kernel<<<(unsigned)a.B, 256, 0, stream>>>(a);
@@ -973,7 +1004,7 @@ extern "C" int sq_tomography_workspace_layout(long long B, int d, long long out[
     SQ_REQUIRE(out && B >= 1 && d > sq_tomography_max_fused_dim(), "sq_tomography_workspace_layout: needs B >= 1 and d > %d",
                sq_tomography_max_fused_dim());
     int nblk, NB, logNB;
-    size_t off[9], total;
+    size_t off[11], total;
     tomo_big_layout(B, d, &nblk, &NB, &logNB, off, &total);
     out[0] = nblk;
     out[1] = TB;
