@@ -65,6 +65,10 @@ struct Philox {
     __host__ __device__ Philox() {}
     // (seed) keys the generator; (a, b, c) name the stream: e.g. vector id,
     // attempt/stage, tree node.  c0 counts blocks inside the stream.
+    // The stream tag b enters the key additively (k1 = seed_hi + b * golden ratio): within one seed every
+    // (a, b, c) is its own stream, which is all the kernels rely on; two DIFFERENT seeds whose high words differ
+    // by (b - b') * 0x9E3779B9 mod 2^32 share streams between tags b and b' - seeds that are meant to be
+    // independent should differ in their low word (sqlearn.QuantumUtility.seed() values do).
     __host__ __device__ Philox(uint64_t seed, uint64_t a, uint32_t b, uint32_t c) {
         k0 = (uint32_t)seed;
         k1 = (uint32_t)(seed >> 32) + b * 0x9E3779B9u;
