@@ -36,6 +36,7 @@ struct IpeGrid {
     double x;      // M theta_a / pi
     double j0, t;  // floor and fraction of x
     int kind;      // 0: S <= 0 (estimate 0), 1: x on a grid point (deterministic), 2: to be sampled
+    double c2t;    // cos(2 theta_a) = 1 - 2a
 };
 
 __host__ __device__ inline double sq_cospi(double y) {
@@ -60,7 +61,7 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
     const double PI = 3.14159265358979323846;
     g.S = xn + cn;
     g.kind = 0;
-    g.M = 16.0; g.x = 0.0; g.j0 = 0.0; g.t = 0.0;
+    g.M = 16.0; g.x = 0.0; g.j0 = 0.0; g.t = 0.0; g.c2t = 1.0;
     if (!(g.S > 0.0)) return;
     double a = (g.S - 2.0 * dot) / (2.0 * g.S);
     if (a < 1e-15) a = 0.0;  // math.isclose(a, 0, abs_tol=1e-15) (Utility.py:730); negatives are rounding noise
@@ -72,6 +73,7 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
     // accuracy as the library call (both are within an ulp or two of the true angle) at a fifth of the instructions.
     double theta;
     const double c = 1.0 - 2.0 * a;
+    g.c2t = c;
     if (fabs(c) < 0.25) {
         const double u = c * c;
         // asin(c) = c * sum_k  (2k)! / (4^k (k!)^2 (2k+1))  c^(2k); 14 terms: next one < 0.25^28 * 0.02 = 3e-19
@@ -189,8 +191,9 @@ __host__ __device__ inline void ipe_sincos_small(double y, double& s, double& c)
 
 // Bracket of  sum_{k=0}^{K-1} f(a + k)  for the convex f above (K >= 1, 1/2 < a, a + K - 1/2 < M).
 // near = true: the near end (a - 1/2, a) is within 0.5 rad of 0 and is done by Taylor series.
+// far_given: (s4, c4) = (sin, cos) of pi (a + K - 1) / M come from the caller.
 __host__ __device__ inline void ipe_run_bracket(double M, double a, double K, bool near, double& lo, double& hi,
-                                                double& s4, double& c4) {
+                                                double& s4, double& c4, bool far_given = false, double c2t = 0.0) {
     const double PI = 3.14159265358979323846;
     const double piM = PI / M;
     double s1, c1, s3, c3;                                  // at d1 = a - 1/2 and d3 = a
@@ -203,7 +206,14 @@ __host__ __device__ inline void ipe_run_bracket(double M, double a, double K, bo
     }
     const double d4 = a + K - 1.0;                          // last point; d2 = d4 + 1/2
     const double invM = 1.0 / M;
-    sq_sincospi(d4 * invM, s4, c4);                         // (handed back: the mirror weights start from here)
+    if (far_given) {
+        // the lean path's run ends at d4 = 2x - (t + 4): pi d4 / M = 2 theta_a - y3, and cos 2 theta_a = 1 - 2a is known
+        const double s2t = sqrt(fmax(1.0 - c2t * c2t, 0.0));
+        s4 = s2t * c3 - c2t * s3;
+        c4 = c2t * c3 + s2t * s3;
+    } else {
+        sq_sincospi(d4 * invM, s4, c4);                     // (handed back: the mirror weights start from here)
+    }
     double sh, ch;
     ipe_sincos_small(0.5 * piM, sh, ch);
     const double s2 = s4 * ch + c4 * sh, c2 = c4 * ch - s4 * sh;
@@ -230,7 +240,7 @@ __host__ __device__ inline int ipe_lean(const IpeGrid& g, double V, double& med)
     double w[8];
     ipe_window(M, t, s2, w);
     double blo, bhi, s4, c4;
-    ipe_run_bracket(M, t + 4.0, 2.0 * j0 - 7.0, true, blo, bhi, s4, c4);
+    ipe_run_bracket(M, t + 4.0, 2.0 * j0 - 7.0, true, blo, bhi, s4, c4, true, g.c2t);
     blo *= s2; bhi *= s2;
     double c0 = w[0], c1 = c0 + w[1], c2 = c1 + w[2], c3 = c2 + w[3], c4_ = c3 + w[4], c5 = c4_ + w[5],
            c6 = c5 + w[6], c7 = c6 + w[7];

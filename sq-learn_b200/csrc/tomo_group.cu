@@ -20,7 +20,7 @@
 
 namespace sq {
 
-static const int GCH = 4;            // nodes per thread and chunk of a level
+static const int GCH = 8;            // nodes per thread and chunk of a level
 static const int GMAXV = 1024;       // most vectors in a group
 static const int GBMAX = 32;         // most (vector, block) members in a group of the long-vector kernel
 
@@ -376,9 +376,9 @@ int tomo_group_size(long long B, int L, int sms, int threads) {
 }
 
 int tomo_group_launch(TomoGroupArgs a, int ctas, int threads, cudaStream_t stream) {
-    if (threads == 256) tomo_group_kernel<256><<<ctas, 256, 0, stream>>>(a);
-    else if (threads == 512) tomo_group_kernel<512><<<ctas, 512, 0, stream>>>(a);
-    else tomo_group_kernel<1024><<<ctas, 1024, 0, stream>>>(a);
+    // (512 and 1024 threads per CTA were measured too: 256, four CTAs per SM, is the fastest - DESIGN.md section 6)
+    (void)threads;
+    tomo_group_kernel<256><<<ctas, 256, 0, stream>>>(a);
     SQ_LAUNCH_CHECK("tomo_group_kernel");
     return SQ_OK;
 }

@@ -770,7 +770,7 @@ extern "C" int sq_tomography_tune(int what, double value) {
         case 6: g_cache_max_L = (int)value; break;
         case 8: g_blockgroup_on = value != 0.0; break;
         case 7: g_early = value != 0.0; break;
-        case 5: SQ_REQUIRE(value == 256.0 || value == 512.0 || value == 1024.0, "sq_tomography_tune: 256, 512 or 1024 threads");
+        case 5: SQ_REQUIRE(value == 256.0, "sq_tomography_tune: the group kernel is built for 256 threads per CTA");
                 g_group_threads = (int)value; break;
         case 4: SQ_REQUIRE(value >= 1.0, "sq_tomography_tune: minimum batch >= 1"); g_group_min_B = (long long)value; break;
         default: SQ_REQUIRE(false, "sq_tomography_tune: unknown tunable %d", what);
