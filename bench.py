@@ -174,7 +174,11 @@ def cpu_iteration_rate(cpu_rows, steps, warmup, mode, total_rows=N_ROWS):
             t_tomo.append(t2 - t1)
     tr, tt = float(np.mean(t_rows)), float(np.mean(t_tomo))
     full = tr * (total_rows / cpu_rows) + tt
-    return {"value": 1.0 / full, "unit": UNIT, "cores": 1, "kind": "port",
+    return {"value": 1.0 / full, "unit": UNIT, "cores": 1, "kind": "port", "extrapolated": True,
+            "measured": {"rows": cpu_rows, "seconds_per_step_rows_part": tr, "seconds_centroid_tomography": tt,
+                         "steps": steps},
+            "threads": "1 (the reference's quantum routines are single-threaded Python and its Lloyd loop limits "
+                       "BLAS to one thread, _dmeans.py:618)",
             "sample": "%d of %d rows per step (E+M-step %.3f s, measured) + 256x128 centroid tomography (%.3f s, "
                       "measured); full-size step time extrapolated linearly in rows: %.1f s.  The port calls scipy's "
                       "cdist like the reference; its M-step and tomography are faster than the reference's own "

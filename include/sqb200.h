@@ -62,9 +62,13 @@ int sq_tomography_batched(const double* V, long long B, int d, double delta, int
                           unsigned long long vec_offset, double* est, double* n_used, double* err, double* trace,
                           int* attempts, void* stream);
 
-/* Same routine for any d up to 4M: vectors longer than sq_tomography_max_fused_dim() are cut into
- * blocks that the whole grid works on, with scratch in (ws, ws_bytes) sized by
- * sq_tomography_workspace_bytes (0 when d fits the fused path; B <= 65535 beyond it).      */
+/* Same routine for any d up to 4M, with scratch in (ws, ws_bytes) sized by sq_tomography_workspace_bytes:
+ *  - d <= sq_tomography_max_fused_dim(): one attempt (single-shot mode, or a schedule without the stop rule) of
+ *    296 vectors or more runs in the group kernel, which keeps the sum trees of a group of vectors in ws (2.5
+ *    doubles per leaf and vector in flight); everything else - and any call whose ws is too small - goes to
+ *    sq_tomography_batched.  The two give the same bits.  workspace_bytes is 0 when the group kernel would not
+ *    be used.
+ *  - longer vectors are cut into blocks of 1024 leaves that the whole grid works on (B <= 65535).           */
 size_t sq_tomography_workspace_bytes(long long B, int d);
 int sq_tomography_batched_ws(const double* V, long long B, int d, double delta, int norm_inf, int stop,
                              const double* sched_host, int sched_len, unsigned long long seed,
@@ -108,12 +112,16 @@ int sq_tomography_batched_spec_fused(const double* V, long long B, int d, double
                                      unsigned long long vec_offset, double* est, double* n_used, double* err,
                                      int* attempts, int* state, void* stream);
 
-/* Measurement hook (no reference counterpart; process-wide and NOT thread-safe - meant for tools/, not for
- * callers): what = 0 sets the factor f of the rule "an attempt with N <= f * clamp(L, 32, 512) measurements
- * draws them one by one instead of splitting counts down the tree" (L = d rounded up to a power of two;
- * both samplers are exact, so the law does not change, the draws do); 1 and 2 set the divisor and the cap of
- * the threads-per-vector rule for large batches (threads = min(L / divisor, cap); results do not depend on
- * them).                                                                                                   */
+/* Measurement hook (no reference counterpart; process-wide and NOT thread-safe - meant for tools/ and the
+ * A/B tests, not for callers).  None of the switches changes the law of a result, and only `what = 0` changes
+ * which draws are used:
+ *   0  factor f of the rule "an attempt with N <= f * clamp(L, 32, 512) measurements draws them one by one instead
+ *      of splitting counts down the tree" (L = d rounded up to a power of two; both samplers are exact);
+ *   1, 2  divisor and cap of the per-vector kernel's threads-per-vector rule for large batches;
+ *   3, 4  group kernel on / off, and the batch size from which it is used (default 296 vectors);
+ *   6  largest L for which the per-vector kernel keeps the input and its stage-1 CDF in shared memory (256);
+ *   7  skipping of attempts that cannot succeed on / off (results are bit-identical either way);
+ *   8  block-group kernel for long vectors on / off (off: round 1's one-CTA-per-block kernel).              */
 int sq_tomography_tune(int what, double value);
 
 /* ---- q-means E-step ------------------------------------------------------ *
