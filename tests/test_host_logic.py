@@ -131,3 +131,15 @@ def test_committed_bench_line_has_the_contract_keys():
     assert set(("value", "unit", "cores", "kind", "sample")) <= set(line["cpu_baseline"])
     assert line["gpu_launches"] > 0 and "workload" in line["config"]
     assert not set(line["clocks"]["reasons"]) & {"hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown"}
+
+
+def test_mle_dimension_matches_stock_scikit_learn():
+    """n_components='mle' (reference: _infer_dimension, _qPCA.py:101-110, Minka's rule): the host restatement picks
+    the rank the installed scikit-learn picks"""
+    from sklearn.decomposition._pca import _infer_dimension as stock
+    from sqlearn.decomposition._qPCA import _infer_dimension
+    rs = np.random.RandomState(0)
+    for n, d, r in [(200, 10, 3), (500, 30, 7), (100, 8, 2), (1000, 50, 10), (60, 6, 5)]:
+        X = rs.randn(n, r) @ rs.randn(r, d) * 3 + rs.randn(n, d) * 0.3
+        spectrum = np.linalg.svd(X - X.mean(axis=0), compute_uv=False) ** 2 / (n - 1)
+        assert _infer_dimension(spectrum, n) == stock(spectrum, n)
