@@ -12,16 +12,16 @@
 // F at the 8 grid points around x ("window") is  F_i = B + cum_i,  cum_i the running sum of the window weights
 // (plus the weights of their mirror images M - r, negligible away from M/2) and B the mass of every r below the
 // window.  In distance from x, B is ONE contiguous run:  B = sin^2(pi t) sum_{k=0}^{K-1} f(a + k),  a = t + 4,
-// K = 2 floor(x) - 7 (the points left of the window down to 0, then their mirror images).  f is convex on (0, M),
-// so the run is bracketed by two integrals with a closed form (the antiderivative of csc^2 is -cot):
-//     int_a^{a+K-1} f + (f(a) + f(a+K-1))/2   <=   sum   <=   int_{a-1/2}^{a+K-1/2} f        (Hermite-Hadamard)
-// The gap is ~3e-4 of the mass.  V is compared with G at both ends of the bracket: if both agree the comparison
-// is certain; otherwise (0.3 % of the pairs) ipe_tighten peels exact terms off both ends of the run, which
-// shrinks the gap like 1/a^3, until every comparison is certain; a median outside the window (1e-6) is found by
-// plain summation (ipe_brute).  All three use the same V, so together they ARE the inversion - exact in law, not
-// an approximation.  ipe_lean declines (IPE_GENERAL) what it is not built for - small grids, windows touching 0
-// or M/2, sizeable mirror weights - before looking at V, so those pairs can go to the general estimator of
-// ipe.cuh with its own draws without touching the law.
+// K = 2 floor(x) - 7 (the points left of the window down to 0, then their mirror images).  Every even derivative of
+// f is positive on (0, M), so the Euler-Maclaurin expansion of the run envelops it (ipe_bracket_ends):
+//     sum = int_a^b f + (f(a) + f(b))/2 + (f'(b) - f'(a))/12 - th (f'''(b) - f'''(a))/720,   0 <= th <= 1,  b = a + K - 1,
+// all in closed form from (sin, cos) at the two ends (the antiderivative of csc^2 is -cot).  The gap is 3e-6 sin^2(pi t).
+// V is compared with G at both ends of the bracket: if both agree the comparison is certain; otherwise (3e-5 of the
+// pairs) ipe_tighten peels exact terms off both ends of the run, which shrinks the gap like 1/a^5, until every
+// comparison is certain; a median outside the window (1e-6) is found by plain summation (ipe_brute).  All three use
+// the same V, so together they ARE the inversion - exact in law, not an approximation.  ipe_lean declines
+// (IPE_GENERAL) what it is not built for - small grids, windows touching 0 or M/2 - before looking at V, so those
+// pairs can go to the general estimator of ipe.cuh with its own draws without touching the law.
 #pragma once
 #include "common.cuh"
 #include "fejer.cuh"
@@ -96,7 +96,7 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
     } else {
         theta = asin(sqrt(a));
     }
-    g.x = g.M * (theta / PI);
+    g.x = g.M * (theta * (1.0 / PI));
     g.j0 = floor(g.x);
     g.t = g.x - g.j0;
     g.kind = (g.t == 0.0) ? 1 : 2;
@@ -136,11 +136,9 @@ __host__ __device__ inline double ipe_f(double M, double d) {
     return 1.0 / (ms * ms);
 }
 
-// window weights w_i = sin^2(pi t) f(|i - 3 - t|), i = 0..7 (grid points j0 - 3 .. j0 + 4), M >= 32
-__host__ __device__ inline void ipe_window(double M, double t, double s2, double w[8]) {
+// (M sin(pi z / M))^2 at the 8 window points z = i - 3 - t (grid points j0 - 3 .. j0 + 4), M >= 32, piM = pi / M
+__host__ __device__ inline void ipe_window_sq(double piM, double t, double pw[8]) {
     const double PI = 3.14159265358979323846;
-    const double piM = PI / M;
-    double pw[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
         // |pi z / M| < pi/8: M sin(pi z/M) = pi z P(u), u = (pi z/M)^2, Taylor to u^7 (next term < 2e-18)
@@ -156,14 +154,30 @@ __host__ __device__ inline void ipe_window(double M, double t, double s2, double
         const double ms = PI * z * P;
         pw[i] = ms * ms;
     }
-    // w_i = s2 / pw_i with one division: prefix and suffix products
-    const double a01 = pw[0] * pw[1], a23 = pw[2] * pw[3], a45 = pw[4] * pw[5], a67 = pw[6] * pw[7];
-    const double lo4 = a01 * a23, hi4 = a45 * a67;
-    const double r = s2 / (lo4 * hi4);
-    const double rl = r * hi4, rh = r * lo4;
-    const double r01 = rl * a23, r23 = rl * a01, r45 = rh * a67, r67 = rh * a45;
-    w[0] = r01 * pw[1]; w[1] = r01 * pw[0]; w[2] = r23 * pw[3]; w[3] = r23 * pw[2];
-    w[4] = r45 * pw[5]; w[5] = r45 * pw[4]; w[6] = r67 * pw[7]; w[7] = r67 * pw[6];
+}
+
+// w_i = s2 / pw_i from r = s2 / (pw_0 ... pw_7): prefix and suffix products, no further division
+struct IpeProd8 {
+    double a01, a23, a45, a67, lo4, hi4;
+    __host__ __device__ inline void of(const double pw[8]) {
+        a01 = pw[0] * pw[1]; a23 = pw[2] * pw[3]; a45 = pw[4] * pw[5]; a67 = pw[6] * pw[7];
+        lo4 = a01 * a23; hi4 = a45 * a67;
+    }
+    __host__ __device__ inline void quotients(const double pw[8], double r, double w[8]) const {
+        const double rl = r * hi4, rh = r * lo4;
+        const double r01 = rl * a23, r23 = rl * a01, r45 = rh * a67, r67 = rh * a45;
+        w[0] = r01 * pw[1]; w[1] = r01 * pw[0]; w[2] = r23 * pw[3]; w[3] = r23 * pw[2];
+        w[4] = r45 * pw[5]; w[5] = r45 * pw[4]; w[6] = r67 * pw[7]; w[7] = r67 * pw[6];
+    }
+};
+
+// window weights w_i = sin^2(pi t) f(|i - 3 - t|), i = 0..7, M >= 32
+__host__ __device__ inline void ipe_window(double M, double t, double s2, double w[8]) {
+    double pw[8];
+    ipe_window_sq(3.14159265358979323846 / M, t, pw);
+    IpeProd8 pr;
+    pr.of(pw);
+    pr.quotients(pw, s2 / (pr.lo4 * pr.hi4), w);
 }
 
 // sin and cos of a small angle (|y| <= 0.5), to full double precision
@@ -189,70 +203,76 @@ __host__ __device__ inline void ipe_sincos_small(double y, double& s, double& c)
     c = fma(Q, u, 1.0);
 }
 
-// Bracket of  sum_{k=0}^{K-1} f(a + k)  for the convex f above (K >= 1, 1/2 < a, a + K - 1/2 < M).
-// near = true: the near end (a - 1/2, a) is within 0.5 rad of 0 and is done by Taylor series.
-// far_given: (s4, c4) = (sin, cos) of pi (a + K - 1) / M come from the caller.
-__host__ __device__ inline void ipe_run_bracket(double M, double a, double K, bool near, double& lo, double& hi,
-                                                double& s4, double& c4, bool far_given = false, double c2t = 0.0) {
-    const double PI = 3.14159265358979323846;
-    const double piM = PI / M;
-    double s1, c1, s3, c3;                                  // at d1 = a - 1/2 and d3 = a
-    if (near) {
-        ipe_sincos_small((a - 0.5) * piM, s1, c1);
-        ipe_sincos_small(a * piM, s3, c3);
-    } else {
-        s1 = sq_sinpi((a - 0.5) / M); c1 = sq_cospi((a - 0.5) / M);
-        s3 = sq_sinpi(a / M); c3 = sq_cospi(a / M);
-    }
-    const double d4 = a + K - 1.0;                          // last point; d2 = d4 + 1/2
-    const double invM = 1.0 / M;
-    if (far_given) {
-        // the lean path's run ends at d4 = 2x - (t + 4): pi d4 / M = 2 theta_a - y3, and cos 2 theta_a = 1 - 2a is known
-        const double s2t = sqrt(fmax(1.0 - c2t * c2t, 0.0));
-        s4 = s2t * c3 - c2t * s3;
-        c4 = c2t * c3 + s2t * s3;
-    } else {
-        sq_sincospi(d4 * invM, s4, c4);                     // (handed back: the mirror weights start from here)
-    }
-    double sh, ch;
-    ipe_sincos_small(0.5 * piM, sh, ch);
-    const double s2 = s4 * ch + c4 * sh, c2 = c4 * ch - s4 * sh;
-    // cot(y1) - cot(y2) = sin(y2 - y1) / (sin y1 sin y2): one division per bracket end
-    const double inv = invM * (1.0 / PI);
-    const double p34 = s3 * s4;
-    hi = (s2 * c1 - c2 * s1) / (s1 * s2) * inv;
-    lo = ((s4 * c3 - c4 * s3) * p34 * (M * (1.0 / PI)) + 0.5 * (s3 * s3 + s4 * s4)) / (p34 * p34) * (invM * invM);
-    // floating-point slack: the brackets are sums of O(10) correctly rounded operations on O(1) quantities
+// Bracket of  sum_{k=0}^{K-1} f(a + k)  (K >= 1, 0 < a, b = a + K - 1 < M) by the Euler-Maclaurin formula.  Every
+// even derivative of csc^2 is positive on (0, pi), so the expansion envelops the sum:
+//     sum = int_a^b f + (f(a) + f(b))/2 + (f'(b) - f'(a))/12 - th (f'''(b) - f'''(a))/720,   0 <= th <= 1,
+// with f' = -(pi/M) 2c / (M^2 s^3), f''' = -(pi/M)^3 8c (2 + c^2) / (M^2 s^5), (s, c) = (sin, cos)(pi d / M), and
+// int f = (cot y_a - cot y_b) / (pi M) = sin(y_b - y_a) / (pi M s_a s_b).  From the values at the two ends:
+// (s3, c3) at a, (s4, c4) at b, q = 1 / (s3 s4).  The gap is 3e-6 at a = 4 (it falls like a^-5).
+__host__ __device__ inline void ipe_bracket_ends(double invM, double piM, double s3, double c3, double s4, double c4,
+                                                 double q, double& lo, double& hi) {
+    const double r3 = q * s4, r4 = q * s3;                  // 1 / sin at the two ends
+    const double r3_2 = r3 * r3, r4_2 = r4 * r4, invM2 = invM * invM;
+    const double integral = (s4 * c3 - c4 * s3) * q * (invM * (1.0 / 3.14159265358979323846));
+    const double ends = 0.5 * (r3_2 + r4_2) * invM2;
+    const double e1 = (c3 * r3_2 * r3 - c4 * r4_2 * r4) * (piM * invM2 * (1.0 / 6.0));
+    const double e3 = (c3 * (2.0 + c3 * c3) * (r3_2 * r3_2) * r3 - c4 * (2.0 + c4 * c4) * (r4_2 * r4_2) * r4) *
+                      ((piM * piM) * (piM * invM2) * (1.0 / 90.0));
+    hi = integral + ends + e1;
+    lo = hi - e3;
+    // floating-point slack: the brackets are sums of O(10) correctly rounded operations on positive terms
     hi = hi * (1.0 + 1e-12) + 1e-300;
     lo = lo * (1.0 - 1e-12);
     if (lo < 0.0) lo = 0.0;
 }
 
+// the general form (ipe_tighten): sines and cosines from the library
+__host__ __device__ inline void ipe_run_bracket(double M, double a, double K, double& lo, double& hi) {
+    const double invM = 1.0 / M;
+    double s3, c3, s4, c4;
+    sq_sincospi(a * invM, s3, c3);
+    sq_sincospi((a + K - 1.0) * invM, s4, c4);
+    ipe_bracket_ends(invM, 3.14159265358979323846 * invM, s3, c3, s4, c4, 1.0 / (s3 * s4), lo, hi);
+}
+
 // The common case.  Returns IPE_DONE with the median's r in `med`, or who should take the pair.
 __host__ __device__ inline int ipe_lean(const IpeGrid& g, double V, double& med) {
+    const double PI = 3.14159265358979323846;
     const double M = g.M, t = g.t, j0 = g.j0;
     if (!(M >= 32.0 && j0 >= 4.0 && 2.0 * (j0 + 4.0) < M)) return IPE_GENERAL;
     // mirror images of the window points sit at distances t + 2 j0 - 3 .. t + 2 j0 + 4; sin(pi d/M) >= 2 min(d, M - d)/M
     const double m = fmin(t + 2.0 * j0 - 3.0, M - (t + 2.0 * j0 + 4.0));
     if (!(m >= 4.0)) return IPE_GENERAL;
     const double st = sq_sinpi(t), s2 = st * st;
-    const double mu = 2.0 * s2 / (m * m);                   // >= the 8 mirror weights together
-    double w[8];
-    ipe_window(M, t, s2, w);
-    double blo, bhi, s4, c4;
-    ipe_run_bracket(M, t + 4.0, 2.0 * j0 - 7.0, true, blo, bhi, s4, c4, true, g.c2t);
+    const double invM = 1.0 / M, piM = PI * invM;
+    // the window, and the two ends of the run below it: a = t + 4 (Taylor: pi a / M < 0.5) and b = 2x - a, where
+    // pi b / M = 2 theta_a - pi a / M and cos 2 theta_a = 1 - 2a is known
+    double pw[8], w[8];
+    ipe_window_sq(piM, t, pw);
+    IpeProd8 pr;
+    pr.of(pw);
+    double s3, c3;
+    ipe_sincos_small((t + 4.0) * piM, s3, c3);
+    const double s2t = sqrt(fmax(1.0 - g.c2t * g.c2t, 0.0));
+    const double s4 = s2t * c3 - g.c2t * s3, c4 = g.c2t * c3 + s2t * s3;
+    // one division for the eight window weights and the two 1 / sin of the bracket
+    const double pwin = pr.lo4 * pr.hi4, pend = s3 * s4;
+    const double inv = 1.0 / (pwin * pend);
+    pr.quotients(pw, s2 * (inv * pend), w);
+    double blo, bhi;
+    ipe_bracket_ends(invM, piM, s3, c3, s4, c4, inv * pwin, blo, bhi);
     blo *= s2; bhi *= s2;
-    double c0 = w[0], c1 = c0 + w[1], c2 = c1 + w[2], c3 = c2 + w[3], c4_ = c3 + w[4], c5 = c4_ + w[5],
+    double c0 = w[0], c1 = c0 + w[1], c2 = c1 + w[2], c3_ = c2 + w[3], c4_ = c3_ + w[4], c5 = c4_ + w[5],
            c6 = c5 + w[6], c7 = c6 + w[7];
     double up = bhi + 1e-15;                                // added to cum_i for the upper end of F_i
     const double dn = blo - 1e-15;
-    if (mu > 1e-6) {
+    double umu;                                             // what `up` carries for the mirror images
+    if (2.0 * s2 > 1e-6 * (m * m)) {
         // sizeable mirror images (small grid, or x near 0 / M/2): their weights exactly.  They sit at the distances
-        // d4 + 1 + i (d4 = t + 2 j0 - 4 is the far end of the run below the window): rotate (sin, cos) of pi d4 / M
-        // by pi / M eight times; one division for the eight reciprocals.
+        // b + 1 + i: rotate (sin, cos) of pi b / M by pi / M eight times; one division for the eight reciprocals.
         double sh, ch;
-        ipe_sincos_small(3.14159265358979323846 / M, sh, ch);
-        double sn = s4, cs = c4, pm[8];
+        ipe_sincos_small(piM, sh, ch);
+        double sn = s4, cs = c4, pm[8], mw[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const double s_ = sn * ch + cs * sh, c_ = cs * ch - sn * sh;
@@ -260,35 +280,37 @@ __host__ __device__ inline int ipe_lean(const IpeGrid& g, double V, double& med)
             const double ms = M * sn;
             pm[i] = ms * ms;
         }
-        const double a01 = pm[0] * pm[1], a23 = pm[2] * pm[3], a45 = pm[4] * pm[5], a67 = pm[6] * pm[7];
-        const double lo4 = a01 * a23, hi4 = a45 * a67;
-        const double r = s2 / (lo4 * hi4);
-        const double rl = r * hi4, rh = r * lo4;
-        const double r01 = rl * a23, r23 = rl * a01, r45 = rh * a67, r67 = rh * a45;
-        const double m0 = r01 * pm[1], m1 = r01 * pm[0], m2 = r23 * pm[3], m3 = r23 * pm[2];
-        const double m4 = r45 * pm[5], m5 = r45 * pm[4], m6 = r67 * pm[7], m7 = r67 * pm[6];
-        double acc = m0;
-        c0 += acc; acc += m1; c1 += acc; acc += m2; c2 += acc; acc += m3; c3 += acc;
-        acc += m4; c4_ += acc; acc += m5; c5 += acc; acc += m6; c6 += acc; acc += m7; c7 += acc;
-        up += 1e-14;                                        // rounding of the rotations
+        IpeProd8 pq;
+        pq.of(pm);
+        pq.quotients(pm, s2 / (pq.lo4 * pq.hi4), mw);
+        double acc = mw[0];
+        c0 += acc; acc += mw[1]; c1 += acc; acc += mw[2]; c2 += acc; acc += mw[3]; c3_ += acc;
+        acc += mw[4]; c4_ += acc; acc += mw[5]; c5 += acc; acc += mw[6]; c6 += acc; acc += mw[7]; c7 += acc;
+        umu = 1e-14;                                        // rounding of the rotations
     } else {
-        up += mu * (1.0 + 1e-12);
+        umu = 1e-6 * (1.0 + 1e-12);                         // >= 2 s2 / m^2 >= the 8 mirror weights together
     }
-    const double umu = (mu > 1e-6) ? 0.0 : mu;              // what `up` carries on top of B's upper end
-    // a median below or above the window: plain summation
-    if (V <= ipe_G_raw(up - umu) || V > ipe_G_raw(dn + c7)) return IPE_BRUTE;
-    // smallest i in 0..7 with V <= G(F_i)  (V <= G(F_7) holds)
-    int i = 0;
-    {
-        const bool a3 = V <= ipe_G_raw(dn + c3), b3 = V > ipe_G_raw(up + c3);
-        if (a3 == b3) return IPE_TIGHTEN;
-        const double cq = a3 ? c1 : c5;
-        const bool a2 = V <= ipe_G_raw(dn + cq), b2 = V > ipe_G_raw(up + cq);
-        if (a2 == b2) return IPE_TIGHTEN;
-        const double cr = a3 ? (a2 ? c0 : c2) : (a2 ? c4_ : c6);
-        const bool a1 = V <= ipe_G_raw(dn + cr), b1 = V > ipe_G_raw(up + cr);
-        if (a1 == b1) return IPE_TIGHTEN;
-        i = (a3 ? 0 : 4) + (a2 ? 0 : 2) + (a1 ? 0 : 1);
+    up += umu;
+    // V against G(F_i), F_i in [dn + c_i, up + c_i]: certain when both ends of the bracket say the same.
+    // Smallest i in 0..7 with V <= G(F_i), taking the median to be in the window; the two edges are checked after.
+    const bool a3 = V <= ipe_G_raw(dn + c3_), b3 = V > ipe_G_raw(up + c3_);
+    if (a3 == b3) return IPE_TIGHTEN;
+    const double cq = a3 ? c1 : c5;
+    const bool a2 = V <= ipe_G_raw(dn + cq), b2 = V > ipe_G_raw(up + cq);
+    if (a2 == b2) return IPE_TIGHTEN;
+    const double cr = a3 ? (a2 ? c0 : c2) : (a2 ? c4_ : c6);
+    const bool a1 = V <= ipe_G_raw(dn + cr), b1 = V > ipe_G_raw(up + cr);
+    if (a1 == b1) return IPE_TIGHTEN;
+    const int i = (a3 ? 0 : 4) + (a2 ? 0 : 2) + (a1 ? 0 : 1);
+    if (i == 0) {
+        // below the window?  B itself is in [dn, up - umu]
+        const bool below = V <= ipe_G_raw(dn), above = V > ipe_G_raw(up - umu);
+        if (below == above) return IPE_TIGHTEN;
+        if (below) return IPE_BRUTE;
+    } else if (i == 7) {
+        const bool in7 = V <= ipe_G_raw(dn + c7), out7 = V > ipe_G_raw(up + c7);
+        if (in7 == out7) return IPE_TIGHTEN;
+        if (out7) return IPE_BRUTE;
     }
     med = j0 - 3.0 + (double)i;
     return IPE_DONE;
@@ -335,8 +357,7 @@ __host__ __device__ inline int ipe_tighten(const IpeGrid& g, double V, double& m
         }
         const double rest = K - 2.0 * n;                   // terms n .. K-1-n are still bracketed
         double blo = 0.0, bhi = 0.0;
-        double s4u, c4u;
-        if (rest >= 1.0) ipe_run_bracket(M, a + n, rest, false, blo, bhi, s4u, c4u);
+        if (rest >= 1.0) ipe_run_bracket(M, a + n, rest, blo, bhi);
         const double dn = (peeled + blo) * s2 * (1.0 - 1e-12) - 1e-16;
         const double up = (peeled + bhi) * s2 * (1.0 + 1e-12) + 1e-16;
         const bool exact = !(rest >= 1.0);
