@@ -20,8 +20,9 @@
 // pairs) ipe_tighten peels exact terms off both ends of the run, which shrinks the gap like 1/a^5, until every
 // comparison is certain; a median outside the window (1e-6) is found by plain summation (ipe_brute).  All three use
 // the same V, so together they ARE the inversion - exact in law, not an approximation.  ipe_lean declines
-// (IPE_GENERAL) what it is not built for - small grids, windows touching 0 or M/2 - before looking at V, so those
-// pairs can go to the general estimator of ipe.cuh with its own draws without touching the law.
+// what it is not built for before looking at V: small grids and windows touching 0 are summed plainly (IPE_BRUTE, a
+// short sum there), windows touching M/2 on a large grid go to the general estimator of ipe.cuh with its own draws
+// (IPE_GENERAL) - neither touches the law.
 #pragma once
 #include "common.cuh"
 #include "fejer.cuh"
@@ -36,6 +37,7 @@ struct IpeGrid {
     double x;      // M theta_a / pi
     double j0, t;  // floor and fraction of x
     int kind;      // 0: S <= 0 (estimate 0), 1: x on a grid point (deterministic), 2: to be sampled
+    double invM;   // 1 / M
     double c2t;    // cos(2 theta_a) = 1 - 2a
 };
 
@@ -61,42 +63,48 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
     const double PI = 3.14159265358979323846;
     g.S = xn + cn;
     g.kind = 0;
-    g.M = 16.0; g.x = 0.0; g.j0 = 0.0; g.t = 0.0; g.c2t = 1.0;
+    g.M = 16.0; g.invM = 1.0 / 16.0; g.x = 0.0; g.j0 = 0.0; g.t = 0.0; g.c2t = 1.0;
     if (!(g.S > 0.0)) return;
-    double a = (g.S - 2.0 * dot) / (2.0 * g.S);
+    // a = (S - 2 dot) / (2 S),  epsilon_a = eps max(1, |dot|) / S,  M = ceil(pi / (2 epsilon_a) (1 + sqrt(1 + 4 epsilon_a))):
+    // the same quantities from ONE reciprocal, r = 1 / (S max(1, |dot|))  (1/S = r mx, S/mx = r S^2)
+    const double mx = fmax(1.0, fabs(dot));
+    const double r = 1.0 / (g.S * mx);
+    const double rS = r * mx;
+    double a = fma(-dot, rS, 0.5);
     if (a < 1e-15) a = 0.0;  // math.isclose(a, 0, abs_tol=1e-15) (Utility.py:730); negatives are rounding noise
     if (a > 1.0) a = 1.0;
-    const double eps_a = eps * fmax(1.0, fabs(dot)) / g.S;
-    g.M = ceil((PI / (2.0 * eps_a)) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
+    const double eps_a = eps * mx * rS;
+    g.M = ceil(((PI / (2.0 * eps)) * (g.S * (r * g.S))) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
+    g.invM = 1.0 / g.M;
     // theta_a = asin(sqrt(a)) (Utility.py:493).  With c = 1 - 2a = cos(2 theta_a), theta_a = pi/4 - asin(c)/2; for the
     // usual pair (|x.c| a small fraction of |x|^2 + |c|^2) c is small and asin(c) is a short odd series - same
     // accuracy as the library call (both are within an ulp or two of the true angle) at a fifth of the instructions.
-    double theta;
+    double frac;                                            // theta_a / pi
     const double c = 1.0 - 2.0 * a;
     g.c2t = c;
     if (fabs(c) < 0.25) {
-        const double u = c * c;
-        // asin(c) = c * sum_k  (2k)! / (4^k (k!)^2 (2k+1))  c^(2k); 14 terms: next one < 0.25^28 * 0.02 = 3e-19
-        // exact rational coefficients (2k)!/(4^k k!^2 (2k+1)), highest first
-        double Q = 10400600.0 / (67108864.0 * 27.0);
-        Q = fma(Q, u, 2704156.0 / (16777216.0 * 25.0));
-        Q = fma(Q, u, 705432.0 / (4194304.0 * 23.0));
-        Q = fma(Q, u, 184756.0 / (1048576.0 * 21.0));
-        Q = fma(Q, u, 48620.0 / (262144.0 * 19.0));
-        Q = fma(Q, u, 12870.0 / (65536.0 * 17.0));
-        Q = fma(Q, u, 3432.0 / (16384.0 * 15.0));
-        Q = fma(Q, u, 924.0 / (4096.0 * 13.0));
-        Q = fma(Q, u, 252.0 / (1024.0 * 11.0));
-        Q = fma(Q, u, 70.0 / (256.0 * 9.0));
-        Q = fma(Q, u, 20.0 / (64.0 * 7.0));
-        Q = fma(Q, u, 6.0 / (16.0 * 5.0));
-        Q = fma(Q, u, 2.0 / (4.0 * 3.0));
-        Q = fma(Q, u, 1.0);
-        theta = 0.25 * PI - 0.5 * (c * Q);
+        // asin(c) = c * sum_k  q_k c^(2k),  q_k = (2k)! / (4^k (k!)^2 (2k+1)) (exact rationals); 14 terms, the next one is
+        // < 0.25^28 * 0.02 = 3e-19.  Even and odd k as two chains in v = c^4, so that they run side by side.
+        const double u = c * c, v = u * u;
+        double E = 2704156.0 / (16777216.0 * 25.0);           // k = 12
+        E = fma(E, v, 184756.0 / (1048576.0 * 21.0));       // 10
+        E = fma(E, v, 12870.0 / (65536.0 * 17.0));          // 8
+        E = fma(E, v, 924.0 / (4096.0 * 13.0));             // 6
+        E = fma(E, v, 70.0 / (256.0 * 9.0));                // 4
+        E = fma(E, v, 6.0 / (16.0 * 5.0));                  // 2
+        E = fma(E, v, 1.0);                                 // 0
+        double O = 10400600.0 / (67108864.0 * 27.0);          // k = 13
+        O = fma(O, v, 705432.0 / (4194304.0 * 23.0));       // 11
+        O = fma(O, v, 48620.0 / (262144.0 * 19.0));         // 9
+        O = fma(O, v, 3432.0 / (16384.0 * 15.0));           // 7
+        O = fma(O, v, 252.0 / (1024.0 * 11.0));             // 5
+        O = fma(O, v, 20.0 / (64.0 * 7.0));                 // 3
+        O = fma(O, v, 2.0 / (4.0 * 3.0));                   // 1
+        frac = fma(-(0.5 / PI) * c, fma(O, u, E), 0.25);    // (exactly 1/4 at c = 0: x = M/4 lands on its grid point)
     } else {
-        theta = asin(sqrt(a));
+        frac = asin(sqrt(a)) * (1.0 / PI);
     }
-    g.x = g.M * (theta * (1.0 / PI));
+    g.x = g.M * frac;
     g.j0 = floor(g.x);
     g.t = g.x - g.j0;
     g.kind = (g.t == 0.0) ? 1 : 2;
@@ -239,12 +247,16 @@ __host__ __device__ inline void ipe_run_bracket(double M, double a, double K, do
 __host__ __device__ inline int ipe_lean(const IpeGrid& g, double V, double& med) {
     const double PI = 3.14159265358979323846;
     const double M = g.M, t = g.t, j0 = g.j0;
-    if (!(M >= 32.0 && j0 >= 4.0 && 2.0 * (j0 + 4.0) < M)) return IPE_GENERAL;
     // mirror images of the window points sit at distances t + 2 j0 - 3 .. t + 2 j0 + 4; sin(pi d/M) >= 2 min(d, M - d)/M
     const double m = fmin(t + 2.0 * j0 - 3.0, M - (t + 2.0 * j0 + 4.0));
-    if (!(m >= 4.0)) return IPE_GENERAL;
+    if (!(M >= 32.0 && j0 >= 4.0 && 2.0 * (j0 + 4.0) < M && m >= 4.0)) {
+        // no room for the window.  On a small grid, or with x within a few points of 0 (nearly parallel vectors of
+        // like norm), plain summation from r = 0 is short: the same inversion, the same V.  The rest (x near M/2 on a
+        // large grid) goes to the general estimator.
+        return (M < 64.0 || j0 < 8.0) ? IPE_BRUTE : IPE_GENERAL;
+    }
     const double st = sq_sinpi(t), s2 = st * st;
-    const double invM = 1.0 / M, piM = PI * invM;
+    const double invM = g.invM, piM = PI * invM;
     // the window, and the two ends of the run below it: a = t + 4 (Taylor: pi a / M < 0.5) and b = 2x - a, where
     // pi b / M = 2 theta_a - pi a / M and cos 2 theta_a = 1 - 2a is known
     double pw[8], w[8];
@@ -318,13 +330,20 @@ __host__ __device__ inline int ipe_lean(const IpeGrid& g, double V, double& med)
 
 // The inversion by plain summation: smallest r with V <= G(F(r)).  O(r) - for the rare pairs only.
 __host__ __device__ inline double ipe_brute(const IpeGrid& g, double V) {
-    const double M = g.M, x = g.x;
+    const double M = g.M, x = g.x, invM = g.invM;
     const double st = sq_sinpi(g.t), s2 = st * st;
     const double rmax = floor(M * 0.5);
     double F = 0.0;
     for (double r = 0.0; r <= rmax; r += 1.0) {
-        double P = ipe_f(M, fabs(r - x));
-        if (r > 0.0 && 2.0 * r < M) P += ipe_f(M, r + x);   // the mirror image M - r, at distance r + x going left
+        // weight of r: the grid point at distance |r - x|, and (0 < r < M/2) its mirror image M - r at distance r + x
+        const double ma = M * sq_sinpi(fabs(r - x) * invM), A = ma * ma;
+        double P;
+        if (r > 0.0 && 2.0 * r < M) {
+            const double mb = M * sq_sinpi((r + x) * invM), B = mb * mb;
+            P = (A + B) / (A * B);
+        } else {
+            P = 1.0 / A;
+        }
         F += s2 * P;
         if (V <= ipe_G(F)) return r;
     }
@@ -382,7 +401,7 @@ __host__ __device__ inline int ipe_tighten(const IpeGrid& g, double V, double& m
 
 // the estimate |x|^2 + |c|^2 - 2 ipe(x, c) from the median's r (Utility.py:733-734, :520-531)
 __host__ __device__ inline double ipe_value(const IpeGrid& g, double med) {
-    const double sn = sq_sinpi(med / g.M);   // (kept as a true division: the estimate is the reference's sin^2(pi j / M))
+    const double sn = sq_sinpi(med * g.invM);
     return 2.0 * g.S * sn * sn;
 }
 

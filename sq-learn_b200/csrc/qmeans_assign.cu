@@ -399,10 +399,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     if (st == IPE_BRUTE) med = ipe_brute(g, V);
                     sc[pos] = ipe_value(g, med) - xn;
                 }
-                // Pass 2b: the general estimator (warp-cooperative: every lane of a warp calls it together)
+                // Pass 2b: the general estimator (warp-cooperative: every lane of a warp calls it together, and its time
+                // grows with the number of live lanes - so the entries are dealt to the warps first here too)
 #pragma unroll 1
                 for (int it = 0; it * Cfg::THREADS < ndef; ++it) {
-                    const int li = it * Cfg::THREADS + tid;
+                    const int li = it * Cfg::THREADS + lane * (Cfg::THREADS / 32) + warp;
                     const int e = li < ndef ? list[li] : IPE_RESOLVE;
                     const bool okd = !(e & IPE_RESOLVE);
                     const int pos = okd ? e : 0;

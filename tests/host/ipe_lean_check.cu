@@ -17,7 +17,7 @@ int main() {
     long long total_bad = 0, lean_cfgs = 0;
     for (auto c : cfgs) {
         IpeGrid g;
-        g.S = 1.0; g.M = c.M; g.x = c.x; g.j0 = floor(c.x); g.t = c.x - g.j0; g.kind = 2;
+        g.S = 1.0; g.M = c.M; g.invM = 1.0 / c.M; g.x = c.x; g.j0 = floor(c.x); g.t = c.x - g.j0; g.kind = 2;
         g.c2t = cos(2.0 * 3.14159265358979323846 * c.x / c.M);
         const long long n = (c.M > 20000) ? 4000 : 40000;
         long long cnt[4] = {0, 0, 0, 0}, bad = 0;
