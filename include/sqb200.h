@@ -142,9 +142,11 @@ int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, c
                      double delta, unsigned long long seed, unsigned long long offset, int* labels,
                      double* mindist, double* inertia, int* n_fixed, void* ws, size_t ws_bytes, void* stream);
 
-/* Test hook (no reference counterpart): with on != 0 every pair of later mode-2 calls is sampled by the
- * draw-by-draw replay path of csrc/ipe.cuh (the path taken when the median of the 13 outcomes may lie outside
- * the enumerated window), so that its law can be tested; results stay exact, only slower.                  */
+/* Test hook (no reference counterpart).  on = 1: every pair of later mode-2 calls is sampled by the draw-by-draw
+ * replay path of csrc/ipe.cuh (the path taken when the median of the 13 outcomes may lie outside the enumerated
+ * window), so that its law can be tested.  on = 2: every pair is sampled by the inversion of csrc/ipe_lean.cuh,
+ * also the ones the kernel normally leaves out because their estimate certainly exceeds one already sampled in
+ * the same row - labels, distances and inertia must come out bit for bit as with on = 0.  on = 0: normal.      */
 int sq_ipe_debug_force_replay(int on);
 /* Test hook: B draws of the amplitude-estimation outcome j conditioned on lying outside the 8-point window
  * around the grid position x (offsets -3..4 from floor(x)), as the tail sampler of csrc/ipe.cuh makes them.   */

@@ -325,7 +325,7 @@ __device__ __forceinline__ double ipe_estimate_warp(double dot, double xn, doubl
     }
     if (!(valid && S > 0.0)) return 0.0;
     const double sn = sinpi(med / M);
-    return 2.0 * S * sn * sn;
+    return __dmul_rn(__dmul_rn(2.0 * S, sn), sn);   // (never fused with the caller's subtraction of |x|^2)
 }
 
 }  // namespace sq

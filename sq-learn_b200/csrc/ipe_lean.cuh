@@ -38,6 +38,7 @@ struct IpeGrid {
     double j0, t;  // floor and fraction of x
     int kind;      // 0: S <= 0 (estimate 0), 1: x on a grid point (deterministic), 2: to be sampled
     double invM;   // 1 / M
+    double rS;     // 1 / S
     double c2t;    // cos(2 theta_a) = 1 - 2a
 };
 
@@ -58,23 +59,32 @@ __host__ __device__ inline void sq_sincospi(double y, double& sn, double& cs) {
 #endif
 }
 
-// a, epsilon_a, M, theta_a of ipe / amplitude_estimation (Utility.py:725-733, :484-493)
-__host__ __device__ inline void ipe_grid(double dot, double xn, double cn, double eps, IpeGrid& g) {
+// a, epsilon_a and M of ipe / amplitude_estimation (Utility.py:725-733, :484).  Returns false for S = |x|^2 + |c|^2 <= 0
+// (the estimate is 0; kind = 0).  `a` is handed to ipe_grid_tail.
+__host__ __device__ inline bool ipe_grid_head(double dot, double xn, double cn, double eps, IpeGrid& g, double& a) {
     const double PI = 3.14159265358979323846;
     g.S = xn + cn;
     g.kind = 0;
-    g.M = 16.0; g.invM = 1.0 / 16.0; g.x = 0.0; g.j0 = 0.0; g.t = 0.0; g.c2t = 1.0;
-    if (!(g.S > 0.0)) return;
+    g.M = 16.0; g.invM = 1.0 / 16.0; g.rS = 0.0; g.x = 0.0; g.j0 = 0.0; g.t = 0.0; g.c2t = 1.0;
+    a = 0.0;
+    if (!(g.S > 0.0)) return false;
     // a = (S - 2 dot) / (2 S),  epsilon_a = eps max(1, |dot|) / S,  M = ceil(pi / (2 epsilon_a) (1 + sqrt(1 + 4 epsilon_a))):
     // the same quantities from ONE reciprocal, r = 1 / (S max(1, |dot|))  (1/S = r mx, S/mx = r S^2)
     const double mx = fmax(1.0, fabs(dot));
     const double r = 1.0 / (g.S * mx);
     const double rS = r * mx;
-    double a = fma(-dot, rS, 0.5);
+    g.rS = rS;
+    a = fma(-dot, rS, 0.5);
     if (a < 1e-15) a = 0.0;  // math.isclose(a, 0, abs_tol=1e-15) (Utility.py:730); negatives are rounding noise
     if (a > 1.0) a = 1.0;
     const double eps_a = eps * mx * rS;
     g.M = ceil(((PI / (2.0 * eps)) * (g.S * (r * g.S))) * (1.0 + sqrt(1.0 + 4.0 * eps_a)));
+    return true;
+}
+
+// theta_a and the position x = M theta_a / pi on the grid (Utility.py:493), after ipe_grid_head returned true
+__host__ __device__ inline void ipe_grid_tail(double a, IpeGrid& g) {
+    const double PI = 3.14159265358979323846;
     g.invM = 1.0 / g.M;
     // theta_a = asin(sqrt(a)) (Utility.py:493).  With c = 1 - 2a = cos(2 theta_a), theta_a = pi/4 - asin(c)/2; for the
     // usual pair (|x.c| a small fraction of |x|^2 + |c|^2) c is small and asin(c) is a short odd series - same
@@ -108,6 +118,27 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
     g.j0 = floor(g.x);
     g.t = g.x - g.j0;
     g.kind = (g.t == 0.0) ? 1 : 2;
+}
+
+__host__ __device__ inline void ipe_grid(double dot, double xn, double cn, double eps, IpeGrid& g) {
+    double a;
+    if (ipe_grid_head(dot, xn, cn, eps, g, a)) ipe_grid_tail(a, g);
+}
+
+// Can the pair be left out of the row's arg-min?  e_star = (some already sampled estimate of the same row) - |x|^2;
+// the pair is out if its own estimate is certainly larger.  With a* = (e_star + |x|^2) / (2 S) and r* the grid position
+// of a* (sin^2(pi r*/M) = a*), every outcome r <= r* lies at a circular distance >= x - r* >= d = M (a - a*) / pi from
+// x (sin^2 has slope <= 1), p(j) <= 1 / (4 dist^2) there, so F(r*) <= (d + 1) / (2 d^2) <= 1 / (2 (d - 1)) and
+// P(median <= r*) = G(F(r*)) <= 1716 F(r*)^7.  The median is the inversion of the pair's uniform V (ipe_lean /
+// ipe_tighten / ipe_brute all are): V > 1716 / (2 (d - 1))^7 therefore certifies median > r*, i.e. estimate > e_star.
+// Three grid points of margin cover the rounding of a, a* and d.  Pairs the inversion does not serve (x within
+// 4.5 points of M/2 on a grid of 64 or more: a > 1 - 200 / M^2) are never left out.  Exact: the labels, distances and
+// inertia are the ones the full computation gives.
+__host__ __device__ inline bool ipe_certainly_larger(const IpeGrid& g, double a, double xn, double e_star, double V) {
+    const double astar = (e_star + xn) * (0.5 * g.rS);
+    const double dd = g.M * (a - astar) * (1.0 / 3.14159265358979323846) - 3.0;      // <= d - 1 with margin
+    const double w = 2.0 * dd, w2 = w * w, w4 = w2 * w2;
+    return dd > 4.0 && (1.0 - a) * (g.M * g.M) > 250.0 && V * (w4 * w2 * w) > 1717.0;
 }
 
 // P(Binomial(13, F) >= 7) = F^7 sum_{i=0}^{6} C(6 + i, i) (1 - F)^i
@@ -399,10 +430,25 @@ __host__ __device__ inline int ipe_tighten(const IpeGrid& g, double V, double& m
     }
 }
 
-// the estimate |x|^2 + |c|^2 - 2 ipe(x, c) from the median's r (Utility.py:733-734, :520-531)
+// the estimate |x|^2 + |c|^2 - 2 ipe(x, c) from the median's r (Utility.py:733-734, :520-531): a function of (S, M, r)
+// alone, rounded the same way wherever it is inlined (no fused multiply-add across the call), so that equal outcomes
+// give equal distances whichever pass of the kernel produced them
 __host__ __device__ inline double ipe_value(const IpeGrid& g, double med) {
     const double sn = sq_sinpi(med * g.invM);
+#ifdef __CUDA_ARCH__
+    return __dmul_rn(__dmul_rn(2.0 * g.S, sn), sn);
+#else
     return 2.0 * g.S * sn * sn;
+#endif
+}
+
+// estimate - |x|^2, what the arg-min compares (one rounding, never fused with the product above)
+__host__ __device__ inline double ipe_minus(double v, double xn) {
+#ifdef __CUDA_ARCH__
+    return __dsub_rn(v, xn);
+#else
+    return v - xn;
+#endif
 }
 
 }  // namespace sq

@@ -54,6 +54,7 @@ struct AssignArgs {
     double* ipe_scratch;   // [grid][BM*BN] MODE_IPE: each CTA's tile of dot products, then of estimates
     size_t ipe_scratch_bytes;   // (host) capacity of ipe_scratch: bounds the grid
     int ipe_force_replay;       // test hook: every pair takes the draw-by-draw replay path of ipe.cuh
+    int ipe_prune;              // 1: pairs that certainly lose the row's arg-min are not sampled (same results)
     double* store;         // [n, k] MODE_STORE: x_i.c_j - cnorm[j]
     unsigned long long* colkey;  // [k] MODE_COLABS: max over rows of (bits(|y|) with the sign of y in bit 0)
     long long n;
@@ -335,15 +336,65 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 const int rows = (int)min((long long)BM, a.n - r0);
                 const int pairs = rows * kk;
                 const int rounds = (pairs + Cfg::THREADS - 1) / Cfg::THREADS;
-                // (the dot product of the next round is fetched while this round's estimate is computed)
-                // Pass 1, one pair per lane: the median of the 13 amplitude-estimation outcomes by one inversion
-                // (ipe_lean.cuh).  Pairs it declines before looking at its uniform (tiny grid, window touching 0 or
-                // M/2) are listed for the general estimator of ipe.cuh; pairs whose uniform falls inside the
-                // bracket of a threshold (0.3 %) are listed for the same inversion with the bracket tightened.
                 int* list = reinterpret_cast<int*>(sc + BM * BN);
                 constexpr int IPE_RESOLVE = 1 << 30;               // list flag: finish the inversion (same uniform)
                 if (tid == 0) *ipe_cnt = 0;
-                __syncthreads();
+                const double eps = 0.5 * a.delta;
+                const bool prune = a.ipe_prune && !a.ipe_force_replay;
+                double* estar_s = thr_s;                           // [BM] (WINDOW's array, free here)
+                int* cand_s = candcols;                            // [BM] (WINDOW's array, free here)
+                if (prune) {
+                    // Pass 0: the row's most promising centroid of this tile (smallest true distance) is sampled first
+                    // and in full; its estimate - or a smaller one from an earlier centroid tile - is what every other
+                    // pair of the row has to beat (ipe_certainly_larger).
+#pragma unroll 1
+                    for (int rr = warp; rr < rows; rr += Cfg::THREADS / 32) {
+                        double bv = INFINITY;
+                        int bc = 0x7fffffff;
+                        for (int c = lane; c < kk; c += 32) {
+                            const double v = fma(-2.0, sc[rr * BN + c], cn_s[n0 + c]);
+                            if (v < bv) { bv = v; bc = c; }
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
+                            const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
+                            if (ov < bv || (ov == bv && oc < bc)) { bv = ov; bc = oc; }
+                        }
+                        if (lane == 0) cand_s[rr] = (bc == 0x7fffffff) ? 0 : bc;
+                    }
+                    __syncthreads();
+                    constexpr int TPR = Cfg::THREADS / BM;         // one thread in TPR takes a row: spread over the warps
+                    if (tid % TPR == 0 && tid / TPR < rows) {
+                        const int row = tid / TPR, cl = cand_s[row];
+                        const double xn = xn_s[row];
+                        IpeGrid g;
+                        ipe_grid(sc[row * BN + cl], xn, cn_s[n0 + cl], eps, g);
+                        double e = INFINITY;
+                        if (g.kind == 2) {
+                            Philox rng(a.seed, a.offset + (unsigned long long)(r0 + row), IPE_TAG_MAIN, (unsigned)(n0 + cl));
+                            double u0, V, med = 0.0;
+                            rng.uniform2(u0, V);
+                            int st = ipe_lean(g, V, med);
+                            if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
+                            if (st == IPE_BRUTE) { med = ipe_brute(g, V); st = IPE_DONE; }
+                            if (st == IPE_DONE) e = ipe_minus(ipe_value(g, med), xn);
+                            else list[atomicAdd(ipe_cnt, 1)] = row * BN + cl;       // the general estimator's
+                        } else {
+                            e = ipe_minus((g.kind == 1) ? ipe_value(g, fmin(g.j0, g.M - g.j0)) : 0.0, xn);
+                        }
+                        if (e < INFINITY) sc[row * BN + cl] = e;
+                        estar_s[row] = fmin(e, nt > 0 ? run_m1[row] : INFINITY);
+                    }
+                }
+                __syncthreads();  // list counter, estar_s, cand_s
+                // Pass 1, one pair per lane: the median of the 13 amplitude-estimation outcomes by one inversion
+                // (ipe_lean.cuh).  Pairs whose estimate is certainly above the row's reference estimate are out
+                // (+inf) after the grid size and the uniform alone.  Pairs the inversion declines before looking at
+                // its uniform (window touching M/2) are listed for the general estimator of ipe.cuh; pairs whose
+                // uniform falls inside the bracket of a threshold, or whose median is to be summed plainly, are
+                // listed for the same inversion finished per lane.
+                // (the dot product of the next round is fetched while this round's estimate is computed)
                 int row = 0, cl = 0;
                 bool ok = tid < pairs;
                 if (ok) { row = tid / kk; cl = tid - row * kk; }
@@ -357,24 +408,34 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     if (cl2 >= kk) { cl2 -= kk; ++row2; }
                     if (!ok2) { row2 = 0; cl2 = 0; }
                     const double dot2 = sc[row2 * BN + cl2];
-                    if (ok) {
+                    if (ok && !(prune && cl == cand_s[row])) {
                         const double xn = xn_s[row];
                         IpeGrid g;
-                        ipe_grid(dot, xn, cn_s[n0 + cl], 0.5 * a.delta, g);
+                        double aa;
                         double v = 0.0;
                         int st = IPE_DONE;
-                        if (g.kind == 1) v = ipe_value(g, fmin(g.j0, g.M - g.j0));      // weight 1 at distance 0 (Utility.py:500-501)
-                        else if (g.kind == 2) {
-                            if (a.ipe_force_replay) st = IPE_GENERAL;
-                            else {
+                        if (ipe_grid_head(dot, xn, cn_s[n0 + cl], eps, g, aa)) {
+                            if (a.ipe_force_replay) {
+                                ipe_grid_tail(aa, g);
+                                if (g.kind == 1) v = ipe_value(g, fmin(g.j0, g.M - g.j0));
+                                else st = IPE_GENERAL;
+                            } else {
                                 Philox rng(a.seed, a.offset + (unsigned long long)(r0 + row), IPE_TAG_MAIN, (unsigned)(n0 + cl));
                                 double u0, V, med = 0.0;
                                 rng.uniform2(u0, V);
-                                st = ipe_lean(g, V, med);
-                                if (st == IPE_DONE) v = ipe_value(g, med);
+                                if (prune && ipe_certainly_larger(g, aa, xn, estar_s[row], V)) {
+                                    v = INFINITY;
+                                } else {
+                                    ipe_grid_tail(aa, g);
+                                    if (g.kind == 1) v = ipe_value(g, fmin(g.j0, g.M - g.j0));      // weight 1 at distance 0 (Utility.py:500-501)
+                                    else {
+                                        st = ipe_lean(g, V, med);
+                                        if (st == IPE_DONE) v = ipe_value(g, med);
+                                    }
+                                }
                             }
                         }
-                        if (st == IPE_DONE) sc[row * BN + cl] = v - xn;
+                        if (st == IPE_DONE) sc[row * BN + cl] = ipe_minus(v, xn);
                         else list[atomicAdd(ipe_cnt, 1)] = (row * BN + cl) | (st == IPE_GENERAL ? 0 : IPE_RESOLVE);
                     }
                     row = row2; cl = cl2; ok = ok2; dot = dot2;
@@ -397,7 +458,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     int st = ipe_lean(g, V, med);
                     if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
                     if (st == IPE_BRUTE) med = ipe_brute(g, V);
-                    sc[pos] = ipe_value(g, med) - xn;
+                    sc[pos] = ipe_minus(ipe_value(g, med), xn);
                 }
                 // Pass 2b: the general estimator (warp-cooperative: every lane of a warp calls it together, and its time
                 // grows with the number of live lanes - so the entries are dealt to the warps first here too)
@@ -413,7 +474,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     const double v = ipe_estimate_warp<false>(sc[pos], xn, okd ? cn_s[n0 + cld] : 0.0, 0.5 * a.delta, okd,
                                                               a.seed, a.offset + (unsigned long long)(r0 + rowd),
                                                               (unsigned)(n0 + cld), a.ipe_force_replay != 0, defer);
-                    if (okd) sc[pos] = v - xn;
+                    if (okd) sc[pos] = ipe_minus(v, xn);
                 }
                 __syncthreads();
 #pragma unroll
@@ -805,6 +866,7 @@ static size_t assign_smem_bytes() {
 // optional timing of the main kernel alone (bench.py's roofline leg): events are
 // recorded on the launching stream around the kernel when profiling is on
 static int g_ipe_force_replay = 0;
+static int g_ipe_prune = 1;
 static bool g_prof_on = false;
 static cudaEvent_t g_prof_ev[2] = {nullptr, nullptr};
 static double g_prof_ms = 0.0;
@@ -975,6 +1037,7 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     a.ipe_scratch = (double*)((char*)ws + need);            // whatever lies behind the fixed part
     a.ipe_scratch_bytes = ws_bytes - need;
     a.ipe_force_replay = g_ipe_force_replay;
+    a.ipe_prune = g_ipe_prune;
     int bn = 0;
     if (mode == MODE_WINDOW && k > 256) {
         // the window needs the row minimum over all k before candidates can be drawn
@@ -1024,7 +1087,8 @@ extern "C" int sq_ipe_debug_tail_sample(double M, double x, long long B, unsigne
 }
 
 extern "C" int sq_ipe_debug_force_replay(int on) {
-    g_ipe_force_replay = on ? 1 : 0;
+    g_ipe_force_replay = (on == 1) ? 1 : 0;
+    g_ipe_prune = (on == 0) ? 1 : 0;
     return SQ_OK;
 }
 

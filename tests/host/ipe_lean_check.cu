@@ -39,5 +39,46 @@ int main() {
         lean_cfgs += cnt[0] > 0;
     }
     printf("TOTAL disagreements %lld, regimes served by the lean path %lld\n", total_bad, lean_cfgs);
-    return (total_bad != 0 || lean_cfgs < 15) ? 1 : 0;
+
+    // The certificate that lets the kernel leave a pair out (ipe_certainly_larger): whenever it holds, the full
+    // computation with the same uniform must give an estimate above the reference estimate.  The uniform is put just
+    // above the certificate's own threshold, where it is weakest.
+    long long cert_n = 0, cert_bad = 0;
+    for (int regime = 0; regime < 6; ++regime) {
+        for (long long i = 0; i < 40000; ++i) {
+            const double eps = (regime >= 4) ? 1e-3 : (regime == 3) ? 0.05 : 0.25;
+            double xn = (regime == 0) ? 1.0 : 20.0 + 2000.0 * U(gen);
+            double cn = (regime == 0) ? 1.0 : (regime == 1 ? 1.0 : xn * (0.5 + U(gen)));
+            if (regime >= 4) cn = xn * (1.0 + 1e-3 * U(gen));
+            double dot = (2.0 * U(gen) - 1.0) * sqrt(xn * cn);
+            if (regime == 4) dot = -sqrt(xn * cn) * (1.0 - pow(10.0, -1.0 - 6.0 * U(gen)));   // nearly opposite: x next to M/2
+            if (regime == 5) dot = sqrt(xn * cn) * (1.0 - pow(10.0, -1.0 - 6.0 * U(gen)));    // nearly equal: x next to 0
+            IpeGrid g;
+            double a;
+            if (!ipe_grid_head(dot, xn, cn, eps, g, a)) continue;
+            // a reference estimate somewhere below this pair's true distance
+            const double e_star = (2.0 * g.S * a) * U(gen) - xn;
+            const double astar = (e_star + xn) * (0.5 * g.rS);
+            const double dd = g.M * (a - astar) * (1.0 / 3.14159265358979323846) - 3.0;
+            if (!(dd > 4.0)) continue;
+            double V = 1717.0 / pow(2.0 * dd, 7.0) * (1.0 + 1e-6 + U(gen) * ((i & 1) ? 1.0 : 1e-3));
+            if (!(V < 1.0)) continue;
+            if (!ipe_certainly_larger(g, a, xn, e_star, V)) continue;
+            ++cert_n;
+            ipe_grid_tail(a, g);
+            double v;
+            if (g.kind == 1) v = ipe_value(g, fmin(g.j0, g.M - g.j0));
+            else {
+                double med = -1.0;
+                int st = ipe_lean(g, V, med);
+                if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
+                if (st == IPE_BRUTE) { med = ipe_brute(g, V); st = IPE_DONE; }
+                if (st != IPE_DONE) { ++cert_bad; continue; }      // a pair of the general estimator must never be left out
+                v = ipe_value(g, med);
+            }
+            if (!(ipe_minus(v, xn) > e_star)) ++cert_bad;
+        }
+    }
+    printf("certificate: held for %lld pairs, violations %lld\n", cert_n, cert_bad);
+    return (total_bad != 0 || lean_cfgs < 15 || cert_bad != 0 || cert_n < 10000) ? 1 : 0;
 }

@@ -339,3 +339,44 @@ def test_ipe_mode_tends_to_exact_labels_for_small_delta(cuda, n, d, k):
     assert np.array_equal(li, le)
     S = (X * X).sum(axis=1) + (cen[lab] ** 2).sum(axis=1)
     assert np.all(np.abs(mi - me) <= 0.01 * S + 1e-9)
+
+
+PRUNE_CASES = [  # n, d, k, delta, how X and C are made
+    (5000, 16, 40, 0.5, "blobs"), (3000, 128, 256, 0.5, "blobs"), (2000, 8, 300, 0.3, "rand"),
+    (4000, 32, 17, 1.0, "unit"), (1000, 64, 600, 0.2, "blobs"), (3000, 5, 3, 2.0, "rand"),
+    (2000, 128, 256, 0.5, "datacentres"), (777, 3, 1, 0.5, "rand"), (1500, 20, 33, 0.05, "unit"),
+]
+
+
+@pytest.mark.parametrize("case", range(len(PRUNE_CASES)))
+def test_ipe_pairs_left_out_change_nothing(cuda, case):
+    """The IPE E-step does not sample a pair whose estimate certainly exceeds one already sampled in the same
+    row (csrc/ipe_lean.cuh: ipe_certainly_larger - a certificate from the pair's own uniform).  With the hook at 2
+    every pair is sampled: labels, distances and inertia must be the same bits - structured data, structureless
+    data, unit-norm centroids (the steady state of the noisy loop), centres that are data points (its first
+    iteration), one centroid, several centroid tiles."""
+    import gpu_util as G
+    from sqlearn import _cabi
+    n, d, k, delta, kind = PRUNE_CASES[case]
+    rng = np.random.default_rng(100 + case)
+    cen = rng.normal(size=(k, d)) * 4
+    X = cen[rng.integers(0, k, n)] + rng.normal(size=(n, d))
+    if kind == "blobs":
+        C = cen + 0.1 * rng.normal(size=(k, d))
+    elif kind == "rand":
+        X, C = rng.normal(size=(n, d)), rng.normal(size=(k, d))
+    elif kind == "unit":
+        C = cen / np.linalg.norm(cen, axis=1, keepdims=True)
+    else:
+        C = X[:k].copy()
+    out = []
+    for hook in (0, 2):
+        _cabi.lib.sq_ipe_debug_force_replay(hook)
+        try:
+            lab, mind, inertia, _ = G.assign(X, C, mode=2, delta=delta, seed=11 + case)
+        finally:
+            _cabi.lib.sq_ipe_debug_force_replay(0)
+        out.append((np.asarray(lab), np.asarray(mind), float(inertia)))
+    np.testing.assert_array_equal(out[0][0], out[1][0])
+    np.testing.assert_array_equal(out[0][1], out[1][1])
+    assert out[0][2] == out[1][2]
