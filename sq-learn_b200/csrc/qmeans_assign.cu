@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     int* run_cnt = run_a1 + BM;                              // [BM]
     double* cn_s = (double*)(run_cnt + BM);                  // [NT*BN] centroid norms (+inf past k)
     unsigned long long* full_bar = (unsigned long long*)(cn_s + a.NT * BN);  // [STAGES] TMA completion barriers
-    int* ipe_cnt = (int*)(full_bar + STAGES);                // [1] MODE_IPE: pairs left to the general pass
+    int* ipe_cnt = (int*)(full_bar + STAGES);                // [2] MODE_IPE: pairs listed for pass 2a / for the general estimator
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp / WN_CNT, wn = warp % WN_CNT;
@@ -337,8 +337,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 const int pairs = rows * kk;
                 const int rounds = (pairs + Cfg::THREADS - 1) / Cfg::THREADS;
                 int* list = reinterpret_cast<int*>(sc + BM * BN);
-                constexpr int IPE_RESOLVE = 1 << 30;               // list flag: finish the inversion (same uniform)
-                if (tid == 0) *ipe_cnt = 0;
+                if (tid == 0) { ipe_cnt[0] = 0; ipe_cnt[1] = 0; }
                 const double eps = 0.5 * a.delta;
                 const bool prune = a.ipe_prune && !a.ipe_force_replay;
                 double* estar_s = thr_s;                           // [BM] (WINDOW's array, free here)
@@ -379,7 +378,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                             if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
                             if (st == IPE_BRUTE) { med = ipe_brute(g, V); st = IPE_DONE; }
                             if (st == IPE_DONE) e = ipe_minus(ipe_value(g, med), xn);
-                            else list[atomicAdd(ipe_cnt, 1)] = row * BN + cl;       // the general estimator's
+                            else list[BM * BN - 1 - atomicAdd(ipe_cnt + 1, 1)] = row * BN + cl;       // the general estimator's
                         } else {
                             e = ipe_minus((g.kind == 1) ? ipe_value(g, fmin(g.j0, g.M - g.j0)) : 0.0, xn);
                         }
@@ -388,13 +387,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     }
                 }
                 __syncthreads();  // list counter, estar_s, cand_s
-                // Pass 1, one pair per lane: the median of the 13 amplitude-estimation outcomes by one inversion
-                // (ipe_lean.cuh).  Pairs whose estimate is certainly above the row's reference estimate are out
-                // (+inf) after the grid size and the uniform alone.  Pairs the inversion declines before looking at
-                // its uniform (window touching M/2) are listed for the general estimator of ipe.cuh; pairs whose
-                // uniform falls inside the bracket of a threshold, or whose median is to be summed plainly, are
-                // listed for the same inversion finished per lane.
-                // (the dot product of the next round is fetched while this round's estimate is computed)
+                // Pass 1, one pair per lane, no divergence: grid size and the pair's uniform; a pair whose estimate is
+                // certainly above the row's reference estimate is out (+inf), the others are listed (front of the
+                // list) for pass 2a.  With the replay hook everything goes to the general estimator (back of the list).
+                // (the dot product of the next round is fetched while this round's test is computed)
+                constexpr int LIST_CAP = BM * BN;
                 int row = 0, cl = 0;
                 bool ok = tid < pairs;
                 if (ok) { row = tid / kk; cl = tid - row * kk; }
@@ -408,70 +405,80 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     if (cl2 >= kk) { cl2 -= kk; ++row2; }
                     if (!ok2) { row2 = 0; cl2 = 0; }
                     const double dot2 = sc[row2 * BN + cl2];
+                    bool want = false;                             // to be sampled in pass 2a
                     if (ok && !(prune && cl == cand_s[row])) {
                         const double xn = xn_s[row];
                         IpeGrid g;
                         double aa;
-                        double v = 0.0;
-                        int st = IPE_DONE;
-                        if (ipe_grid_head(dot, xn, cn_s[n0 + cl], eps, g, aa)) {
-                            if (a.ipe_force_replay) {
-                                ipe_grid_tail(aa, g);
-                                if (g.kind == 1) v = ipe_value(g, fmin(g.j0, g.M - g.j0));
-                                else st = IPE_GENERAL;
-                            } else {
+                        if (!ipe_grid_head(dot, xn, cn_s[n0 + cl], eps, g, aa)) {
+                            sc[row * BN + cl] = ipe_minus(0.0, xn);                    // |x|^2 + |c|^2 = 0: the estimate is 0
+                        } else if (a.ipe_force_replay) {
+                            list[LIST_CAP - 1 - atomicAdd(ipe_cnt + 1, 1)] = row * BN + cl;
+                        } else {
+                            want = true;
+                            if (prune) {
                                 Philox rng(a.seed, a.offset + (unsigned long long)(r0 + row), IPE_TAG_MAIN, (unsigned)(n0 + cl));
-                                double u0, V, med = 0.0;
+                                double u0, V;
                                 rng.uniform2(u0, V);
-                                if (prune && ipe_certainly_larger(g, aa, xn, estar_s[row], V)) {
-                                    v = INFINITY;
-                                } else {
-                                    ipe_grid_tail(aa, g);
-                                    if (g.kind == 1) v = ipe_value(g, fmin(g.j0, g.M - g.j0));      // weight 1 at distance 0 (Utility.py:500-501)
-                                    else {
-                                        st = ipe_lean(g, V, med);
-                                        if (st == IPE_DONE) v = ipe_value(g, med);
-                                    }
+                                if (ipe_certainly_larger(g, aa, xn, estar_s[row], V)) {
+                                    sc[row * BN + cl] = INFINITY;
+                                    want = false;
                                 }
                             }
                         }
-                        if (st == IPE_DONE) sc[row * BN + cl] = ipe_minus(v, xn);
-                        else list[atomicAdd(ipe_cnt, 1)] = (row * BN + cl) | (st == IPE_GENERAL ? 0 : IPE_RESOLVE);
+                    }
+                    const unsigned wm_ = __ballot_sync(0xffffffffu, want);
+                    if (wm_) {
+                        int base = 0;
+                        if (lane == __ffs(wm_) - 1) base = atomicAdd(ipe_cnt, __popc(wm_));
+                        base = __shfl_sync(0xffffffffu, base, __ffs(wm_) - 1);
+                        if (want) list[base + __popc(wm_ & ((1u << lane) - 1u))] = row * BN + cl;
                     }
                     row = row2; cl = cl2; ok = ok2; dot = dot2;
                 }
                 __syncthreads();
-                const int ndef = *ipe_cnt;
-                // Pass 2a: finish the inversions (per lane; tens of pairs per tile, dealt to the warps first so that
-                // they run side by side instead of one after the other in the lanes of one warp)
+                const int nres = ipe_cnt[0];
+                // Pass 2a: the median of the 13 amplitude-estimation outcomes by one inversion (ipe_lean.cuh), one
+                // listed pair per lane (dealt to the warps first, so that a short list still runs side by side).  A
+                // pair the inversion declines before looking at its uniform (window touching M/2 on a large grid)
+                // moves to the back of the list for the general estimator.
 #pragma unroll 1
-                for (int li = lane * (Cfg::THREADS / 32) + warp; li < ndef; li += Cfg::THREADS) {
-                    const int e = list[li];
-                    if (!(e & IPE_RESOLVE)) continue;
-                    const int pos = e & (IPE_RESOLVE - 1), rowd = pos / BN, cld = pos - rowd * BN;
+                for (int li = lane * (Cfg::THREADS / 32) + warp; li < nres; li += Cfg::THREADS) {
+                    const int pos = list[li], rowd = pos / BN, cld = pos - rowd * BN;
                     const double xn = xn_s[rowd];
                     IpeGrid g;
-                    ipe_grid(sc[pos], xn, cn_s[n0 + cld], 0.5 * a.delta, g);
-                    Philox rng(a.seed, a.offset + (unsigned long long)(r0 + rowd), IPE_TAG_MAIN, (unsigned)(n0 + cld));
-                    double u0, V, med = 0.0;
-                    rng.uniform2(u0, V);
-                    int st = ipe_lean(g, V, med);
-                    if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
-                    if (st == IPE_BRUTE) med = ipe_brute(g, V);
-                    sc[pos] = ipe_minus(ipe_value(g, med), xn);
+                    ipe_grid(sc[pos], xn, cn_s[n0 + cld], eps, g);
+                    double v;
+                    if (g.kind == 1) {
+                        v = ipe_value(g, fmin(g.j0, g.M - g.j0));      // weight 1 at distance 0 (Utility.py:500-501)
+                    } else {
+                        Philox rng(a.seed, a.offset + (unsigned long long)(r0 + rowd), IPE_TAG_MAIN, (unsigned)(n0 + cld));
+                        double u0, V, med = 0.0;
+                        rng.uniform2(u0, V);
+                        int st = ipe_lean(g, V, med);
+                        if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
+                        if (st == IPE_BRUTE) { med = ipe_brute(g, V); st = IPE_DONE; }
+                        if (st != IPE_DONE) {
+                            list[LIST_CAP - 1 - atomicAdd(ipe_cnt + 1, 1)] = pos;
+                            continue;
+                        }
+                        v = ipe_value(g, med);
+                    }
+                    sc[pos] = ipe_minus(v, xn);
                 }
+                __syncthreads();
+                const int ngen = ipe_cnt[1];
                 // Pass 2b: the general estimator (warp-cooperative: every lane of a warp calls it together, and its time
                 // grows with the number of live lanes - so the entries are dealt to the warps first here too)
 #pragma unroll 1
-                for (int it = 0; it * Cfg::THREADS < ndef; ++it) {
+                for (int it = 0; it * Cfg::THREADS < ngen; ++it) {
                     const int li = it * Cfg::THREADS + lane * (Cfg::THREADS / 32) + warp;
-                    const int e = li < ndef ? list[li] : IPE_RESOLVE;
-                    const bool okd = !(e & IPE_RESOLVE);
-                    const int pos = okd ? e : 0;
+                    const bool okd = li < ngen;
+                    const int pos = okd ? list[LIST_CAP - 1 - li] : 0;
                     const int rowd = pos / BN, cld = pos - rowd * BN;
                     const double xn = xn_s[rowd];
                     bool defer;
-                    const double v = ipe_estimate_warp<false>(sc[pos], xn, okd ? cn_s[n0 + cld] : 0.0, 0.5 * a.delta, okd,
+                    const double v = ipe_estimate_warp<false>(sc[pos], xn, okd ? cn_s[n0 + cld] : 0.0, eps, okd,
                                                               a.seed, a.offset + (unsigned long long)(r0 + rowd),
                                                               (unsigned)(n0 + cld), a.ipe_force_replay != 0, defer);
                     if (okd) sc[pos] = ipe_minus(v, xn);
