@@ -131,14 +131,22 @@ __host__ __device__ inline void ipe_grid(double dot, double xn, double cn, doubl
 // x (sin^2 has slope <= 1), p(j) <= 1 / (4 dist^2) there, so F(r*) <= (d + 1) / (2 d^2) <= 1 / (2 (d - 1)) and
 // P(median <= r*) = G(F(r*)) <= 1716 F(r*)^7.  The median is the inversion of the pair's uniform V (ipe_lean /
 // ipe_tighten / ipe_brute all are): V > 1716 / (2 (d - 1))^7 therefore certifies median > r*, i.e. estimate > e_star.
-// Three grid points of margin cover the rounding of a, a* and d.  Pairs the inversion does not serve (x within
-// 4.5 points of M/2 on a grid of 64 or more: a > 1 - 200 / M^2) are never left out.  Exact: the labels, distances and
-// inertia are the ones the full computation gives.
-__host__ __device__ inline bool ipe_certainly_larger(const IpeGrid& g, double a, double xn, double e_star, double V) {
-    const double astar = (e_star + xn) * (0.5 * g.rS);
-    const double dd = g.M * (a - astar) * (1.0 / 3.14159265358979323846) - 3.0;      // <= d - 1 with margin
-    const double w = 2.0 * dd, w2 = w * w, w4 = w2 * w2;
-    return dd > 4.0 && (1.0 - a) * (g.M * g.M) > 250.0 && V * (w4 * w2 * w) > 1717.0;
+// No grid is needed for it: M >= pi / epsilon_a = pi S / (eps mx), mx = max(1, |x.c|), and a - a* =
+// (|c|^2 - 2 x.c - e_star) / (2 S), so d >= D / (2 eps mx) with D = (true distance - |x|^2) - e_star: S cancels, no
+// division, no square root.  Three grid points of margin (6 eps mx off D) cover the roundings and the clamps of a.
+// Pairs the inversion does not serve (x within 4.5 points of M/2 on a grid of 64 or more, i.e. (1 - a) M^2 < 200:
+// nearly opposite vectors) are never left out: (S + 2 x.c) S pi^2 > 500 (eps mx)^2 is asked for.
+// Returns false if the pair must be sampled whatever its uniform; otherwise the pair is out iff V * lhs > rhs.
+// Exact: the labels, distances and inertia are the ones the full computation gives.
+__host__ __device__ inline bool ipe_out_possible(double dot, double xn, double cn, double eps, double e_star, double& lhs,
+                                                 double& rhs) {
+    const double PI = 3.14159265358979323846;
+    const double S = xn + cn, em = eps * fmax(1.0, fabs(dot));
+    const double D = fma(-2.0, dot, cn) - e_star - 6.0 * em;          // = 2 eps mx (d - 3)
+    const double D2 = D * D, D4 = D2 * D2, e2 = em * em, e4 = e2 * e2;
+    lhs = D4 * D2 * D;
+    rhs = 1717.0 * (e4 * e2 * em);
+    return D > 8.0 * em && fma(2.0, dot, S) * S * (PI * PI) > 500.0 * e2;
 }
 
 // P(Binomial(13, F) >= 7) = F^7 sum_{i=0}^{6} C(6 + i, i) (1 - F)^i

@@ -407,20 +407,19 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     const double dot2 = sc[row2 * BN + cl2];
                     bool want = false;                             // to be sampled in pass 2a
                     if (ok && !(prune && cl == cand_s[row])) {
-                        const double xn = xn_s[row];
-                        IpeGrid g;
-                        double aa;
-                        if (!ipe_grid_head(dot, xn, cn_s[n0 + cl], eps, g, aa)) {
+                        const double xn = xn_s[row], cn = cn_s[n0 + cl];
+                        if (!(xn + cn > 0.0)) {
                             sc[row * BN + cl] = ipe_minus(0.0, xn);                    // |x|^2 + |c|^2 = 0: the estimate is 0
                         } else if (a.ipe_force_replay) {
                             list[LIST_CAP - 1 - atomicAdd(ipe_cnt + 1, 1)] = row * BN + cl;
                         } else {
                             want = true;
-                            if (prune) {
+                            double lhs, rhs;
+                            if (prune && ipe_out_possible(dot, xn, cn, eps, estar_s[row], lhs, rhs)) {
                                 Philox rng(a.seed, a.offset + (unsigned long long)(r0 + row), IPE_TAG_MAIN, (unsigned)(n0 + cl));
                                 double u0, V;
                                 rng.uniform2(u0, V);
-                                if (ipe_certainly_larger(g, aa, xn, estar_s[row], V)) {
+                                if (V * lhs > rhs) {
                                     sc[row * BN + cl] = INFINITY;
                                     want = false;
                                 }

@@ -40,7 +40,7 @@ int main() {
     }
     printf("TOTAL disagreements %lld, regimes served by the lean path %lld\n", total_bad, lean_cfgs);
 
-    // The certificate that lets the kernel leave a pair out (ipe_certainly_larger): whenever it holds, the full
+    // The certificate that lets the kernel leave a pair out (ipe_out_possible): whenever it holds, the full
     // computation with the same uniform must give an estimate above the reference estimate.  The uniform is put just
     // above the certificate's own threshold, where it is weakest.
     long long cert_n = 0, cert_bad = 0;
@@ -58,12 +58,10 @@ int main() {
             if (!ipe_grid_head(dot, xn, cn, eps, g, a)) continue;
             // a reference estimate somewhere below this pair's true distance
             const double e_star = (2.0 * g.S * a) * U(gen) - xn;
-            const double astar = (e_star + xn) * (0.5 * g.rS);
-            const double dd = g.M * (a - astar) * (1.0 / 3.14159265358979323846) - 3.0;
-            if (!(dd > 4.0)) continue;
-            double V = 1717.0 / pow(2.0 * dd, 7.0) * (1.0 + 1e-6 + U(gen) * ((i & 1) ? 1.0 : 1e-3));
-            if (!(V < 1.0)) continue;
-            if (!ipe_certainly_larger(g, a, xn, e_star, V)) continue;
+            double lhs, rhs;
+            if (!ipe_out_possible(dot, xn, cn, eps, e_star, lhs, rhs)) continue;
+            const double V = rhs / lhs * (1.0 + 1e-6 + U(gen) * ((i & 1) ? 1.0 : 1e-3));
+            if (!(V < 1.0) || !(V * lhs > rhs)) continue;
             ++cert_n;
             ipe_grid_tail(a, g);
             double v;
