@@ -31,6 +31,20 @@ namespace sq {
 
 enum { IPE_DONE = 0, IPE_GENERAL = 1, IPE_TIGHTEN = 2, IPE_BRUTE = 3 };
 
+// The inversion's uniform V of the pair (row, col): stream (seed, row, IPE_TAG_PAIR, col / 2), whose one block serves the
+// two columns 2c and 2c + 1 (the two a lane of the E-step kernel owns side by side).  The general estimator of ipe.cuh
+// draws from other tags, so a pair it serves stays independent of its neighbour.
+static constexpr uint32_t IPE_TAG_PAIR = 0x1bE1u;
+__host__ __device__ inline void ipe_pair_uniforms(uint64_t seed, uint64_t rowkey, uint32_t col_even, double& v_even, double& v_odd) {
+    Philox rng(seed, rowkey, IPE_TAG_PAIR, col_even >> 1);
+    rng.uniform2(v_even, v_odd);
+}
+__host__ __device__ inline double ipe_pair_uniform(uint64_t seed, uint64_t rowkey, uint32_t col) {
+    double ve, vo;
+    ipe_pair_uniforms(seed, rowkey, col & ~1u, ve, vo);
+    return (col & 1u) ? vo : ve;
+}
+
 struct IpeGrid {
     double S;      // |x|^2 + |c|^2
     double M;      // grid size of amplitude estimation (Utility.py:484)

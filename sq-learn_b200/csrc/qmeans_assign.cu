@@ -334,8 +334,6 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 __syncthreads();  // xn_s, sc
                 const int kk = min(BN, a.k - n0);                  // live columns of this centroid tile
                 const int rows = (int)min((long long)BM, a.n - r0);
-                const int pairs = rows * kk;
-                const int rounds = (pairs + Cfg::THREADS - 1) / Cfg::THREADS;
                 int* list = reinterpret_cast<int*>(sc + BM * BN);
                 if (tid == 0) { ipe_cnt[0] = 0; ipe_cnt[1] = 0; }
                 const double eps = 0.5 * a.delta;
@@ -346,21 +344,36 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     // Pass 0: the row's most promising centroid of this tile (smallest true distance) is sampled first
                     // and in full; its estimate - or a smaller one from an earlier centroid tile - is what every other
                     // pair of the row has to beat (ipe_certainly_larger).
-#pragma unroll 1
-                    for (int rr = warp; rr < rows; rr += Cfg::THREADS / 32) {
-                        double bv = INFINITY;
-                        int bc = 0x7fffffff;
-                        for (int c = lane; c < kk; c += 32) {
-                            const double v = fma(-2.0, sc[rr * BN + c], cn_s[n0 + c]);
-                            if (v < bv) { bv = v; bc = c; }
-                        }
+                    // (any column would do as the reference, so the arg-min is taken on keys: |c|^2 - 2 x.c with the
+                    // column in its low 8 mantissa bits, straight from the accumulators)
+                    static_assert(BN <= 256, "the candidate key carries the column in 8 bits");
 #pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) {
-                            const double ov = __shfl_xor_sync(0xffffffffu, bv, o);
-                            const int oc = __shfl_xor_sync(0xffffffffu, bc, o);
-                            if (ov < bv || (ov == bv && oc < bc)) { bv = ov; bc = oc; }
+                    for (int i = 0; i < MI; ++i) {
+                        double key = INFINITY;
+#pragma unroll
+                        for (int j = 0; j < NI; ++j)
+#pragma unroll
+                            for (int e = 0; e < 2; ++e) {
+                                const int col = cl0 + j * 8 + e;
+                                const double v = fma(-2.0, acc[i][j][e], cn_s[n0 + col]);          // +inf past k
+                                const double kv = __longlong_as_double((__double_as_longlong(v) & ~0xffLL) | (long long)col);
+                                key = dmin(key, (v < INFINITY) ? kv : INFINITY);
+                            }
+                        key = dmin(key, __shfl_xor_sync(0xffffffffu, key, 1));
+                        key = dmin(key, __shfl_xor_sync(0xffffffffu, key, 2));
+                        if (lr4 == 0) wmin[(wm * Cfg::WM + i * 8 + lq) * WN_CNT + wn] = key;
+                    }
+                    __syncthreads();
+                    {
+                        constexpr int ENTRIES = BM * WN_CNT;
+                        for (int e0 = 0; e0 < ENTRIES; e0 += Cfg::THREADS) {
+                            const int e = e0 + tid;
+                            double m = (e < ENTRIES) ? wmin[e] : INFINITY;
+#pragma unroll
+                            for (int o = 1; o < WN_CNT; o <<= 1) m = dmin(m, __shfl_xor_sync(0xffffffffu, m, o));
+                            if (e < ENTRIES && (e % WN_CNT) == 0)
+                                cand_s[e / WN_CNT] = (m < INFINITY) ? (int)(__double_as_longlong(m) & 0xffLL) : 0;
                         }
-                        if (lane == 0) cand_s[rr] = (bc == 0x7fffffff) ? 0 : bc;
                     }
                     __syncthreads();
                     constexpr int TPR = Cfg::THREADS / BM;         // one thread in TPR takes a row: spread over the warps
@@ -371,9 +384,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                         ipe_grid(sc[row * BN + cl], xn, cn_s[n0 + cl], eps, g);
                         double e = INFINITY;
                         if (g.kind == 2) {
-                            Philox rng(a.seed, a.offset + (unsigned long long)(r0 + row), IPE_TAG_MAIN, (unsigned)(n0 + cl));
-                            double u0, V, med = 0.0;
-                            rng.uniform2(u0, V);
+                            const double V = ipe_pair_uniform(a.seed, a.offset + (unsigned long long)(r0 + row), (unsigned)(n0 + cl));
+                            double med = 0.0;
                             int st = ipe_lean(g, V, med);
                             if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
                             if (st == IPE_BRUTE) { med = ipe_brute(g, V); st = IPE_DONE; }
@@ -392,48 +404,59 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 // list) for pass 2a.  With the replay hook everything goes to the general estimator (back of the list).
                 // (the dot product of the next round is fetched while this round's test is computed)
                 constexpr int LIST_CAP = BM * BN;
-                int row = 0, cl = 0;
-                bool ok = tid < pairs;
-                if (ok) { row = tid / kk; cl = tid - row * kk; }
-                const int drow = Cfg::THREADS / kk, dcl = Cfg::THREADS - drow * kk;     // one round further on
-                double dot = sc[row * BN + cl];
+                // (one unit = the columns 2c and 2c + 1 of a row: they share one block of the generator; the dot
+                // products of the next round are fetched while this round's test is computed)
+                const int hk = (kk + 1) >> 1, units = rows * hk;
+                const int urounds = (units + Cfg::THREADS - 1) / Cfg::THREADS;
+                int row = 0, c2 = 0;
+                bool ok = tid < units;
+                if (ok) { row = tid / hk; c2 = tid - row * hk; }
+                const int drow = Cfg::THREADS / hk, dc2 = Cfg::THREADS - drow * hk;     // one round further on
+                double2 dots = *reinterpret_cast<const double2*>(sc + row * BN + 2 * c2);
 #pragma unroll 1
-                for (int it = 0; it < rounds; ++it) {
-                    const int idx2 = (it + 1) * Cfg::THREADS + tid;
-                    const bool ok2 = idx2 < pairs;
-                    int row2 = row + drow, cl2 = cl + dcl;
-                    if (cl2 >= kk) { cl2 -= kk; ++row2; }
-                    if (!ok2) { row2 = 0; cl2 = 0; }
-                    const double dot2 = sc[row2 * BN + cl2];
-                    bool want = false;                             // to be sampled in pass 2a
-                    if (ok && !(prune && cl == cand_s[row])) {
-                        const double xn = xn_s[row], cn = cn_s[n0 + cl];
-                        if (!(xn + cn > 0.0)) {
-                            sc[row * BN + cl] = ipe_minus(0.0, xn);                    // |x|^2 + |c|^2 = 0: the estimate is 0
-                        } else if (a.ipe_force_replay) {
-                            list[LIST_CAP - 1 - atomicAdd(ipe_cnt + 1, 1)] = row * BN + cl;
-                        } else {
-                            want = true;
-                            double lhs, rhs;
-                            if (prune && ipe_out_possible(dot, xn, cn, eps, estar_s[row], lhs, rhs)) {
-                                Philox rng(a.seed, a.offset + (unsigned long long)(r0 + row), IPE_TAG_MAIN, (unsigned)(n0 + cl));
-                                double u0, V;
-                                rng.uniform2(u0, V);
-                                if (V * lhs > rhs) {
-                                    sc[row * BN + cl] = INFINITY;
-                                    want = false;
-                                }
+                for (int it = 0; it < urounds; ++it) {
+                    const bool ok2 = (it + 1) * Cfg::THREADS + tid < units;
+                    int row2 = row + drow, c22 = c2 + dc2;
+                    if (c22 >= hk) { c22 -= hk; ++row2; }
+                    if (!ok2) { row2 = 0; c22 = 0; }
+                    const double2 dots2 = *reinterpret_cast<const double2*>(sc + row2 * BN + 2 * c22);
+                    const int cl = 2 * c2;
+                    const double xn = xn_s[row];
+                    const double dot[2] = {dots.x, dots.y};
+                    double lhs[2] = {0.0, 0.0}, rhs[2] = {0.0, 0.0};
+                    bool want[2] = {false, false}, poss[2] = {false, false};  // want: to be sampled in pass 2a
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        if (ok && cl + e < kk && !(prune && cl + e == cand_s[row])) {
+                            const double cn = cn_s[n0 + cl + e];
+                            if (!(xn + cn > 0.0)) {
+                                sc[row * BN + cl + e] = ipe_minus(0.0, xn);                // |x|^2 + |c|^2 = 0: the estimate is 0
+                            } else if (a.ipe_force_replay) {
+                                list[LIST_CAP - 1 - atomicAdd(ipe_cnt + 1, 1)] = row * BN + cl + e;
+                            } else {
+                                want[e] = true;
+                                poss[e] = prune && ipe_out_possible(dot[e], xn, cn, eps, estar_s[row], lhs[e], rhs[e]);
                             }
                         }
                     }
-                    const unsigned wm_ = __ballot_sync(0xffffffffu, want);
-                    if (wm_) {
-                        int base = 0;
-                        if (lane == __ffs(wm_) - 1) base = atomicAdd(ipe_cnt, __popc(wm_));
-                        base = __shfl_sync(0xffffffffu, base, __ffs(wm_) - 1);
-                        if (want) list[base + __popc(wm_ & ((1u << lane) - 1u))] = row * BN + cl;
+                    if (poss[0] || poss[1]) {
+                        double V[2];
+                        ipe_pair_uniforms(a.seed, a.offset + (unsigned long long)(r0 + row), (unsigned)(n0 + cl), V[0], V[1]);
+#pragma unroll
+                        for (int e = 0; e < 2; ++e)
+                            if (poss[e] && V[e] * lhs[e] > rhs[e]) { sc[row * BN + cl + e] = INFINITY; want[e] = false; }
                     }
-                    row = row2; cl = cl2; ok = ok2; dot = dot2;
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const unsigned wm_ = __ballot_sync(0xffffffffu, want[e]);
+                        if (wm_) {
+                            int base = 0;
+                            if (lane == __ffs(wm_) - 1) base = atomicAdd(ipe_cnt, __popc(wm_));
+                            base = __shfl_sync(0xffffffffu, base, __ffs(wm_) - 1);
+                            if (want[e]) list[base + __popc(wm_ & ((1u << lane) - 1u))] = row * BN + cl + e;
+                        }
+                    }
+                    row = row2; c2 = c22; ok = ok2; dots = dots2;
                 }
                 __syncthreads();
                 const int nres = ipe_cnt[0];
@@ -451,9 +474,8 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     if (g.kind == 1) {
                         v = ipe_value(g, fmin(g.j0, g.M - g.j0));      // weight 1 at distance 0 (Utility.py:500-501)
                     } else {
-                        Philox rng(a.seed, a.offset + (unsigned long long)(r0 + rowd), IPE_TAG_MAIN, (unsigned)(n0 + cld));
-                        double u0, V, med = 0.0;
-                        rng.uniform2(u0, V);
+                        const double V = ipe_pair_uniform(a.seed, a.offset + (unsigned long long)(r0 + rowd), (unsigned)(n0 + cld));
+                        double med = 0.0;
                         int st = ipe_lean(g, V, med);
                         if (st == IPE_TIGHTEN) st = ipe_tighten(g, V, med);
                         if (st == IPE_BRUTE) { med = ipe_brute(g, V); st = IPE_DONE; }
