@@ -105,6 +105,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
     double* cn_s = (double*)(run_cnt + BM);                  // [NT*BN] centroid norms (+inf past k)
     unsigned long long* full_bar = (unsigned long long*)(cn_s + a.NT * BN);  // [STAGES] TMA completion barriers
     int* ipe_cnt = (int*)(full_bar + STAGES);                // [2] MODE_IPE: pairs listed for pass 2a / for the general estimator
+    unsigned* keep_s = (unsigned*)(ipe_cnt + 2);             // [BM*BN/32] MODE_IPE: bit (row*BN + col) = the pair's value comes back from the workspace
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp / WN_CNT, wn = warp % WN_CNT;
@@ -331,7 +332,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     for (int j = 0; j < NI; ++j)
                         *reinterpret_cast<double2*>(sc + (wm * Cfg::WM + i * 8 + lq) * BN + cl0 + j * 8) =
                             make_double2(acc[i][j][0], acc[i][j][1]);
-                __syncthreads();  // xn_s, sc
+                for (int w = tid; w < BM * BN / 32; w += Cfg::THREADS) keep_s[w] = 0u;
                 const int kk = min(BN, a.k - n0);                  // live columns of this centroid tile
                 const int rows = (int)min((long long)BM, a.n - r0);
                 int* list = reinterpret_cast<int*>(sc + BM * BN);
@@ -395,6 +396,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                             e = ipe_minus((g.kind == 1) ? ipe_value(g, fmin(g.j0, g.M - g.j0)) : 0.0, xn);
                         }
                         if (e < INFINITY) sc[row * BN + cl] = e;
+                        atomicOr(&keep_s[(row * BN + cl) >> 5], 1u << ((row * BN + cl) & 31));
                         estar_s[row] = fmin(e, nt > 0 ? run_m1[row] : INFINITY);
                     }
                 }
@@ -431,8 +433,10 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                             const double cn = cn_s[n0 + cl + e];
                             if (!(xn + cn > 0.0)) {
                                 sc[row * BN + cl + e] = ipe_minus(0.0, xn);                // |x|^2 + |c|^2 = 0: the estimate is 0
+                                atomicOr(&keep_s[(row * BN + cl + e) >> 5], 1u << ((row * BN + cl + e) & 31));
                             } else if (a.ipe_force_replay) {
                                 list[LIST_CAP - 1 - atomicAdd(ipe_cnt + 1, 1)] = row * BN + cl + e;
+                                atomicOr(&keep_s[(row * BN + cl + e) >> 5], 1u << ((row * BN + cl + e) & 31));
                             } else {
                                 want[e] = true;
                                 poss[e] = prune && ipe_out_possible(dot[e], xn, cn, eps, estar_s[row], lhs[e], rhs[e]);
@@ -444,7 +448,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                         ipe_pair_uniforms(a.seed, a.offset + (unsigned long long)(r0 + row), (unsigned)(n0 + cl), V[0], V[1]);
 #pragma unroll
                         for (int e = 0; e < 2; ++e)
-                            if (poss[e] && V[e] * lhs[e] > rhs[e]) { sc[row * BN + cl + e] = INFINITY; want[e] = false; }
+                            if (poss[e] && V[e] * lhs[e] > rhs[e]) want[e] = false;          // out: its bit stays clear
                     }
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
@@ -453,7 +457,10 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                             int base = 0;
                             if (lane == __ffs(wm_) - 1) base = atomicAdd(ipe_cnt, __popc(wm_));
                             base = __shfl_sync(0xffffffffu, base, __ffs(wm_) - 1);
-                            if (want[e]) list[base + __popc(wm_ & ((1u << lane) - 1u))] = row * BN + cl + e;
+                            if (want[e]) {
+                                list[base + __popc(wm_ & ((1u << lane) - 1u))] = row * BN + cl + e;
+                                atomicOr(&keep_s[(row * BN + cl + e) >> 5], 1u << ((row * BN + cl + e) & 31));
+                            }
                         }
                     }
                     row = row2; c2 = c22; ok = ok2; dots = dots2;
@@ -510,10 +517,11 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                     const int row = wm * Cfg::WM + i * 8 + lq;
 #pragma unroll
                     for (int j = 0; j < NI; ++j) {
-                        const double2 v2 = *reinterpret_cast<const double2*>(sc + row * BN + cl0 + j * 8);
-                        const int col = colbase + j * 8;
-                        acc[i][j][0] = (row < rows && col < a.k) ? v2.x : INFINITY;
-                        acc[i][j][1] = (row < rows && col + 1 < a.k) ? v2.y : INFINITY;
+                        // (only the pairs that were sampled come back; the others are out: +inf)
+                        const int lc = cl0 + j * 8;
+                        const unsigned kb2 = (keep_s[(row * BN + lc) >> 5] >> ((row * BN + lc) & 31)) & 3u;
+                        acc[i][j][0] = (kb2 & 1u) ? sc[row * BN + lc] : INFINITY;
+                        acc[i][j][1] = (kb2 & 2u) ? sc[row * BN + lc + 1] : INFINITY;
                     }
                 }
             }
@@ -930,7 +938,7 @@ static int launch_assign(AssignArgs a, cudaStream_t stream) {
         int r2 = make_tensor_map_2d(&tmB, a.C, (unsigned long long)a.d, (unsigned long long)a.k, 4, Cfg::BN);
         if (r1 || r2) use_tma = false;  // driver without the encoder: 8-byte cp.async path
     }
-    smem += Cfg::STAGES * sizeof(unsigned long long) + 8;
+    smem += Cfg::STAGES * sizeof(unsigned long long) + 8 + (size_t)Cfg::BM * Cfg::BN / 8;   // barriers, two counters, IPE's keep bits
     // persistent grid: one CTA per resident slot, tiles handed out by static striding
 #define SQ_LAUNCH_ASSIGN(V, M, T)                                                                                     \
     do {                                                                                                            \
