@@ -13,6 +13,9 @@
 //                                     ipe = median of 13 amplitude-estimation
 //                                     draws (:753-769), then argmin
 // In every mode the reported inertia is sum_i min_j D_ij (:751, :773-775).
+// IPE draws the median by one inversion per pair (ipe_lean.cuh) and leaves out, with a certificate from the pair's own
+// uniform, the pairs whose estimate certainly exceeds one already sampled in the row: labels, distances and inertia are
+// those of sampling every pair.
 //
 // Layout: X [n, d] and C [k, d] row-major fp64.  One CTA owns BM rows and
 // sweeps BN centroids at a time; X and C stream through a STAGES-deep
@@ -320,10 +323,10 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 if (MODE != MODE_WINDOW || nt == 0) { cnt[tid] = 0; first[tid] = 0x7fffffff; }
             }
             if (MODE == MODE_IPE) {
-                // Every pair is sampled: the accumulator becomes (noisy squared distance - |x|^2).  The tile of
-                // dot products is parked in this CTA's slice of the workspace (L2-resident), so that the
-                // sampler runs with the whole register file instead of beside 2*MI*NI live accumulators, and
-                // the pairs are dealt to the lanes as a flat list (no idle lanes for k < BN).
+                // The accumulator (x.c) becomes (noisy squared distance - |x|^2), or +inf for a pair that certainly
+                // loses the row's arg-min.  The tile of dot products is parked in this CTA's slice of the workspace
+                // (L2-resident), so that the sampler runs with the whole register file instead of beside 2*MI*NI
+                // live accumulators, and the pairs are dealt to the lanes as a flat list (no idle lanes for k < BN).
                 double* sc = a.ipe_scratch + (size_t)blockIdx.x * (BM * BN + BM * BN / 2);   // dots, then the pass-2 list
                 const int cl0 = wn * Cfg::WN + lr4 * 2;
 #pragma unroll
@@ -344,7 +347,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 if (prune) {
                     // Pass 0: the row's most promising centroid of this tile (smallest true distance) is sampled first
                     // and in full; its estimate - or a smaller one from an earlier centroid tile - is what every other
-                    // pair of the row has to beat (ipe_certainly_larger).
+                    // pair of the row has to beat (ipe_out_possible).
                     // (any column would do as the reference, so the arg-min is taken on keys: |c|^2 - 2 x.c with the
                     // column in its low 8 mantissa bits, straight from the accumulators)
                     static_assert(BN <= 256, "the candidate key carries the column in 8 bits");

@@ -351,7 +351,7 @@ PRUNE_CASES = [  # n, d, k, delta, how X and C are made
 @pytest.mark.parametrize("case", range(len(PRUNE_CASES)))
 def test_ipe_pairs_left_out_change_nothing(cuda, case):
     """The IPE E-step does not sample a pair whose estimate certainly exceeds one already sampled in the same
-    row (csrc/ipe_lean.cuh: ipe_certainly_larger - a certificate from the pair's own uniform).  With the hook at 2
+    row (csrc/ipe_lean.cuh: ipe_out_possible - a certificate from the pair's own uniform).  With the hook at 2
     every pair is sampled: labels, distances and inertia must be the same bits - structured data, structureless
     data, unit-norm centroids (the steady state of the noisy loop), centres that are data points (its first
     iteration), one centroid, several centroid tiles."""
