@@ -380,9 +380,9 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                         }
                     }
                     __syncthreads();
-                    constexpr int TPR = Cfg::THREADS / BM;         // one thread in TPR takes a row: spread over the warps
-                    if (tid % TPR == 0 && tid / TPR < rows) {
-                        const int row = tid / TPR, cl = cand_s[row];
+                    static_assert(BM <= Cfg::THREADS, "one thread per row");
+                    if (tid < rows) {                              // full warps: the chain is as long, the issue slots are not
+                        const int row = tid, cl = cand_s[row];
                         const double xn = xn_s[row];
                         IpeGrid g;
                         ipe_grid(sc[row * BN + cl], xn, cn_s[n0 + cl], eps, g);
@@ -471,11 +471,12 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 __syncthreads();
                 const int nres = ipe_cnt[0];
                 // Pass 2a: the median of the 13 amplitude-estimation outcomes by one inversion (ipe_lean.cuh), one
-                // listed pair per lane (dealt to the warps first, so that a short list still runs side by side).  A
-                // pair the inversion declines before looking at its uniform (window touching M/2 on a large grid)
-                // moves to the back of the list for the general estimator.
+                // listed pair per lane, packed into as few warps as possible (a short list is one dependent chain
+                // either way; full warps leave the issue slots to the CTA next door).  A pair the inversion declines
+                // before looking at its uniform (window touching M/2 on a large grid) moves to the back of the list for
+                // the general estimator.
 #pragma unroll 1
-                for (int li = lane * (Cfg::THREADS / 32) + warp; li < nres; li += Cfg::THREADS) {
+                for (int li = tid; li < nres; li += Cfg::THREADS) {
                     const int pos = list[li], rowd = pos / BN, cld = pos - rowd * BN;
                     const double xn = xn_s[rowd];
                     IpeGrid g;
