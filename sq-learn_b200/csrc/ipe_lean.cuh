@@ -31,18 +31,24 @@ namespace sq {
 
 enum { IPE_DONE = 0, IPE_GENERAL = 1, IPE_TIGHTEN = 2, IPE_BRUTE = 3 };
 
-// The inversion's uniform V of the pair (row, col): stream (seed, row, IPE_TAG_PAIR, col / 2), whose one block serves the
-// two columns 2c and 2c + 1 (the two a lane of the E-step kernel owns side by side).  The general estimator of ipe.cuh
-// draws from other tags, so a pair it serves stays independent of its neighbour.
-static constexpr uint32_t IPE_TAG_PAIR = 0x1bE1u;
-__host__ __device__ inline void ipe_pair_uniforms(uint64_t seed, uint64_t rowkey, uint32_t col_even, double& v_even, double& v_odd) {
-    Philox rng(seed, rowkey, IPE_TAG_PAIR, col_even >> 1);
-    rng.uniform2(v_even, v_odd);
+// The inversion's uniform V of the pair (row, col), in two parts: V = (H + L) / 65536.  H, 16 bits, comes from the block
+// (seed, row, IPE_TAG_OCT, col / 8) that serves the eight columns 8c .. 8c + 7 of a row (32 bits per column pair); L, a
+// uniform in (0, 1), from the pair's own stream (seed, row, IPE_TAG_LOW, col).  V is uniform in (0, 1) and V >= H / 65536,
+// which is all the certificate below needs to know of it - so the E-step draws one block per eight pairs, and the
+// second one only for the pairs it samples.  The general estimator of ipe.cuh draws from other tags.
+static constexpr uint32_t IPE_TAG_OCT = 0x1bE1u, IPE_TAG_LOW = 0x1bE2u;
+__host__ __device__ inline void ipe_oct_bits(uint64_t seed, uint64_t rowkey, uint32_t col, uint32_t out[4]) {
+    Philox rng(seed, rowkey, IPE_TAG_OCT, col >> 3);
+    rng.block(out);
+}
+__host__ __device__ inline uint32_t ipe_oct_high(const uint32_t bits[4], uint32_t col) {
+    return (bits[(col & 7u) >> 1] >> ((col & 1u) * 16u)) & 0xffffu;
 }
 __host__ __device__ inline double ipe_pair_uniform(uint64_t seed, uint64_t rowkey, uint32_t col) {
-    double ve, vo;
-    ipe_pair_uniforms(seed, rowkey, col & ~1u, ve, vo);
-    return (col & 1u) ? vo : ve;
+    uint32_t bits[4];
+    ipe_oct_bits(seed, rowkey, col, bits);
+    Philox rng(seed, rowkey, IPE_TAG_LOW, col);
+    return ((double)ipe_oct_high(bits, col) + rng.uniform()) * (1.0 / 65536.0);
 }
 
 struct IpeGrid {

@@ -409,64 +409,81 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                 // list) for pass 2a.  With the replay hook everything goes to the general estimator (back of the list).
                 // (the dot product of the next round is fetched while this round's test is computed)
                 constexpr int LIST_CAP = BM * BN;
-                // (one unit = the columns 2c and 2c + 1 of a row: they share one block of the generator; the dot
-                // products of the next round are fetched while this round's test is computed)
-                const int hk = (kk + 1) >> 1, units = rows * hk;
+                // (one unit = the eight columns 8c .. 8c + 7 of a row: they share one block of the generator, whose 16
+                // bits per pair bound the pair's uniform from below - enough for the certificate; the dot products of
+                // the next round are fetched while this round's tests are computed)
+                static_assert(BN % 8 == 0, "units of eight columns");
+                const int hk = (kk + 7) >> 3, units = rows * hk;
                 const int urounds = (units + Cfg::THREADS - 1) / Cfg::THREADS;
-                int row = 0, c2 = 0;
+                int row = 0, c8 = 0;
                 bool ok = tid < units;
-                if (ok) { row = tid / hk; c2 = tid - row * hk; }
-                const int drow = Cfg::THREADS / hk, dc2 = Cfg::THREADS - drow * hk;     // one round further on
-                double2 dots = *reinterpret_cast<const double2*>(sc + row * BN + 2 * c2);
+                if (ok) { row = tid / hk; c8 = tid - row * hk; }
+                const int drow = Cfg::THREADS / hk, dc8 = Cfg::THREADS - drow * hk;     // one round further on
+                double2 dots[4];
+#pragma unroll
+                for (int h = 0; h < 4; ++h) dots[h] = *reinterpret_cast<const double2*>(sc + row * BN + 8 * c8 + 2 * h);
 #pragma unroll 1
                 for (int it = 0; it < urounds; ++it) {
                     const bool ok2 = (it + 1) * Cfg::THREADS + tid < units;
-                    int row2 = row + drow, c22 = c2 + dc2;
-                    if (c22 >= hk) { c22 -= hk; ++row2; }
-                    if (!ok2) { row2 = 0; c22 = 0; }
-                    const double2 dots2 = *reinterpret_cast<const double2*>(sc + row2 * BN + 2 * c22);
-                    const int cl = 2 * c2;
-                    const double xn = xn_s[row];
-                    const double dot[2] = {dots.x, dots.y};
-                    double lhs[2] = {0.0, 0.0}, rhs[2] = {0.0, 0.0};
-                    bool want[2] = {false, false}, poss[2] = {false, false};  // want: to be sampled in pass 2a
+                    int row2 = row + drow, c82 = c8 + dc8;
+                    if (c82 >= hk) { c82 -= hk; ++row2; }
+                    if (!ok2) { row2 = 0; c82 = 0; }
+                    double2 dots2[4];
 #pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        if (ok && cl + e < kk && !(prune && cl + e == cand_s[row])) {
+                    for (int h = 0; h < 4; ++h) dots2[h] = *reinterpret_cast<const double2*>(sc + row2 * BN + 8 * c82 + 2 * h);
+                    const int cl = 8 * c8;
+                    const double xn = xn_s[row];
+                    const double es = prune ? estar_s[row] : INFINITY;
+                    const int cand = prune ? cand_s[row] : -1;
+                    uint32_t hb[4] = {0u, 0u, 0u, 0u};
+                    if (prune && ok) ipe_oct_bits(a.seed, a.offset + (unsigned long long)(r0 + row), (unsigned)(n0 + cl), hb);
+                    unsigned want = 0, keep = 0;                   // want: bit e = column cl + e is to be sampled in pass 2a
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) {
+                        const double dot = (e & 1) ? dots[e >> 1].y : dots[e >> 1].x;
+                        if (ok && cl + e < kk && cl + e != cand) {
                             const double cn = cn_s[n0 + cl + e];
                             if (!(xn + cn > 0.0)) {
                                 sc[row * BN + cl + e] = ipe_minus(0.0, xn);                // |x|^2 + |c|^2 = 0: the estimate is 0
-                                atomicOr(&keep_s[(row * BN + cl + e) >> 5], 1u << ((row * BN + cl + e) & 31));
+                                keep |= 1u << e;
                             } else if (a.ipe_force_replay) {
                                 list[LIST_CAP - 1 - atomicAdd(ipe_cnt + 1, 1)] = row * BN + cl + e;
-                                atomicOr(&keep_s[(row * BN + cl + e) >> 5], 1u << ((row * BN + cl + e) & 31));
+                                keep |= 1u << e;
                             } else {
-                                want[e] = true;
-                                poss[e] = prune && ipe_out_possible(dot[e], xn, cn, eps, estar_s[row], lhs[e], rhs[e]);
+                                double lhs, rhs;
+                                const bool out = prune && ipe_out_possible(dot, xn, cn, eps, es, lhs, rhs) &&
+                                                 (double)ipe_oct_high(hb, (unsigned)e) * (1.0 / 65536.0) * lhs > rhs;
+                                if (!out) want |= 1u << e;
                             }
                         }
                     }
-                    if (poss[0] || poss[1]) {
-                        double V[2];
-                        ipe_pair_uniforms(a.seed, a.offset + (unsigned long long)(r0 + row), (unsigned)(n0 + cl), V[0], V[1]);
+                    // the listed pairs: one counter bump per warp, one bit-mask update per unit
+                    {
+                        const int mine = __popc(want);
+                        int incl = mine;
 #pragma unroll
-                        for (int e = 0; e < 2; ++e)
-                            if (poss[e] && V[e] * lhs[e] > rhs[e]) want[e] = false;          // out: its bit stays clear
-                    }
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const unsigned wm_ = __ballot_sync(0xffffffffu, want[e]);
-                        if (wm_) {
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const int y = __shfl_up_sync(0xffffffffu, incl, o);
+                            if (lane >= o) incl += y;
+                        }
+                        const int total = __shfl_sync(0xffffffffu, incl, 31);
+                        if (total) {
                             int base = 0;
-                            if (lane == __ffs(wm_) - 1) base = atomicAdd(ipe_cnt, __popc(wm_));
-                            base = __shfl_sync(0xffffffffu, base, __ffs(wm_) - 1);
-                            if (want[e]) {
-                                list[base + __popc(wm_ & ((1u << lane) - 1u))] = row * BN + cl + e;
-                                atomicOr(&keep_s[(row * BN + cl + e) >> 5], 1u << ((row * BN + cl + e) & 31));
+                            if (lane == 31) base = atomicAdd(ipe_cnt, total);
+                            base = __shfl_sync(0xffffffffu, base, 31) + incl - mine;
+                            unsigned w = want;
+                            while (w) {
+                                const int e = __ffs(w) - 1;
+                                w &= w - 1;
+                                list[base++] = row * BN + cl + e;
                             }
                         }
+                        keep |= want;
+                        if (keep) atomicOr(&keep_s[(row * BN + cl) >> 5], keep << ((row * BN + cl) & 31));
                     }
-                    row = row2; c2 = c22; ok = ok2; dots = dots2;
+                    row = row2; c8 = c82; ok = ok2;
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) dots[h] = dots2[h];
                 }
                 __syncthreads();
                 const int nres = ipe_cnt[0];
