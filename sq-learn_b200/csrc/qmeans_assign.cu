@@ -532,7 +532,7 @@ __global__ void __launch_bounds__(Cfg::THREADS, Cfg::MIN_CTAS) qmeans_assign_ker
                                                               (unsigned)(n0 + cld), a.ipe_force_replay != 0, defer);
                     if (okd) sc[pos] = ipe_minus(v, xn);
                 }
-                __syncthreads();
+                if (ngen > 0) __syncthreads();                     // (the same for every thread; usually there is nothing to wait for)
 #pragma unroll
                 for (int i = 0; i < MI; ++i) {
                     const int row = wm * Cfg::WM + i * 8 + lq;
