@@ -345,6 +345,7 @@ PRUNE_CASES = [  # n, d, k, delta, how X and C are made
     (5000, 16, 40, 0.5, "blobs"), (3000, 128, 256, 0.5, "blobs"), (2000, 8, 300, 0.3, "rand"),
     (4000, 32, 17, 1.0, "unit"), (1000, 64, 600, 0.2, "blobs"), (3000, 5, 3, 2.0, "rand"),
     (2000, 128, 256, 0.5, "datacentres"), (777, 3, 1, 0.5, "rand"), (1500, 20, 33, 0.05, "unit"),
+    (1200, 16, 24, 0.5, "zeros"), (1500, 24, 40, 0.5, "huge"), (1500, 24, 40, 1e-4, "tiny"), (900, 12, 20, 0.5, "opposite"),
 ]
 
 
@@ -367,6 +368,20 @@ def test_ipe_pairs_left_out_change_nothing(cuda, case):
         X, C = rng.normal(size=(n, d)), rng.normal(size=(k, d))
     elif kind == "unit":
         C = cen / np.linalg.norm(cen, axis=1, keepdims=True)
+    elif kind == "zeros":                 # null rows, a null centroid, duplicated centroids
+        C = cen.copy()
+        X[::7] = 0.0
+        C[3] = 0.0
+        C[5] = C[4]
+    elif kind == "huge":                  # norms of 1e6 and of 1e-6 side by side
+        C = cen * 1e6
+        X = X * 1e6
+        X[::5] *= 1e-12
+    elif kind == "tiny":
+        C = cen * 1e-3
+        X = X * 1e-3
+    elif kind == "opposite":              # nearly opposite vectors: the general estimator's pairs
+        C = np.concatenate([-X[:k // 2] * (1.0 + 1e-9 * rng.normal(size=(k // 2, 1))), cen[:k - k // 2]])
     else:
         C = X[:k].copy()
     out = []
@@ -380,3 +395,4 @@ def test_ipe_pairs_left_out_change_nothing(cuda, case):
     np.testing.assert_array_equal(out[0][0], out[1][0])
     np.testing.assert_array_equal(out[0][1], out[1][1])
     assert out[0][2] == out[1][2]
+    assert np.isfinite(out[0][1]).all() and (out[0][0] >= 0).all() and (out[0][0] < k).all()
