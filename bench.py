@@ -278,7 +278,20 @@ def run_b200(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"      # keep stdout to the one JSON line
-        dist.init_process_group("nccl", device_id=device)
+        # NCCL prints its version banner on stdout when the communicator comes up: send stdout to stderr until
+        # then, so that the JSON line is the only thing the caller reads there
+        sys.stdout.flush()
+        saved_fd = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=device)
+            warm = torch.zeros(1, device=device)
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_fd, 1)
+            os.close(saved_fd)
     assert world == args.gpus or world == 1, "launch with torchrun --nproc-per-node == --gpus"
     c = Ctx()
     c.torch, c.dist, c.Q, c.cabi, c.D, c.world, c.rank, c.device, c.args = torch, dist, Q, _cabi, D, world, rank, device, args
