@@ -148,6 +148,12 @@ int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, c
  * also the ones the kernel normally leaves out because their estimate certainly exceeds one already sampled in
  * the same row - labels, distances and inertia must come out bit for bit as with on = 0.  on = 0: normal.      */
 int sq_ipe_debug_force_replay(int on);
+/* Test hook (no reference counterpart).  on = 0: modes 0 and 1 of later sq_qmeans_assign calls run the fp64
+ * tensor-core kernel for every shape; on = 1 (the default): shapes with k <= 256, d <= 128, d a multiple of 16 and
+ * 16-byte aligned X / C first narrow each row down to a few columns on the bf16 tensor cores, with a rigorous error
+ * bound, and take every decision on fp64 distances of those columns (csrc/qmeans_filter.cuh).  Same labels; the
+ * distances agree to the rounding of two fp64 summation orders.  Process-wide, not thread-safe.                  */
+int sq_qmeans_debug_filter(int on);
 /* Test hook: B draws of the amplitude-estimation outcome j conditioned on lying outside the 8-point window
  * around the grid position x (offsets -3..4 from floor(x)), as the tail sampler of csrc/ipe.cuh makes them.   */
 int sq_ipe_debug_tail_sample(double M, double x, long long B, unsigned long long seed, double* out_j, void* stream);

@@ -58,6 +58,7 @@ struct AssignArgs {
     size_t ipe_scratch_bytes;   // (host) capacity of ipe_scratch: bounds the grid
     int ipe_force_replay;       // test hook: every pair takes the draw-by-draw replay path of ipe.cuh
     int ipe_prune;              // 1: pairs that certainly lose the row's arg-min are not sampled (same results)
+    int fix_mindist;            // 1: the window fix-up also writes the row's distance (rows the bf16 filter gave up on)
     double* store;         // [n, k] MODE_STORE: x_i.c_j - cnorm[j]
     unsigned long long* colkey;  // [k] MODE_COLABS: max over rows of (bits(|y|) with the sign of y in bit 0)
     long long n;
@@ -830,7 +831,10 @@ __global__ void qmeans_window_fixup_kernel(AssignArgs a) {
                 seen += c;
             }
         }
-        if (lane == 0) a.labels[gr] = label;
+        if (lane == 0) {
+            a.labels[gr] = label;
+            if (a.fix_mindist) a.mindist[gr] = fmax(a.xnorm[gr] + base, 0.0);
+        }
     }
 }
 
@@ -885,6 +889,10 @@ __global__ void sum_final_kernel(const double* __restrict__ part, int np, double
     }
 }
 
+}  // namespace sq
+#include "qmeans_filter.cuh"
+namespace sq {
+
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
@@ -924,6 +932,7 @@ static size_t assign_smem_bytes() {
 // recorded on the launching stream around the kernel when profiling is on
 static int g_ipe_force_replay = 0;
 static int g_ipe_prune = 1;
+static int g_filter_on = 1;           // exact / window E-step through the bf16 filter (qmeans_filter.cuh) when the shape allows
 static bool g_prof_on = false;
 static cudaEvent_t g_prof_ev[2] = {nullptr, nullptr};
 static double g_prof_ms = 0.0;
@@ -1104,8 +1113,41 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
         if (rc) return rc;
         a.rowmin_in = w.rowmin;
     }
-    rc = dispatch_assign(a, stream, &bn);
-    if (rc) return rc;
+    a.fix_mindist = 0;
+    // exact and delta-window modes, all centroids in one tile: filter on the bf16 tensor cores, decide in fp64
+    // (qmeans_filter.cuh); otherwise the fp64 tensor-core kernel
+    const bool filter = g_filter_on && mode != MODE_IPE && k <= FilterCfg::BN && d <= FilterCfg::DMAX && d % 16 == 0 &&
+                        ((uintptr_t)X & 15) == 0 && ((uintptr_t)C & 15) == 0;
+    if (filter) {
+        a.fix_mindist = 1;
+        const size_t smem = filter_smem_bytes(d);
+        long long tiles = (n + FilterCfg::BM - 1) / FilterCfg::BM;
+        int grid = device_sm_count();
+        if (grid > tiles) grid = (int)tiles;
+        if (g_prof_on) {
+            if (!g_prof_ev[0]) { SQ_CUDA(cudaEventCreate(&g_prof_ev[0])); SQ_CUDA(cudaEventCreate(&g_prof_ev[1])); }
+            SQ_CUDA(cudaEventRecord(g_prof_ev[0], stream));
+        }
+        if (mode == MODE_EXACT) {
+            SQ_CUDA(cudaFuncSetAttribute(qmeans_filter_kernel<MODE_EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            qmeans_filter_kernel<MODE_EXACT><<<grid, FilterCfg::THREADS, smem, stream>>>(a);
+        } else {
+            SQ_CUDA(cudaFuncSetAttribute(qmeans_filter_kernel<MODE_WINDOW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            qmeans_filter_kernel<MODE_WINDOW><<<grid, FilterCfg::THREADS, smem, stream>>>(a);
+        }
+        SQ_LAUNCH_CHECK("qmeans_filter_kernel");
+        if (g_prof_on) {
+            cudaEventRecord(g_prof_ev[1], stream);
+            cudaEventSynchronize(g_prof_ev[1]);
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, g_prof_ev[0], g_prof_ev[1]);
+            g_prof_ms += ms;
+            ++g_prof_launches;
+        }
+    } else {
+        rc = dispatch_assign(a, stream, &bn);
+        if (rc) return rc;
+    }
     if (mode == MODE_EXACT) {
         int fb = device_sm_count() * 4;
         qmeans_fixup_kernel<<<fb, 256, 0, stream>>>(a);
@@ -1140,6 +1182,11 @@ extern "C" int sq_ipe_debug_tail_sample(double M, double x, long long B, unsigne
     if (B == 0) return SQ_OK;
     ipe_tail_test_kernel<<<(unsigned)((B + 127) / 128), 128, 0, stream>>>(M, x, B, seed, out_j);
     SQ_LAUNCH_CHECK("ipe_tail_test_kernel");
+    return SQ_OK;
+}
+
+extern "C" int sq_qmeans_debug_filter(int on) {
+    g_filter_on = on ? 1 : 0;
     return SQ_OK;
 }
 

@@ -1,0 +1,352 @@
+// K2f - the E-step of the exact and delta-window modes as "filter in bf16, decide in fp64".
+//
+// Only the row's arg-min, its value and the columns within delta of it leave the E-step (labels_estimation,
+// sklearn/cluster/_dmeans.py:732-777).  So the n x k distance matrix is first computed APPROXIMATELY on the bf16
+// tensor cores (mma.sync.m16n8k16, fp32 accumulation) with a rigorous error bound, which tells, per row, which few
+// columns can be the minimum or lie in the window; for exactly those columns the distance is then computed in fp64
+// from the fp64 tile still sitting in shared memory, and every decision (arg-min, window, near-tie flag, uniform
+// pick) is taken on the fp64 values by the same rules as qmeans_assign_kernel's epilogue.  Nothing approximate
+// reaches an output: labels, distances and inertia are fp64 results, and rows the filter cannot narrow down (more
+// than CAP columns inside the bound, or non-finite numbers) go to the exact fix-up kernels that already exist.
+//
+// Error bound.  bf16 has 8 significant bits: |bf16(u) - u| <= 2^-8 |u| (through fp32: + 2^-24), so
+// |x~.c~ - x.c| <= (2 * 2^-8 + 2^-16 + d 2^-24 (fp32 accumulation)) |x||c| < 0.0079 |x||c|  (d <= 128).
+// With v = |c|^2 - 2 x.c and E = 0.0158 |x| max_j|c_j| (+ the fp32 rounding of |c|^2): |v~ - v| <= E, hence every
+// column with v <= min v + delta has v~ <= min v~ + delta + 2E.  Columns passing that test are the candidates.
+//
+// The kernel is HBM-bound by design: X is read once in fp64 (8 n d bytes) by bulk copies (cp.async.bulk, one per
+// tile: the rows of a tile are contiguous) into a two-deep ring; the centroids stay in shared memory as bf16 for the
+// whole launch.  One CTA of 256 threads per SM, 64 rows per tile, all k <= 256 columns at once.
+#pragma once
+#include <cuda_bf16.h>
+
+namespace sq {
+
+struct FilterCfg {
+    static constexpr int BM = 64, BN = 256, THREADS = 256, WARPS = 8, CAP = 8, DMAX = 128;
+};
+
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (unsigned)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"((unsigned)__cvta_generic_to_shared(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4(unsigned& r0, unsigned& r1, unsigned& r2, unsigned& r3, const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+                 : "r"((unsigned)__cvta_generic_to_shared(p)));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], unsigned a0, unsigned a1, unsigned a2, unsigned a3, unsigned b0,
+                                         unsigned b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+// dynamic shared memory of the kernel for feature count d (a multiple of 16, <= 128)
+__host__ __device__ inline size_t filter_smem_bytes(int d) {
+    const size_t cp = (size_t)d + 8;                               // bf16 row pitch: rows 16 bytes apart modulo 128
+    return 2 * (size_t)FilterCfg::BM * d * 8                       // xs: two fp64 tiles
+           + (size_t)FilterCfg::BN * cp * 2                        // cb: centroids, bf16
+           + (size_t)FilterCfg::BM * cp * 2                        // xb: the tile, bf16
+           + (size_t)FilterCfg::BN * 8                             // cn_s
+           + (size_t)FilterCfg::BN * 4                             // cnf_s
+           + (size_t)FilterCfg::BM * FilterCfg::WARPS * 4          // wmin
+           + (size_t)FilterCfg::BM * 4 * 3                         // thr_s, slack_s, ccnt
+           + (size_t)FilterCfg::BM * FilterCfg::CAP * 4            // ccol
+           + (size_t)FilterCfg::BM * FilterCfg::CAP * 8            // cval
+           + 8                                                     // cmax
+           + 64;                                                   // two mbarriers, padding
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(AssignArgs a) {
+    constexpr int BM = FilterCfg::BM, BN = FilterCfg::BN, CAP = FilterCfg::CAP, WARPS = FilterCfg::WARPS;
+    extern __shared__ __align__(1024) unsigned char fsm[];
+    const int d = a.d, cp = d + 8;
+    double* xs = reinterpret_cast<double*>(fsm);                                       // [2][BM*d]
+    __nv_bfloat16* cb = reinterpret_cast<__nv_bfloat16*>(xs + 2 * BM * d);             // [BN][cp]
+    __nv_bfloat16* xb = cb + (size_t)BN * cp;                                          // [BM][cp]
+    double* cn_s = reinterpret_cast<double*>(xb + (size_t)BM * cp);                    // [BN]
+    float* cnf_s = reinterpret_cast<float*>(cn_s + BN);                                // [BN] |c|^2 in fp32 (+inf past k)
+    float* wmin = cnf_s + BN;                                                          // [BM][WARPS]
+    float* thr_s = wmin + BM * WARPS;                                                  // [BM]
+    float* slack_s = thr_s + BM;                                                       // [BM]
+    int* ccnt = reinterpret_cast<int*>(slack_s + BM);                                  // [BM]
+    int* ccol = ccnt + BM;                                                             // [BM][CAP]
+    double* cval = reinterpret_cast<double*>(((uintptr_t)(ccol + BM * CAP) + 7) & ~(uintptr_t)7);     // [BM][CAP] fp64 v of the candidates
+    double* cmax_s = cval + BM * CAP;                                                  // [1] max_j |c_j|
+    unsigned long long* bar = reinterpret_cast<unsigned long long*>(cmax_s + 1);       // [2]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, t4 = lane & 3;
+    const long long num_tiles = (a.n + BM - 1) / BM;
+    const unsigned tile_bytes = (unsigned)(BM * d * 8);
+
+    if (tid == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    // centroids: fp64 -> bf16 (zero rows past k), norms in fp64 and fp32
+    for (int idx = tid; idx < BN * (d / 2); idx += FilterCfg::THREADS) {
+        const int j = idx / (d / 2), c2 = idx - j * (d / 2);
+        double2 v = make_double2(0.0, 0.0);
+        if (j < a.k) v = *reinterpret_cast<const double2*>(a.C + (long long)j * d + 2 * c2);
+        *reinterpret_cast<__nv_bfloat162*>(cb + (size_t)j * cp + 2 * c2) = __floats2bfloat162_rn((float)v.x, (float)v.y);
+    }
+    for (int j = tid; j < BN; j += FilterCfg::THREADS) {
+        const double cn = (j < a.k) ? a.cnorm[j] : INFINITY;
+        cn_s[j] = cn;
+        cnf_s[j] = (float)cn;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        double m = 0.0;
+        for (int j = lane; j < a.k; j += 32) m = fmax(m, cn_s[j]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (lane == 0) *cmax_s = sqrt(m);
+    }
+    __syncthreads();
+    const double cmax = *cmax_s;
+
+    auto issue = [&](long long tile, int stage) {
+        // one thread: the whole tile is one contiguous block of X (rows of d doubles, no padding)
+        const long long r0 = tile * BM;
+        const long long rows = (a.n - r0 < BM) ? (a.n - r0) : BM;
+        const unsigned bytes = (unsigned)(rows * d * 8);
+        mbar_expect_tx(&bar[stage], bytes);
+        bulk_load(xs + (size_t)stage * BM * d, a.X + r0 * d, bytes, &bar[stage]);
+    };
+    (void)tile_bytes;
+
+    long long tile = blockIdx.x;
+    if (tid == 0 && tile < num_tiles) issue(tile, 0);
+    unsigned phases = 0u;                                  // bit s: parity to wait for on bar[s]
+    int stage = 0;
+    // relative error of a bf16 product sum (see the header) and of |c|^2 rounded to fp32
+    const float EREL = 0.0158f;
+
+    for (; tile < num_tiles; tile += gridDim.x, stage ^= 1) {
+        const long long r0 = tile * BM;
+        const int rows = (int)((a.n - r0 < BM) ? (a.n - r0) : BM);
+        // the next tile of this CTA goes into the other buffer (its previous readers finished before the barrier that
+        // ended the previous iteration)
+        if (tid == 0 && tile + gridDim.x < num_tiles) issue(tile + gridDim.x, stage ^ 1);
+        mbar_wait(&bar[stage], (phases >> stage) & 1u);
+        phases ^= 1u << stage;
+        const double* xt = xs + (size_t)stage * BM * d;
+
+        // ---- fp64 tile -> bf16 tile; per-row slack of the filter ----
+        for (int idx = tid; idx < BM * (d / 2); idx += FilterCfg::THREADS) {
+            const int r = idx / (d / 2), c2 = idx - r * (d / 2);
+            double2 v = *reinterpret_cast<const double2*>(xt + (size_t)r * d + 2 * c2);
+            if (r >= rows) v = make_double2(0.0, 0.0);
+            *reinterpret_cast<__nv_bfloat162*>(xb + (size_t)r * cp + 2 * c2) = __floats2bfloat162_rn((float)v.x, (float)v.y);
+        }
+        if (tid < BM) {
+            const double xn = (tid < rows) ? a.xnorm[r0 + tid] : 0.0;
+            // E = 0.0158 |x| max|c| bounds |v~ - v|, plus the rounding of |c|^2 to fp32 and of the fp32 arithmetic on v~
+            const double E = (double)EREL * sqrt(xn) * cmax + 2.4e-7 * (cmax * cmax + 2.0 * sqrt(xn) * cmax) + 1e-30;
+            slack_s[tid] = __double2float_ru(2.0 * E);
+            ccnt[tid] = 0;
+        }
+        __syncthreads();
+
+        // ---- approximate x.c on the tensor cores: warp w owns columns [32 w, 32 w + 32) of all 64 rows ----
+        float acc[4][4][4];
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                for (int r = 0; r < 4; ++r) acc[mi][ni][r] = 0.0f;
+        const int a_row = (lane & 7) + 8 * ((lane >> 3) & 1), a_k = 8 * (lane >> 4);
+        const int b_row = (lane & 7) + 8 * (lane >> 4), b_k = 8 * ((lane >> 3) & 1);
+        for (int k0 = 0; k0 < d; k0 += 16) {
+            unsigned af[4][4], bf[2][4];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi)
+                ldmatrix_x4(af[mi][0], af[mi][1], af[mi][2], af[mi][3], xb + (size_t)(mi * 16 + a_row) * cp + k0 + a_k);
+#pragma unroll
+            for (int np = 0; np < 2; ++np)
+                ldmatrix_x4(bf[np][0], bf[np][1], bf[np][2], bf[np][3],
+                            cb + (size_t)(warp * 32 + np * 16 + b_row) * cp + k0 + b_k);
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni)
+                    mma_bf16(acc[mi][ni], af[mi][0], af[mi][1], af[mi][2], af[mi][3], bf[ni >> 1][(ni & 1) * 2],
+                             bf[ni >> 1][(ni & 1) * 2 + 1]);
+        }
+        // ---- v~ = |c|^2 - 2 x~.c~ in place; per-warp row minima ----
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) {
+            const int col = warp * 32 + ni * 8 + 2 * t4;
+            const float c0 = cnf_s[col], c1 = cnf_s[col + 1];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi) {
+                acc[mi][ni][0] = fmaf(-2.0f, acc[mi][ni][0], c0);
+                acc[mi][ni][1] = fmaf(-2.0f, acc[mi][ni][1], c1);
+                acc[mi][ni][2] = fmaf(-2.0f, acc[mi][ni][2], c0);
+                acc[mi][ni][3] = fmaf(-2.0f, acc[mi][ni][3], c1);
+            }
+        }
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float m = INFINITY;
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) m = fminf(m, fminf(acc[mi][ni][2 * h], acc[mi][ni][2 * h + 1]));
+                m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 1));
+                m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 2));
+                if (t4 == 0) wmin[(mi * 16 + h * 8 + g) * WARPS + warp] = m;
+            }
+        __syncthreads();
+        if (tid < BM) {
+            float m = wmin[tid * WARPS];
+#pragma unroll
+            for (int w = 1; w < WARPS; ++w) m = fminf(m, wmin[tid * WARPS + w]);
+            // every column with v <= min v + delta has v~ <= min v~ + delta + 2E; NaN (non-finite input) fails the test
+            // below for every column of the row, which sends the row to the exact fix-up
+            thr_s[tid] = (m + (MODE == MODE_WINDOW ? __double2float_ru(a.delta) : 0.0f) + slack_s[tid]) * (1.0f + 1e-6f) +
+                         1e-30f;
+            if (!(m < INFINITY)) ccnt[tid] = CAP + 1;               // nothing finite in the row
+        }
+        __syncthreads();
+        // ---- candidates ----
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int row = mi * 16 + h * 8 + g;
+                const float thr = thr_s[row];
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float v = acc[mi][ni][2 * h + e];
+                        const int col = warp * 32 + ni * 8 + 2 * t4 + e;
+                        if (row < rows && col < a.k && !(v > thr)) {
+                            const int slot = atomicAdd(&ccnt[row], 1);
+                            if (slot < CAP) ccol[row * CAP + slot] = col;
+                        }
+                    }
+            }
+        __syncthreads();
+        // ---- fp64 for the candidates: a warp owns the rows warp, warp + 8, ...; its candidates, flattened, are dealt to
+        // its four groups of eight lanes, so that four fp64 dot products (their centroid rows come from L2) are in
+        // flight at a time.  The summation order of a dot product depends on (d) alone. ----
+        {
+            constexpr int RPW = BM / WARPS;                    // rows per warp
+            const int grp = lane >> 3, sub = lane & 7;
+            int pre[RPW + 1];
+            pre[0] = 0;
+#pragma unroll
+            for (int j = 0; j < RPW; ++j) {
+                const int row = warp + WARPS * j;
+                const int nc = (row < rows) ? ccnt[row] : 0;
+                pre[j + 1] = pre[j] + ((nc >= 1 && nc <= CAP) ? nc : 0);
+            }
+            const int total = pre[RPW];
+            for (int cbase = 0; cbase < total; cbase += 4) {       // (the same trip count for every lane: full-mask shuffles below)
+                const bool live = cbase + grp < total;
+                const int c = live ? cbase + grp : 0;
+                int j = 0;
+#pragma unroll
+                for (int q = 1; q < RPW; ++q) j += (c >= pre[q]) ? 1 : 0;
+                int base = 0;
+#pragma unroll
+                for (int q = 0; q < RPW; ++q) base = (q == j) ? pre[q] : base;
+                const int row = warp + WARPS * j, slot = c - base;
+                const int col = ccol[row * CAP + slot];
+                const double* xr = xt + (size_t)row * d;
+                const double* cr = a.C + (long long)col * d;
+                double p0 = 0.0, p1 = 0.0;
+                for (int f = 2 * sub; f < d; f += 16) {
+                    const double2 xv = *reinterpret_cast<const double2*>(xr + f);
+                    const double2 cv = __ldg(reinterpret_cast<const double2*>(cr + f));
+                    p0 = fma(xv.x, cv.x, p0);
+                    p1 = fma(xv.y, cv.y, p1);
+                }
+                double p = p0 + p1;
+                p += __shfl_xor_sync(0xffffffffu, p, 4);
+                p += __shfl_xor_sync(0xffffffffu, p, 2);
+                p += __shfl_xor_sync(0xffffffffu, p, 1);
+                if (live && sub == 0) cval[row * CAP + slot] = fma(-2.0, p, cn_s[col]);
+            }
+            __syncwarp();
+            // ---- the decision, one lane per row ----
+            if (lane < RPW && warp + WARPS * lane < rows) {
+                const int row = warp + WARPS * lane;
+                const long long gr = r0 + row;
+                const int nc = ccnt[row];
+                const double xn = a.xnorm[gr];
+                if (nc > CAP || nc < 1) {
+                    // too many columns inside the bound (or non-finite numbers): the exact fix-up kernels redo the row
+                    const int slot = atomicAdd(a.flag_count, 1);
+                    a.flag_rows[slot] = (int)gr;
+                    a.labels[gr] = 0;
+                    a.mindist[gr] = 0.0;
+                } else {
+                    double tmin = INFINITY;
+                    int amin = 0x7fffffff;
+                    for (int s2 = 0; s2 < nc; ++s2) {
+                        const double v = cval[row * CAP + s2];
+                        const int cc = ccol[row * CAP + s2];
+                        if (v < tmin || (v == tmin && cc < amin)) { tmin = v; amin = cc; }
+                    }
+                    if (!(tmin < INFINITY)) {                  // NaN / inf in fp64 too
+                        const int slot = atomicAdd(a.flag_count, 1);
+                        a.flag_rows[slot] = (int)gr;
+                        a.labels[gr] = 0;
+                        a.mindist[gr] = 0.0;
+                    } else if (MODE == MODE_WINDOW) {
+                        const double thr = tmin + a.delta;
+                        int c = 0, c0 = 0x7fffffff, c1 = 0x7fffffff, c2 = 0x7fffffff, c3 = 0x7fffffff;
+                        for (int s2 = 0; s2 < nc; ++s2)
+                            if (cval[row * CAP + s2] <= thr) {
+                                // keep the four lowest columns, sorted
+                                int x = ccol[row * CAP + s2], t;
+                                if (x < c0) { t = c0; c0 = x; x = t; }
+                                if (x < c1) { t = c1; c1 = x; x = t; }
+                                if (x < c2) { t = c2; c2 = x; x = t; }
+                                if (x < c3) { c3 = x; }
+                                ++c;
+                            }
+                        int label = c0;
+                        if (c > 4) {
+                            const int slot = atomicAdd(a.flag_count, 1);
+                            a.flag_rows[slot] = (int)gr;          // redone by qmeans_window_fixup_kernel
+                        } else if (c > 1) {
+                            // uniform pick among the candidates (reference: random.choice, _dmeans.py:2252-2257)
+                            Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, 0u);
+                            int r = (int)(rng.uniform() * c);
+                            if (r >= c) r = c - 1;
+                            label = r == 0 ? c0 : r == 1 ? c1 : r == 2 ? c2 : c3;
+                        }
+                        a.labels[gr] = label;
+                        a.mindist[gr] = fmax(xn + tmin, 0.0);
+                    } else {
+                        const double thr = tmin + fmax(a.tie_tol, 0.0) * (xn + 2.0 * fabs(tmin));
+                        int rc = 0;
+                        for (int s2 = 0; s2 < nc; ++s2) rc += (cval[row * CAP + s2] <= thr) ? 1 : 0;
+                        a.labels[gr] = amin;
+                        a.mindist[gr] = fmax(xn + tmin, 0.0);
+                        if (rc > 1 && a.tie_tol >= 0.0) {
+                            const int slot = atomicAdd(a.flag_count, 1);
+                            a.flag_rows[slot] = (int)gr;          // redone by qmeans_fixup_kernel in the reference's arithmetic
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();   // xs[stage], xb, ccnt, ccol free for the next tiles
+    }
+}
+
+}  // namespace sq

@@ -38,6 +38,7 @@ SIGNATURES = {
                                                  c_ull, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "sq_tomography_tune": (c_int, [c_int, c_double]),
     "sq_ipe_debug_force_replay": (c_int, [c_int]),
+    "sq_qmeans_debug_filter": (c_int, [c_int]),
     "sq_ipe_debug_tail_sample": (c_int, [c_double, c_double, c_ll, c_ull, c_void_p, c_void_p]),
     "sq_qmeans_assign_workspace_bytes": (c_size_t, [c_ll, c_int, c_int]),
     "sq_qmeans_assign": (c_int, [c_void_p, c_void_p, c_ll, c_int, c_void_p, c_int, c_int, c_double, c_ull, c_ull,
