@@ -16,14 +16,17 @@
 //
 // The kernel is HBM-bound by design: X is read once in fp64 (8 n d bytes) by bulk copies (cp.async.bulk, one per
 // tile: the rows of a tile are contiguous) into a two-deep ring; the centroids stay in shared memory as bf16 for the
-// whole launch.  One CTA of 256 threads per SM, 64 rows per tile, all k <= 256 columns at once.
+// whole launch.  One CTA of 512 threads per SM, 64 rows per tile, all k <= 256 columns at once.
 #pragma once
 #include <cuda_bf16.h>
 
 namespace sq {
 
 struct FilterCfg {
-    static constexpr int BM = 64, BN = 256, THREADS = 256, WARPS = 8, CAP = 8, DMAX = 128;
+    // two teams of eight warps per CTA, each working on its own 32-row tiles (own ring, own barriers), sharing the
+    // bf16 centroids: what two CTAs per SM would be if the centroids did not have to be there twice
+    static constexpr int TEAMS = 2, TWARPS = 8, TTHREADS = 256, THREADS = TEAMS * TTHREADS;
+    static constexpr int BM = 32, BN = 256, CAP = 8, DMAX = 128;
 };
 
 __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, unsigned bytes, unsigned long long* bar) {
@@ -47,42 +50,52 @@ __device__ __forceinline__ void mma_bf16(float (&c)[4], unsigned a0, unsigned a1
 // dynamic shared memory of the kernel for feature count d (a multiple of 16, <= 128)
 __host__ __device__ inline size_t filter_smem_bytes(int d) {
     const size_t cp = (size_t)d + 8;                               // bf16 row pitch: rows 16 bytes apart modulo 128
-    return 2 * (size_t)FilterCfg::BM * d * 8                       // xs: two fp64 tiles
+    const size_t T = FilterCfg::TEAMS, BM = FilterCfg::BM;
+    return T * 2 * BM * d * 8                                      // xs: two fp64 tiles per team
            + (size_t)FilterCfg::BN * cp * 2                        // cb: centroids, bf16
-           + (size_t)FilterCfg::BM * cp * 2                        // xb: the tile, bf16
+           + T * BM * cp * 2                                       // xb: the teams' tiles, bf16
            + (size_t)FilterCfg::BN * 8                             // cn_s
-           + (size_t)FilterCfg::BN * 4                             // cnf_s
-           + (size_t)FilterCfg::BM * FilterCfg::WARPS * 4          // wmin
-           + (size_t)FilterCfg::BM * 4 * 3                         // thr_s, slack_s, ccnt
-           + (size_t)FilterCfg::BM * FilterCfg::CAP * 4            // ccol
-           + (size_t)FilterCfg::BM * FilterCfg::CAP * 8            // cval
+           + T * BM * FilterCfg::TWARPS * 4                        // wmin
+           + T * BM * 4 * 3                                        // thr_s, slack_s, ccnt
+           + T * BM * FilterCfg::CAP * 4                           // ccol
+           + T * BM * FilterCfg::CAP * 8                           // cval
            + 8                                                     // cmax
-           + 64;                                                   // two mbarriers, padding
+           + 8 * T * 2 + 64;                                       // mbarriers, padding
 }
 
 template <int MODE>
 __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(AssignArgs a) {
-    constexpr int BM = FilterCfg::BM, BN = FilterCfg::BN, CAP = FilterCfg::CAP, WARPS = FilterCfg::WARPS;
+    constexpr int BM = FilterCfg::BM, BN = FilterCfg::BN, CAP = FilterCfg::CAP, WARPS = FilterCfg::TWARPS;
+    constexpr int TEAMS = FilterCfg::TEAMS, TT = FilterCfg::TTHREADS;
     extern __shared__ __align__(1024) unsigned char fsm[];
     const int d = a.d, cp = d + 8;
-    double* xs = reinterpret_cast<double*>(fsm);                                       // [2][BM*d]
-    __nv_bfloat16* cb = reinterpret_cast<__nv_bfloat16*>(xs + 2 * BM * d);             // [BN][cp]
-    __nv_bfloat16* xb = cb + (size_t)BN * cp;                                          // [BM][cp]
-    double* cn_s = reinterpret_cast<double*>(xb + (size_t)BM * cp);                    // [BN]
-    float* cnf_s = reinterpret_cast<float*>(cn_s + BN);                                // [BN] |c|^2 in fp32 (+inf past k)
-    float* wmin = cnf_s + BN;                                                          // [BM][WARPS]
-    float* thr_s = wmin + BM * WARPS;                                                  // [BM]
-    float* slack_s = thr_s + BM;                                                       // [BM]
-    int* ccnt = reinterpret_cast<int*>(slack_s + BM);                                  // [BM]
-    int* ccol = ccnt + BM;                                                             // [BM][CAP]
-    double* cval = reinterpret_cast<double*>(((uintptr_t)(ccol + BM * CAP) + 7) & ~(uintptr_t)7);     // [BM][CAP] fp64 v of the candidates
-    double* cmax_s = cval + BM * CAP;                                                  // [1] max_j |c_j|
-    unsigned long long* bar = reinterpret_cast<unsigned long long*>(cmax_s + 1);       // [2]
+    const int team = threadIdx.x / TT, tid = threadIdx.x % TT, lane = tid & 31, warp = tid >> 5;
+    double* xs_all = reinterpret_cast<double*>(fsm);                                   // [TEAMS][2][BM*d]
+    __nv_bfloat16* cb = reinterpret_cast<__nv_bfloat16*>(xs_all + (size_t)TEAMS * 2 * BM * d);   // [BN][cp]
+    __nv_bfloat16* xb_all = cb + (size_t)BN * cp;                                      // [TEAMS][BM][cp]
+    double* cn_s = reinterpret_cast<double*>(xb_all + (size_t)TEAMS * BM * cp);        // [BN]
+    float* wmin_all = reinterpret_cast<float*>(cn_s + BN);                             // [TEAMS][BM][WARPS]
+    float* thr_all = wmin_all + TEAMS * BM * WARPS;                                    // [TEAMS][BM]
+    float* slack_all = thr_all + TEAMS * BM;                                           // [TEAMS][BM]
+    int* ccnt_all = reinterpret_cast<int*>(slack_all + TEAMS * BM);                    // [TEAMS][BM]
+    int* ccol_all = ccnt_all + TEAMS * BM;                                             // [TEAMS][BM][CAP]
+    double* cval_all = reinterpret_cast<double*>(((uintptr_t)(ccol_all + TEAMS * BM * CAP) + 7) & ~(uintptr_t)7);   // [TEAMS][BM][CAP]
+    double* cmax_s = cval_all + TEAMS * BM * CAP;                                      // [1] max_j |c_j|
+    unsigned long long* bar_all = reinterpret_cast<unsigned long long*>(cmax_s + 1);   // [TEAMS][2]
+    // this team's slices
+    double* xs = xs_all + (size_t)team * 2 * BM * d;
+    __nv_bfloat16* xb = xb_all + (size_t)team * BM * cp;
+    float* wmin = wmin_all + team * BM * WARPS;
+    float* thr_s = thr_all + team * BM;
+    float* slack_s = slack_all + team * BM;
+    int* ccnt = ccnt_all + team * BM;
+    int* ccol = ccol_all + team * BM * CAP;
+    double* cval = cval_all + team * BM * CAP;
+    unsigned long long* bar = bar_all + team * 2;
+    auto team_sync = [&]() { asm volatile("barrier.sync %0, %1;" ::"r"(1 + team), "r"(TT) : "memory"); };
 
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, t4 = lane & 3;
     const long long num_tiles = (a.n + BM - 1) / BM;
-    const unsigned tile_bytes = (unsigned)(BM * d * 8);
 
     if (tid == 0) {
         mbar_init(&bar[0], 1);
@@ -90,20 +103,22 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    // centroids: fp64 -> bf16 (zero rows past k), norms in fp64 and fp32
-    for (int idx = tid; idx < BN * (d / 2); idx += FilterCfg::THREADS) {
-        const int j = idx / (d / 2), c2 = idx - j * (d / 2);
-        double2 v = make_double2(0.0, 0.0);
-        if (j < a.k) v = *reinterpret_cast<const double2*>(a.C + (long long)j * d + 2 * c2);
-        *reinterpret_cast<__nv_bfloat162*>(cb + (size_t)j * cp + 2 * c2) = __floats2bfloat162_rn((float)v.x, (float)v.y);
-    }
-    for (int j = tid; j < BN; j += FilterCfg::THREADS) {
-        const double cn = (j < a.k) ? a.cnorm[j] : INFINITY;
-        cn_s[j] = cn;
-        cnf_s[j] = (float)cn;
+    // centroids: fp64 -> bf16 (zero rows past k), by the whole CTA
+    // (pairs of features; a thread walks (row, pair) = (t / h, t % h), then + stride, without dividing again)
+    const int h = d / 2;
+    {
+        const int t = threadIdx.x, sr = FilterCfg::THREADS / h, sc = FilterCfg::THREADS - sr * h;
+        for (int j = t / h, c2 = t % h; j < BN;) {
+            double2 v = make_double2(0.0, 0.0);
+            if (j < a.k) v = *reinterpret_cast<const double2*>(a.C + (long long)j * d + 2 * c2);
+            *reinterpret_cast<__nv_bfloat162*>(cb + (size_t)j * cp + 2 * c2) = __floats2bfloat162_rn((float)v.x, (float)v.y);
+            j += sr; c2 += sc;
+            if (c2 >= h) { c2 -= h; ++j; }
+        }
+        for (int j = t; j < BN; j += FilterCfg::THREADS) cn_s[j] = (j < a.k) ? a.cnorm[j] : INFINITY;
     }
     __syncthreads();
-    if (warp == 0) {
+    if (threadIdx.x < 32) {
         double m = 0.0;
         for (int j = lane; j < a.k; j += 32) m = fmax(m, cn_s[j]);
 #pragma unroll
@@ -112,6 +127,8 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
     }
     __syncthreads();
     const double cmax = *cmax_s;
+    const int step_r = TT / h, step_c = TT - step_r * h;
+    const int r_first = tid / h, c_first = tid - r_first * h;
 
     auto issue = [&](long long tile, int stage) {
         // one thread: the whole tile is one contiguous block of X (rows of d doubles, no padding)
@@ -121,31 +138,32 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         mbar_expect_tx(&bar[stage], bytes);
         bulk_load(xs + (size_t)stage * BM * d, a.X + r0 * d, bytes, &bar[stage]);
     };
-    (void)tile_bytes;
 
-    long long tile = blockIdx.x;
+    const long long tstride = (long long)gridDim.x * TEAMS;
+    long long tile = (long long)blockIdx.x * TEAMS + team;
     if (tid == 0 && tile < num_tiles) issue(tile, 0);
     unsigned phases = 0u;                                  // bit s: parity to wait for on bar[s]
     int stage = 0;
     // relative error of a bf16 product sum (see the header) and of |c|^2 rounded to fp32
     const float EREL = 0.0158f;
 
-    for (; tile < num_tiles; tile += gridDim.x, stage ^= 1) {
+    for (; tile < num_tiles; tile += tstride, stage ^= 1) {
         const long long r0 = tile * BM;
         const int rows = (int)((a.n - r0 < BM) ? (a.n - r0) : BM);
-        // the next tile of this CTA goes into the other buffer (its previous readers finished before the barrier that
-        // ended the previous iteration)
-        if (tid == 0 && tile + gridDim.x < num_tiles) issue(tile + gridDim.x, stage ^ 1);
+        // the team's next tile goes into its other buffer (whose readers finished before the barrier that ended the
+        // previous iteration)
+        if (tid == 0 && tile + tstride < num_tiles) issue(tile + tstride, stage ^ 1);
         mbar_wait(&bar[stage], (phases >> stage) & 1u);
         phases ^= 1u << stage;
         const double* xt = xs + (size_t)stage * BM * d;
 
         // ---- fp64 tile -> bf16 tile; per-row slack of the filter ----
-        for (int idx = tid; idx < BM * (d / 2); idx += FilterCfg::THREADS) {
-            const int r = idx / (d / 2), c2 = idx - r * (d / 2);
+        for (int r = r_first, c2 = c_first; r < BM;) {
             double2 v = *reinterpret_cast<const double2*>(xt + (size_t)r * d + 2 * c2);
             if (r >= rows) v = make_double2(0.0, 0.0);
             *reinterpret_cast<__nv_bfloat162*>(xb + (size_t)r * cp + 2 * c2) = __floats2bfloat162_rn((float)v.x, (float)v.y);
+            r += step_r; c2 += step_c;
+            if (c2 >= h) { c2 -= h; ++r; }
         }
         if (tid < BM) {
             const double xn = (tid < rows) ? a.xnorm[r0 + tid] : 0.0;
@@ -154,12 +172,12 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
             slack_s[tid] = __double2float_ru(2.0 * E);
             ccnt[tid] = 0;
         }
-        __syncthreads();
+        team_sync();
 
-        // ---- approximate x.c on the tensor cores: warp w owns columns [32 w, 32 w + 32) of all 64 rows ----
-        float acc[4][4][4];
+        // ---- approximate x.c on the tensor cores: warp w of the team owns columns [32 w, 32 w + 32) of the 32 rows ----
+        float acc[2][4][4];
 #pragma unroll
-        for (int mi = 0; mi < 4; ++mi)
+        for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
             for (int ni = 0; ni < 4; ++ni)
 #pragma unroll
@@ -167,16 +185,16 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         const int a_row = (lane & 7) + 8 * ((lane >> 3) & 1), a_k = 8 * (lane >> 4);
         const int b_row = (lane & 7) + 8 * (lane >> 4), b_k = 8 * ((lane >> 3) & 1);
         for (int k0 = 0; k0 < d; k0 += 16) {
-            unsigned af[4][4], bf[2][4];
+            unsigned af[2][4], bf[2][4];
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi)
+            for (int mi = 0; mi < 2; ++mi)
                 ldmatrix_x4(af[mi][0], af[mi][1], af[mi][2], af[mi][3], xb + (size_t)(mi * 16 + a_row) * cp + k0 + a_k);
 #pragma unroll
             for (int np = 0; np < 2; ++np)
                 ldmatrix_x4(bf[np][0], bf[np][1], bf[np][2], bf[np][3],
                             cb + (size_t)(warp * 32 + np * 16 + b_row) * cp + k0 + b_k);
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi)
+            for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
                 for (int ni = 0; ni < 4; ++ni)
                     mma_bf16(acc[mi][ni], af[mi][0], af[mi][1], af[mi][2], af[mi][3], bf[ni >> 1][(ni & 1) * 2],
@@ -186,9 +204,9 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) {
             const int col = warp * 32 + ni * 8 + 2 * t4;
-            const float c0 = cnf_s[col], c1 = cnf_s[col + 1];
+            const float c0 = (float)cn_s[col], c1 = (float)cn_s[col + 1];
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi) {
+            for (int mi = 0; mi < 2; ++mi) {
                 acc[mi][ni][0] = fmaf(-2.0f, acc[mi][ni][0], c0);
                 acc[mi][ni][1] = fmaf(-2.0f, acc[mi][ni][1], c1);
                 acc[mi][ni][2] = fmaf(-2.0f, acc[mi][ni][2], c0);
@@ -196,54 +214,51 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
             }
         }
 #pragma unroll
-        for (int mi = 0; mi < 4; ++mi)
+        for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int hh = 0; hh < 2; ++hh) {
                 float m = INFINITY;
 #pragma unroll
-                for (int ni = 0; ni < 4; ++ni) m = fminf(m, fminf(acc[mi][ni][2 * h], acc[mi][ni][2 * h + 1]));
+                for (int ni = 0; ni < 4; ++ni) m = fminf(m, fminf(acc[mi][ni][2 * hh], acc[mi][ni][2 * hh + 1]));
                 m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 1));
                 m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 2));
-                if (t4 == 0) wmin[(mi * 16 + h * 8 + g) * WARPS + warp] = m;
+                if (t4 == 0) wmin[(mi * 16 + hh * 8 + g) * WARPS + warp] = m;
             }
-        __syncthreads();
+        team_sync();
         if (tid < BM) {
             float m = wmin[tid * WARPS];
 #pragma unroll
             for (int w = 1; w < WARPS; ++w) m = fminf(m, wmin[tid * WARPS + w]);
-            // every column with v <= min v + delta has v~ <= min v~ + delta + 2E; NaN (non-finite input) fails the test
-            // below for every column of the row, which sends the row to the exact fix-up
+            // every column with v <= min v + delta has v~ <= min v~ + delta + 2E; a row without a finite minimum
+            // (non-finite input) goes to the exact fix-up
             thr_s[tid] = (m + (MODE == MODE_WINDOW ? __double2float_ru(a.delta) : 0.0f) + slack_s[tid]) * (1.0f + 1e-6f) +
                          1e-30f;
-            if (!(m < INFINITY)) ccnt[tid] = CAP + 1;               // nothing finite in the row
+            if (!(m < INFINITY)) ccnt[tid] = CAP + 1;
         }
-        __syncthreads();
-        // ---- candidates ----
+        team_sync();
+        // ---- candidates (columns past k carry +inf and never pass; rows past the end are never looked at again) ----
 #pragma unroll
-        for (int mi = 0; mi < 4; ++mi)
+        for (int mi = 0; mi < 2; ++mi)
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int row = mi * 16 + h * 8 + g;
+            for (int hh = 0; hh < 2; ++hh) {
+                const int row = mi * 16 + hh * 8 + g;
                 const float thr = thr_s[row];
 #pragma unroll
                 for (int ni = 0; ni < 4; ++ni)
 #pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const float v = acc[mi][ni][2 * h + e];
-                        const int col = warp * 32 + ni * 8 + 2 * t4 + e;
-                        if (row < rows && col < a.k && !(v > thr)) {
+                    for (int e = 0; e < 2; ++e)
+                        if (!(acc[mi][ni][2 * hh + e] > thr)) {
                             const int slot = atomicAdd(&ccnt[row], 1);
-                            if (slot < CAP) ccol[row * CAP + slot] = col;
+                            if (slot < CAP) ccol[row * CAP + slot] = warp * 32 + ni * 8 + 2 * t4 + e;
                         }
-                    }
             }
-        __syncthreads();
+        team_sync();
         // ---- fp64 for the candidates: a warp owns the rows warp, warp + 8, ...; its candidates, flattened, are dealt to
-        // its four groups of eight lanes, so that four fp64 dot products (their centroid rows come from L2) are in
-        // flight at a time.  The summation order of a dot product depends on (d) alone. ----
+        // its eight groups of four lanes, so that eight fp64 dot products (their centroid rows come from L2) are in
+        // flight at a time.  The summation order of a dot product depends on d alone. ----
         {
             constexpr int RPW = BM / WARPS;                    // rows per warp
-            const int grp = lane >> 3, sub = lane & 7;
+            const int grp = lane >> 2, sub = lane & 3;
             int pre[RPW + 1];
             pre[0] = 0;
 #pragma unroll
@@ -253,7 +268,7 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
                 pre[j + 1] = pre[j] + ((nc >= 1 && nc <= CAP) ? nc : 0);
             }
             const int total = pre[RPW];
-            for (int cbase = 0; cbase < total; cbase += 4) {       // (the same trip count for every lane: full-mask shuffles below)
+            for (int cbase = 0; cbase < total; cbase += 8) {       // (the same trip count for every lane: full-mask shuffles below)
                 const bool live = cbase + grp < total;
                 const int c = live ? cbase + grp : 0;
                 int j = 0;
@@ -267,14 +282,13 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
                 const double* xr = xt + (size_t)row * d;
                 const double* cr = a.C + (long long)col * d;
                 double p0 = 0.0, p1 = 0.0;
-                for (int f = 2 * sub; f < d; f += 16) {
+                for (int f = 2 * sub; f < d; f += 8) {
                     const double2 xv = *reinterpret_cast<const double2*>(xr + f);
                     const double2 cv = __ldg(reinterpret_cast<const double2*>(cr + f));
                     p0 = fma(xv.x, cv.x, p0);
                     p1 = fma(xv.y, cv.y, p1);
                 }
                 double p = p0 + p1;
-                p += __shfl_xor_sync(0xffffffffu, p, 4);
                 p += __shfl_xor_sync(0xffffffffu, p, 2);
                 p += __shfl_xor_sync(0xffffffffu, p, 1);
                 if (live && sub == 0) cval[row * CAP + slot] = fma(-2.0, p, cn_s[col]);
@@ -345,7 +359,7 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
                 }
             }
         }
-        __syncthreads();   // xs[stage], xb, ccnt, ccol free for the next tiles
+        team_sync();   // xs[stage], xb, ccnt, ccol free for the team's next tiles
     }
 }
 
