@@ -23,10 +23,12 @@
 namespace sq {
 
 struct FilterCfg {
-    // two teams of eight warps per CTA, each working on its own 32-row tiles (own ring, own barriers), sharing the
-    // bf16 centroids: what two CTAs per SM would be if the centroids did not have to be there twice
-    static constexpr int TEAMS = 2, TWARPS = 8, TTHREADS = 256, THREADS = TEAMS * TTHREADS;
+    // TEAMS teams of TWARPS warps per CTA, each working on its own BM-row tiles (own ring, own barriers), sharing the
+    // bf16 centroids: what several CTAs per SM would be if the centroids did not have to be there once per CTA
+    // (measured: 2 teams x 8 warps x 32 rows 1.35 ms per 2M x 128, 4 x 4 x 16 rows 1.36 ms, one team of 16 warps x 64 rows 1.65 ms)
+    static constexpr int TEAMS = 2, TWARPS = 8, TTHREADS = 32 * TWARPS, THREADS = TEAMS * TTHREADS;
     static constexpr int BM = 32, BN = 256, CAP = 8, DMAX = 128;
+    static constexpr int MI = BM / 16, WN = BN / TWARPS, NI = WN / 8, NP = NI / 2;   // warp tile: BM rows x WN columns
 };
 
 __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, unsigned bytes, unsigned long long* bar) {
@@ -67,6 +69,7 @@ template <int MODE>
 __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(AssignArgs a) {
     constexpr int BM = FilterCfg::BM, BN = FilterCfg::BN, CAP = FilterCfg::CAP, WARPS = FilterCfg::TWARPS;
     constexpr int TEAMS = FilterCfg::TEAMS, TT = FilterCfg::TTHREADS;
+    constexpr int MI = FilterCfg::MI, NI = FilterCfg::NI, NP = FilterCfg::NP, WN = FilterCfg::WN;
     extern __shared__ __align__(1024) unsigned char fsm[];
     const int d = a.d, cp = d + 8;
     const int team = threadIdx.x / TT, tid = threadIdx.x % TT, lane = tid & 31, warp = tid >> 5;
@@ -174,39 +177,39 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         }
         team_sync();
 
-        // ---- approximate x.c on the tensor cores: warp w of the team owns columns [32 w, 32 w + 32) of the 32 rows ----
-        float acc[2][4][4];
+        // ---- approximate x.c on the tensor cores: warp w of the team owns WN columns of the tile's rows ----
+        float acc[MI][NI][4];
 #pragma unroll
-        for (int mi = 0; mi < 2; ++mi)
+        for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni)
+            for (int ni = 0; ni < NI; ++ni)
 #pragma unroll
                 for (int r = 0; r < 4; ++r) acc[mi][ni][r] = 0.0f;
         const int a_row = (lane & 7) + 8 * ((lane >> 3) & 1), a_k = 8 * (lane >> 4);
         const int b_row = (lane & 7) + 8 * (lane >> 4), b_k = 8 * ((lane >> 3) & 1);
         for (int k0 = 0; k0 < d; k0 += 16) {
-            unsigned af[2][4], bf[2][4];
+            unsigned af[MI][4], bf[NP][4];
 #pragma unroll
-            for (int mi = 0; mi < 2; ++mi)
+            for (int mi = 0; mi < MI; ++mi)
                 ldmatrix_x4(af[mi][0], af[mi][1], af[mi][2], af[mi][3], xb + (size_t)(mi * 16 + a_row) * cp + k0 + a_k);
 #pragma unroll
-            for (int np = 0; np < 2; ++np)
+            for (int np = 0; np < NP; ++np)
                 ldmatrix_x4(bf[np][0], bf[np][1], bf[np][2], bf[np][3],
-                            cb + (size_t)(warp * 32 + np * 16 + b_row) * cp + k0 + b_k);
+                            cb + (size_t)(warp * WN + np * 16 + b_row) * cp + k0 + b_k);
 #pragma unroll
-            for (int mi = 0; mi < 2; ++mi)
+            for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
-                for (int ni = 0; ni < 4; ++ni)
+                for (int ni = 0; ni < NI; ++ni)
                     mma_bf16(acc[mi][ni], af[mi][0], af[mi][1], af[mi][2], af[mi][3], bf[ni >> 1][(ni & 1) * 2],
                              bf[ni >> 1][(ni & 1) * 2 + 1]);
         }
         // ---- v~ = |c|^2 - 2 x~.c~ in place; per-warp row minima ----
 #pragma unroll
-        for (int ni = 0; ni < 4; ++ni) {
-            const int col = warp * 32 + ni * 8 + 2 * t4;
+        for (int ni = 0; ni < NI; ++ni) {
+            const int col = warp * WN + ni * 8 + 2 * t4;
             const float c0 = (float)cn_s[col], c1 = (float)cn_s[col + 1];
 #pragma unroll
-            for (int mi = 0; mi < 2; ++mi) {
+            for (int mi = 0; mi < MI; ++mi) {
                 acc[mi][ni][0] = fmaf(-2.0f, acc[mi][ni][0], c0);
                 acc[mi][ni][1] = fmaf(-2.0f, acc[mi][ni][1], c1);
                 acc[mi][ni][2] = fmaf(-2.0f, acc[mi][ni][2], c0);
@@ -214,12 +217,12 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
             }
         }
 #pragma unroll
-        for (int mi = 0; mi < 2; ++mi)
+        for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
                 float m = INFINITY;
 #pragma unroll
-                for (int ni = 0; ni < 4; ++ni) m = fminf(m, fminf(acc[mi][ni][2 * hh], acc[mi][ni][2 * hh + 1]));
+                for (int ni = 0; ni < NI; ++ni) m = fminf(m, fminf(acc[mi][ni][2 * hh], acc[mi][ni][2 * hh + 1]));
                 m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 1));
                 m = fminf(m, __shfl_xor_sync(0xffffffffu, m, 2));
                 if (t4 == 0) wmin[(mi * 16 + hh * 8 + g) * WARPS + warp] = m;
@@ -238,18 +241,18 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         team_sync();
         // ---- candidates (columns past k carry +inf and never pass; rows past the end are never looked at again) ----
 #pragma unroll
-        for (int mi = 0; mi < 2; ++mi)
+        for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
             for (int hh = 0; hh < 2; ++hh) {
                 const int row = mi * 16 + hh * 8 + g;
                 const float thr = thr_s[row];
 #pragma unroll
-                for (int ni = 0; ni < 4; ++ni)
+                for (int ni = 0; ni < NI; ++ni)
 #pragma unroll
                     for (int e = 0; e < 2; ++e)
                         if (!(acc[mi][ni][2 * hh + e] > thr)) {
                             const int slot = atomicAdd(&ccnt[row], 1);
-                            if (slot < CAP) ccol[row * CAP + slot] = warp * 32 + ni * 8 + 2 * t4 + e;
+                            if (slot < CAP) ccol[row * CAP + slot] = warp * WN + ni * 8 + 2 * t4 + e;
                         }
             }
         team_sync();
