@@ -812,7 +812,8 @@ __global__ void qmeans_window_fixup_kernel(AssignArgs a) {
         }
         int label = amin;
         if (total > 0) {
-            Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, 1u);
+            // (rows the bf16 filter handed over with four candidates or fewer draw what the main kernel would have drawn)
+            Philox rng(a.seed, a.offset + (unsigned long long)gr, 0x51CEu, total > 4 ? 1u : 0u);
             int pick = (int)(rng.uniform() * total);
             if (pick >= total) pick = total - 1;
             int seen = 0;

@@ -49,6 +49,19 @@ __device__ __forceinline__ void mma_bf16(float (&c)[4], unsigned a0, unsigned a1
                  : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
 }
 
+// fp64 -> bf16, round to nearest (ties up), from the high word of the double alone: integer pipe only.  |error| <= 2^-8 |u|
+// (+ 2^-21 |u| for the low word that is not looked at); magnitudes below 2^-126 become 0, above bf16's range +-inf
+// (the row then has non-finite approximate distances and goes to the exact fix-up).
+__device__ __forceinline__ unsigned f64_to_bf16_bits(double u) {
+    const unsigned hi = (unsigned)__double2hiint(u);
+    const unsigned r = (hi & 0x7fffffffu) + 0x1000u;               // round at bit 13 of the high word
+    const unsigned em = r >> 13;                                   // 11-bit exponent : 7-bit mantissa
+    unsigned out = em - (896u << 7);                               // re-bias 1023 -> 127
+    if (em < (897u << 7)) out = 0u;
+    if (em >= (1151u << 7)) out = 0x7f80u;
+    return out | ((hi >> 16) & 0x8000u);
+}
+
 // dynamic shared memory of the kernel for feature count d (a multiple of 16, <= 128)
 __host__ __device__ inline size_t filter_smem_bytes(int d) {
     const size_t cp = (size_t)d + 8;                               // bf16 row pitch: rows 16 bytes apart modulo 128
@@ -114,7 +127,7 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         for (int j = t / h, c2 = t % h; j < BN;) {
             double2 v = make_double2(0.0, 0.0);
             if (j < a.k) v = *reinterpret_cast<const double2*>(a.C + (long long)j * d + 2 * c2);
-            *reinterpret_cast<__nv_bfloat162*>(cb + (size_t)j * cp + 2 * c2) = __floats2bfloat162_rn((float)v.x, (float)v.y);
+            *reinterpret_cast<unsigned*>(cb + (size_t)j * cp + 2 * c2) = f64_to_bf16_bits(v.x) | (f64_to_bf16_bits(v.y) << 16);
             j += sr; c2 += sc;
             if (c2 >= h) { c2 -= h; ++j; }
         }
@@ -164,7 +177,7 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         for (int r = r_first, c2 = c_first; r < BM;) {
             double2 v = *reinterpret_cast<const double2*>(xt + (size_t)r * d + 2 * c2);
             if (r >= rows) v = make_double2(0.0, 0.0);
-            *reinterpret_cast<__nv_bfloat162*>(xb + (size_t)r * cp + 2 * c2) = __floats2bfloat162_rn((float)v.x, (float)v.y);
+            *reinterpret_cast<unsigned*>(xb + (size_t)r * cp + 2 * c2) = f64_to_bf16_bits(v.x) | (f64_to_bf16_bits(v.y) << 16);
             r += step_r; c2 += step_c;
             if (c2 >= h) { c2 -= h; ++r; }
         }
@@ -239,22 +252,31 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
             if (!(m < INFINITY)) ccnt[tid] = CAP + 1;
         }
         team_sync();
-        // ---- candidates (columns past k carry +inf and never pass; rows past the end are never looked at again) ----
+        // ---- candidates (columns past k carry +inf and never pass; rows past the end are never looked at again):
+        // a bit per accumulator first, then a loop over the few hits ----
+        {
+            unsigned hits = 0u;
 #pragma unroll
-        for (int mi = 0; mi < MI; ++mi)
+            for (int mi = 0; mi < MI; ++mi)
 #pragma unroll
-            for (int hh = 0; hh < 2; ++hh) {
-                const int row = mi * 16 + hh * 8 + g;
-                const float thr = thr_s[row];
+                for (int hh = 0; hh < 2; ++hh) {
+                    const float thr = thr_s[mi * 16 + hh * 8 + g];
 #pragma unroll
-                for (int ni = 0; ni < NI; ++ni)
+                    for (int ni = 0; ni < NI; ++ni)
 #pragma unroll
-                    for (int e = 0; e < 2; ++e)
-                        if (!(acc[mi][ni][2 * hh + e] > thr)) {
-                            const int slot = atomicAdd(&ccnt[row], 1);
-                            if (slot < CAP) ccol[row * CAP + slot] = warp * WN + ni * 8 + 2 * t4 + e;
-                        }
+                        for (int e = 0; e < 2; ++e)
+                            hits |= (!(acc[mi][ni][2 * hh + e] > thr) ? 1u : 0u) << (((mi * 2 + hh) * NI + ni) * 2 + e);
+                }
+            static_assert(MI * 2 * NI * 2 <= 32, "one bit per accumulator");
+            while (hits) {
+                const int b = __ffs(hits) - 1;
+                hits &= hits - 1;
+                const int e = b & 1, ni = (b >> 1) % NI, mh = (b >> 1) / NI;
+                const int row = (mh >> 1) * 16 + (mh & 1) * 8 + g;
+                const int slot = atomicAdd(&ccnt[row], 1);
+                if (slot < CAP) ccol[row * CAP + slot] = warp * WN + ni * 8 + 2 * t4 + e;
             }
+        }
         team_sync();
         // ---- fp64 for the candidates: a warp owns the rows warp, warp + 8, ...; its candidates, flattened, are dealt to
         // its eight groups of four lanes, so that eight fp64 dot products (their centroid rows come from L2) are in
