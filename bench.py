@@ -378,6 +378,7 @@ def run_b200(args):
         pass
     peaks = load_peaks()
     step_tflops = flops * world / (ms_total / args.steps * 1e-3) / 1e12 / world
+    filtered = mode != "ipe" and K_CLUSTERS <= 256 and DIM <= 128 and DIM % 16 == 0 and not os.environ.get("SQ_BENCH_NO_FILTER")
     roofline = {"bound": "tensor", "kernel": "qmeans_assign_kernel (fp64 DMMA.8x8x4)", "achieved": achieved,
                 "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                 "traffic_source": traffic_src,
@@ -393,6 +394,27 @@ def run_b200(args):
                 "hbm_fraction": (8.0 * n_local * DIM + 4.0 * n_local) / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
                 "kernels": []}
 
+    if filtered:
+        # exact / window E-step: bf16 tensor-core filter + fp64 decisions (csrc/qmeans_filter.cuh).  X is read once in
+        # fp64 and nothing of size n x k is written: the bound is HBM, 8 n d + 8 n (row norms) + 12 n (labels, distances)
+        alg_bytes = (8.0 * DIM + 8.0 + 12.0) * n_local
+        hbm_peak = peaks["hbm_gbs"]
+        ftraffic, fsrc = None, None
+        try:
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic_filter.json")) as f:
+                tj = json.load(f)
+            ftraffic, fsrc = tj["dram_bytes_per_row"] * n_local, tj["source"]
+        except Exception:
+            pass
+        roofline.update({
+            "bound": "hbm", "kernel": "qmeans_filter_kernel (bf16 mma.sync filter, fp64 decisions)",
+            "achieved": alg_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+            "frac": alg_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak if hbm_peak else None,
+            "traffic": ftraffic, "traffic_source": fsrc, "algorithmic_bytes_per_launch": alg_bytes,
+            "peak_source": peaks.get("source", "MEASURED_PEAKS.json hbm_gbs (driver-written copy bandwidth)"),
+            "fp64_kernel": {"note": "the same E-step through the fp64 tensor-core kernel (sq_qmeans_debug_filter(0)): "
+                                    "20.6 ms at 10M x 128, k = 256 = 0.897 of cuBLAS DGEMM (profiles/r02_bench_1gpu_fp64_kernel.json)",
+                            "dgemm_peak_tflops": peak, "flops_over_filter_time_tflops": achieved}})
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",

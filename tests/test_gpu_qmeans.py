@@ -396,3 +396,58 @@ def test_ipe_pairs_left_out_change_nothing(cuda, case):
     np.testing.assert_array_equal(out[0][1], out[1][1])
     assert out[0][2] == out[1][2]
     assert np.isfinite(out[0][1]).all() and (out[0][0] >= 0).all() and (out[0][0] < k).all()
+
+
+FILTER_CASES = [  # n, d, k, delta, mode, data
+    (5000, 128, 256, 0.0, 0, "blobs"), (5000, 128, 256, 0.5, 1, "blobs"), (3000, 16, 40, 0.5, 1, "blobs"),
+    (3000, 64, 17, 0.0, 0, "rand"), (4000, 128, 256, 0.5, 1, "unit"), (2000, 32, 200, 2.0, 1, "rand"),
+    (4097, 128, 256, 0.0, 0, "dup"), (1000, 48, 3, 0.3, 1, "blobs"), (70, 128, 256, 0.5, 1, "blobs"),
+    (3000, 128, 256, 50.0, 1, "blobs"), (3000, 128, 100, 0.0, 0, "huge"), (2500, 96, 130, 0.0, 0, "tiny"),
+    (1800, 128, 256, 0.5, 1, "datacentres"), (1200, 64, 64, 0.0, 0, "nan"),
+]
+
+
+@pytest.mark.parametrize("case", range(len(FILTER_CASES)))
+def test_bf16_filter_changes_nothing(cuda, case):
+    """Exact and delta-window E-step: narrowing every row down to a few columns on the bf16 tensor cores (with a
+    rigorous error bound) and deciding on fp64 distances of those columns (csrc/qmeans_filter.cuh) must give the
+    labels of the fp64 tensor-core kernel, and its distances up to the rounding of two fp64 summation orders -
+    whatever the scale of the data, with duplicated centroids, null rows, windows wider than the filter keeps
+    columns for, centres that are data points, and non-finite input (which both paths hand to the exact fix-up)."""
+    import gpu_util as G
+    from sqlearn import _cabi
+    n, d, k, delta, mode, kind = FILTER_CASES[case]
+    rng = np.random.default_rng(200 + case)
+    cen = rng.normal(size=(k, d)) * 4
+    X = cen[rng.integers(0, k, n)] + rng.normal(size=(n, d))
+    C = cen + 0.1 * rng.normal(size=(k, d))
+    if kind == "rand":
+        X, C = rng.normal(size=(n, d)), rng.normal(size=(k, d))
+    elif kind == "unit":
+        C = cen / np.linalg.norm(cen, axis=1, keepdims=True)
+    elif kind == "dup":
+        C[5] = C[4]
+        C[7] = C[4]
+        X[::9] = 0.0
+    elif kind == "huge":
+        X, C = X * 1e6, C * 1e6
+    elif kind == "tiny":
+        X, C = X * 1e-20, C * 1e-20
+    elif kind == "datacentres":
+        C = X[:k].copy()
+    elif kind == "nan":
+        X[::101, 3] = np.nan
+        X[50::101, 7] = np.inf
+    out = []
+    for on in (1, 0):
+        _cabi.lib.sq_qmeans_debug_filter(on)
+        try:
+            lab, mind, inertia, nfix = G.assign(X, C, mode=mode, delta=delta, seed=5 + case)
+        finally:
+            _cabi.lib.sq_qmeans_debug_filter(1)
+        out.append((np.asarray(lab), np.asarray(mind), float(inertia)))
+    ok = np.isfinite(X).all(axis=1)
+    np.testing.assert_array_equal(out[0][0][ok], out[1][0][ok])
+    np.testing.assert_allclose(out[0][1][ok], out[1][1][ok], rtol=1e-11, atol=1e-11 * float(np.abs(X[ok]).max()) ** 2)
+    if ok.all():
+        assert abs(out[0][2] - out[1][2]) <= 1e-11 * abs(out[1][2])
