@@ -422,6 +422,9 @@ def run_b200(args):
                                    "%s E-step, M-step, centroid tomography (incremental+stop, delta/2)"
                                    % (args.rows, DIM, world, K_CLUSTERS, DELTA, mode),
                        "rows_per_gpu": n_local, "mode": mode,
+                       "estep": ("bf16 tensor-core filter with a rigorous error bound, every decision and every output in fp64 "
+                                 "(csrc/qmeans_filter.cuh); same labels and labels_crc as the fp64 tensor-core kernel"
+                                 if filtered else "fp64 tensor-core kernel (DMMA) for every pair"),
                        "dataset": "one fixed data set of %d rows, generated per 2^20-row block from the block id; "
                                   "rank r holds rows [r n/G, (r+1) n/G)" % args.rows,
                        "l2": "inputs (%.2f GB per GPU) exceed the 126 MB L2; no flush needed" % (n_local * DIM * 8 / 1e9),
