@@ -378,7 +378,7 @@ def run_b200(args):
         pass
     peaks = load_peaks()
     step_tflops = flops * world / (ms_total / args.steps * 1e-3) / 1e12 / world
-    filtered = mode != "ipe" and K_CLUSTERS <= 256 and DIM <= 128 and DIM % 16 == 0 and not os.environ.get("SQ_BENCH_NO_FILTER")
+    filtered = mode != "ipe" and K_CLUSTERS <= 256 and DIM <= 128 and DIM % 2 == 0 and not os.environ.get("SQ_BENCH_NO_FILTER")
     roofline = {"bound": "tensor", "kernel": "qmeans_assign_kernel (fp64 DMMA.8x8x4)", "achieved": achieved,
                 "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak if peak else None, "traffic": traffic,
                 "traffic_source": traffic_src,

@@ -149,7 +149,7 @@ int sq_qmeans_assign(const double* X, const double* xnorm, long long n, int d, c
  * the same row - labels, distances and inertia must come out bit for bit as with on = 0.  on = 0: normal.      */
 int sq_ipe_debug_force_replay(int on);
 /* Test hook (no reference counterpart).  on = 0: modes 0 and 1 of later sq_qmeans_assign calls run the fp64
- * tensor-core kernel for every shape; on = 1 (the default): shapes with k <= 256, d <= 128, d a multiple of 16 and
+ * tensor-core kernel for every shape; on = 1 (the default): shapes with k <= 256, d <= 128, d even and
  * 16-byte aligned X / C first narrow each row down to a few columns on the bf16 tensor cores, with a rigorous error
  * bound, and take every decision on fp64 distances of those columns (csrc/qmeans_filter.cuh).  Same labels; the
  * distances agree to the rounding of two fp64 summation orders.  Process-wide, not thread-safe.                  */

@@ -1117,7 +1117,7 @@ extern "C" int sq_qmeans_assign(const double* X, const double* xnorm, long long 
     a.fix_mindist = 0;
     // exact and delta-window modes, all centroids in one tile: filter on the bf16 tensor cores, decide in fp64
     // (qmeans_filter.cuh); otherwise the fp64 tensor-core kernel
-    const bool filter = g_filter_on && mode != MODE_IPE && k <= FilterCfg::BN && d <= FilterCfg::DMAX && d % 16 == 0 &&
+    const bool filter = g_filter_on && mode != MODE_IPE && k <= FilterCfg::BN && d <= FilterCfg::DMAX && d % 2 == 0 &&
                         ((uintptr_t)X & 15) == 0 && ((uintptr_t)C & 15) == 0;
     if (filter) {
         a.fix_mindist = 1;

@@ -64,9 +64,9 @@ __device__ __forceinline__ unsigned f64_to_bf16_bits(double u) {
     return out | ((hi >> 16) & 0x8000u);
 }
 
-// dynamic shared memory of the kernel for feature count d (a multiple of 16, <= 128)
+// dynamic shared memory of the kernel for feature count d (even, <= 128)
 __host__ __device__ inline size_t filter_smem_bytes(int d) {
-    const size_t cp = (size_t)d + 8;                               // bf16 row pitch: rows 16 bytes apart modulo 128
+    const size_t cp = (size_t)((d + 15) & ~15) + 8;               // bf16 row pitch (d padded to 16): rows 16 bytes apart modulo 128
     const size_t T = FilterCfg::TEAMS, BM = FilterCfg::BM;
     return T * 2 * BM * d * 8                                      // xs: two fp64 tiles per team
            + (size_t)FilterCfg::BN * cp * 2                        // cb: centroids, bf16
@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
     constexpr int TEAMS = FilterCfg::TEAMS, TT = FilterCfg::TTHREADS;
     constexpr int MI = FilterCfg::MI, NI = FilterCfg::NI, NP = FilterCfg::NP, WN = FilterCfg::WN;
     extern __shared__ __align__(1024) unsigned char fsm[];
-    const int d = a.d, cp = d + 8;
+    const int d = a.d, d16 = (d + 15) & ~15, cp = d16 + 8;        // (columns d .. d16 of the bf16 tiles stay zero)
     const int team = threadIdx.x / TT, tid = threadIdx.x % TT, lane = tid & 31, warp = tid >> 5;
     double* xs_all = reinterpret_cast<double*>(fsm);                                   // [TEAMS][2][BM*d]
     __nv_bfloat16* cb = reinterpret_cast<__nv_bfloat16*>(xs_all + (size_t)TEAMS * 2 * BM * d);   // [BN][cp]
@@ -120,6 +120,13 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
         mbar_init(&bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (d16 != d) {
+        // the padding columns of the bf16 tiles are zero for the whole launch
+        uint4* z = reinterpret_cast<uint4*>(cb);
+        const int n16 = (int)(((size_t)BN * cp + (size_t)TEAMS * BM * cp) * 2 / 16);
+        for (int i = threadIdx.x; i < n16; i += FilterCfg::THREADS) z[i] = make_uint4(0u, 0u, 0u, 0u);
+        __syncthreads();
     }
     // centroids: fp64 -> bf16 (zero rows past k), by the whole CTA
     // (pairs of features; a thread walks (row, pair) = (t / h, t % h), then + stride, without dividing again)
@@ -202,7 +209,7 @@ __global__ void __launch_bounds__(FilterCfg::THREADS, 1) qmeans_filter_kernel(As
                 for (int r = 0; r < 4; ++r) acc[mi][ni][r] = 0.0f;
         const int a_row = (lane & 7) + 8 * ((lane >> 3) & 1), a_k = 8 * (lane >> 4);
         const int b_row = (lane & 7) + 8 * (lane >> 4), b_k = 8 * ((lane >> 3) & 1);
-        for (int k0 = 0; k0 < d; k0 += 16) {
+        for (int k0 = 0; k0 < d16; k0 += 16) {
             unsigned af[MI][4], bf[NP][4];
 #pragma unroll
             for (int mi = 0; mi < MI; ++mi)

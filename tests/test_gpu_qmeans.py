@@ -404,6 +404,8 @@ FILTER_CASES = [  # n, d, k, delta, mode, data
     (4097, 128, 256, 0.0, 0, "dup"), (1000, 48, 3, 0.3, 1, "blobs"), (70, 128, 256, 0.5, 1, "blobs"),
     (3000, 128, 256, 50.0, 1, "blobs"), (3000, 128, 100, 0.0, 0, "huge"), (2500, 96, 130, 0.0, 0, "tiny"),
     (1800, 128, 256, 0.5, 1, "datacentres"), (1200, 64, 64, 0.0, 0, "nan"),
+    (2000, 10, 7, 0.0, 0, "blobs"), (2500, 50, 33, 0.5, 1, "blobs"), (1500, 100, 256, 0.0, 0, "rand"), (900, 2, 5, 0.3, 1, "blobs"),
+    (3100, 126, 200, 0.5, 1, "unit"),
 ]
 
 
@@ -412,7 +414,7 @@ def test_bf16_filter_changes_nothing(cuda, case):
     """Exact and delta-window E-step: narrowing every row down to a few columns on the bf16 tensor cores (with a
     rigorous error bound) and deciding on fp64 distances of those columns (csrc/qmeans_filter.cuh) must give the
     labels of the fp64 tensor-core kernel, and its distances up to the rounding of two fp64 summation orders -
-    whatever the scale of the data, with duplicated centroids, null rows, windows wider than the filter keeps
+    whatever the scale of the data, for any even number of features up to 128, with duplicated centroids, null rows, windows wider than the filter keeps
     columns for, centres that are data points, and non-finite input (which both paths hand to the exact fix-up)."""
     import gpu_util as G
     from sqlearn import _cabi
